@@ -1,0 +1,619 @@
+// C ABI (include/b200_infer.h) over the engine: contexts, model load, batched predict with
+// per-GPU pinned double-buffered staging and contiguous batch sharding (no collective), plus the
+// single-kernel entry points the parity tests drive.
+#include "../../include/b200_infer.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "engine.h"
+#include "resize.h"
+
+using namespace b2i;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+  return fail(e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? B2I_ENODEV : B2I_ECUDA,
+              std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CAPI_CUDA(call)                                   \
+  do {                                                    \
+    cudaError_t e_ = (call);                              \
+    if (e_ != cudaSuccess) return cuda_fail(e_, #call);   \
+  } while (0)
+
+inline uint16_t f2bf(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return static_cast<uint16_t>(u >> 16);
+}
+inline float bf2f(uint16_t h) {
+  uint32_t u = static_cast<uint32_t>(h) << 16;
+  float f;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
+};
+
+// fp32 host -> device in the kernel dtype
+cudaError_t upload(DevBuf* d, const float* src, size_t n, int prec) {
+  cudaError_t e = d->alloc(n * (prec == B2I_PREC_FP32 ? 4 : 2));
+  if (e != cudaSuccess) return e;
+  if (prec == B2I_PREC_FP32) return cudaMemcpy(d->p, src, n * 4, cudaMemcpyHostToDevice);
+  std::vector<uint16_t> t(n);
+  for (size_t i = 0; i < n; ++i) t[i] = f2bf(src[i]);
+  return cudaMemcpy(d->p, t.data(), n * 2, cudaMemcpyHostToDevice);
+}
+cudaError_t download(const void* dsrc, float* dst, size_t n, int prec) {
+  if (prec == B2I_PREC_FP32) return cudaMemcpy(dst, dsrc, n * 4, cudaMemcpyDeviceToHost);
+  std::vector<uint16_t> t(n);
+  cudaError_t e = cudaMemcpy(t.data(), dsrc, n * 2, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return e;
+  for (size_t i = 0; i < n; ++i) dst[i] = bf2f(t[i]);
+  return cudaSuccess;
+}
+
+bool is_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+}  // namespace
+
+struct b2i_ctx {
+  std::vector<int> devices;
+};
+
+// Per-GPU staging state of one model.
+struct DevSlot {
+  std::unique_ptr<DeviceModel> dm;
+  cudaStream_t copy_st = nullptr, comp_st = nullptr;
+  cudaEvent_t copied[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr};
+  uint8_t* h_stage[2] = {nullptr, nullptr};  // pinned
+  uint8_t* d_in[2] = {nullptr, nullptr};
+  int32_t* d_idx = nullptr;
+  float* d_prob = nullptr;
+  float* d_logits = nullptr;
+  int32_t* h_idx = nullptr;  // pinned results
+  float* h_prob = nullptr;
+  float* h_logits = nullptr;  // pinned, allocated on first use
+  int chunk = 0;
+};
+
+struct b2i_model {
+  b2i_ctx* ctx = nullptr;
+  std::string name;
+  double flops = 0;
+  std::vector<DevSlot> slots;
+  std::mutex mu;
+  int max_batch = 0;
+};
+
+namespace {
+
+void free_slot(DevSlot& s) {
+  if (!s.dm) return;
+  cudaSetDevice(s.dm->device());
+  for (int i = 0; i < 2; ++i) {
+    if (s.h_stage[i]) cudaFreeHost(s.h_stage[i]);
+    if (s.d_in[i]) cudaFree(s.d_in[i]);
+    if (s.copied[i]) cudaEventDestroy(s.copied[i]);
+    if (s.done[i]) cudaEventDestroy(s.done[i]);
+  }
+  if (s.d_idx) cudaFree(s.d_idx);
+  if (s.d_prob) cudaFree(s.d_prob);
+  if (s.d_logits) cudaFree(s.d_logits);
+  if (s.h_idx) cudaFreeHost(s.h_idx);
+  if (s.h_prob) cudaFreeHost(s.h_prob);
+  if (s.h_logits) cudaFreeHost(s.h_logits);
+  if (s.copy_st) cudaStreamDestroy(s.copy_st);
+  if (s.comp_st) cudaStreamDestroy(s.comp_st);
+  s.dm.reset();
+}
+
+// One GPU's share of a predict call. Returns 0 or a B2I_E* code with `err` filled.
+int run_slot(DevSlot& s, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
+             float* logits, std::string* err) {
+  if (n == 0) return B2I_OK;
+  auto cu = [&](cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return false;
+    *err = std::string(what) + ": " + cudaGetErrorString(e);
+    return true;
+  };
+  if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return B2I_ECUDA;
+  const bool pinned = is_pinned(images);
+  const int classes = s.dm->classes();
+  if (logits && !s.h_logits) {
+    if (cu(cudaMallocHost(reinterpret_cast<void**>(&s.h_logits),
+                          static_cast<size_t>(s.dm->max_batch()) * classes * 4), "cudaMallocHost(logits)"))
+      return B2I_ENOMEM;
+  }
+  int c = 0;
+  for (int off = 0; off < n; off += s.chunk, ++c) {
+    const int nb = std::min(s.chunk, n - off);
+    const int b = c & 1;
+    const size_t bytes = static_cast<size_t>(nb) * B2I_IMAGE_BYTES;
+    const uint8_t* src = images + static_cast<size_t>(off) * B2I_IMAGE_BYTES;
+    if (c >= 2) {
+      // slot b is free once the forward that read d_in[b] two chunks ago has finished
+      if (cu(cudaEventSynchronize(s.done[b]), "cudaEventSynchronize")) return B2I_ECUDA;
+    }
+    if (!pinned) {
+      std::memcpy(s.h_stage[b], src, bytes);
+      src = s.h_stage[b];
+    }
+    if (cu(cudaMemcpyAsync(s.d_in[b], src, bytes, cudaMemcpyHostToDevice, s.copy_st), "H2D copy")) return B2I_ECUDA;
+    if (cu(cudaEventRecord(s.copied[b], s.copy_st), "cudaEventRecord")) return B2I_ECUDA;
+    if (cu(cudaStreamWaitEvent(s.comp_st, s.copied[b], 0), "cudaStreamWaitEvent")) return B2I_ECUDA;
+    if (!s.dm->forward(s.d_in[b], nb, k, s.d_idx + static_cast<size_t>(off) * k,
+                       s.d_prob + static_cast<size_t>(off) * k,
+                       logits ? s.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, err))
+      return B2I_ECUDA;
+    if (cu(cudaEventRecord(s.done[b], s.comp_st), "cudaEventRecord")) return B2I_ECUDA;
+    // the next H2D into the other slot may start at once; the one after waits on `done`
+    if (cu(cudaStreamWaitEvent(s.copy_st, s.done[b], 0), "cudaStreamWaitEvent")) return B2I_ECUDA;
+  }
+  const size_t nk = static_cast<size_t>(n) * k;
+  if (cu(cudaMemcpyAsync(s.h_idx, s.d_idx, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H idx")) return B2I_ECUDA;
+  if (cu(cudaMemcpyAsync(s.h_prob, s.d_prob, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H prob")) return B2I_ECUDA;
+  if (logits &&
+      cu(cudaMemcpyAsync(s.h_logits, s.d_logits, static_cast<size_t>(n) * classes * 4,
+                         cudaMemcpyDeviceToHost, s.comp_st), "D2H logits"))
+    return B2I_ECUDA;
+  if (cu(cudaStreamSynchronize(s.comp_st), "cudaStreamSynchronize")) return B2I_ECUDA;
+  std::memcpy(idx, s.h_idx, nk * 4);
+  std::memcpy(prob, s.h_prob, nk * 4);
+  if (logits) std::memcpy(logits, s.h_logits, static_cast<size_t>(n) * classes * 4);
+  return B2I_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b2i_last_error(void) { return g_err.c_str(); }
+
+int b2i_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int b2i_init(const int* device_ids, int n_devices, b2i_ctx** out) {
+  if (!out || n_devices < 1 || !device_ids) return fail(B2I_EINVAL, "b2i_init: need at least one device id");
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return fail(B2I_ENODEV, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                                " (this library has no CPU path)");
+  }
+  auto ctx = std::make_unique<b2i_ctx>();
+  for (int i = 0; i < n_devices; ++i) {
+    const int d = device_ids[i];
+    if (d < 0 || d >= count) return fail(B2I_EINVAL, "b2i_init: device ordinal " + std::to_string(d) + " out of range");
+    cudaDeviceProp prop;
+    CAPI_CUDA(cudaGetDeviceProperties(&prop, d));
+    if (prop.major != 10)
+      return fail(B2I_ENODEV, "device " + std::to_string(d) + " (" + prop.name + ") is not sm_100; kernels are sm_100a only");
+    ctx->devices.push_back(d);
+  }
+  *out = ctx.release();
+  return B2I_OK;
+}
+
+void b2i_shutdown(b2i_ctx* ctx) { delete ctx; }
+
+void b2i_default_config(b2i_model_config* cfg) {
+  if (!cfg) return;
+  cfg->precision = B2I_PREC_BF16;
+  cfg->max_batch = 256;
+  cfg->micro_batch = 0;
+  cfg->alexnet_geometry = B2I_ALEXNET_TCH;
+  cfg->conv_mode = -1;
+  cfg->weights_tma = 1;
+  cfg->tile_n_max = 0;
+  cfg->keep_tensors = 0;
+}
+
+int b2i_ot_inspect(const char* path, char* names_out, size_t cap) {
+  if (!path) return fail(B2I_EINVAL, "null path");
+  std::map<std::string, HostTensor> t;
+  std::string err;
+  if (!read_ot_archive(path, &t, &err)) return fail(B2I_EIO, err);
+  if (names_out && cap) {
+    std::string s;
+    for (auto& kv : t) {
+      s += kv.first + ":";
+      for (size_t i = 0; i < kv.second.shape.size(); ++i) s += (i ? "x" : "") + std::to_string(kv.second.shape[i]);
+      s += "\n";
+    }
+    std::strncpy(names_out, s.c_str(), cap - 1);
+    names_out[cap - 1] = 0;
+  }
+  return static_cast<int>(t.size());
+}
+
+long long b2i_ot_read_tensor(const char* path, const char* name, float* out, long long cap) {
+  if (!path || !name) return fail(B2I_EINVAL, "null argument");
+  std::map<std::string, HostTensor> t;
+  std::string err;
+  if (!read_ot_archive(path, &t, &err)) return fail(B2I_EIO, err);
+  std::string key(name);
+  for (char& c : key) if (c == '|') c = '.';
+  auto it = t.find(key);
+  if (it == t.end()) return fail(B2I_EINVAL, "no tensor named " + key);
+  const long long n = it->second.numel();
+  if (out) {
+    if (cap < n) return fail(B2I_EINVAL, "output buffer too small");
+    std::memcpy(out, it->second.data.data(), static_cast<size_t>(n) * 4);
+  }
+  return n;
+}
+
+int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
+                   const b2i_model_config* cfg_in, b2i_model** out) {
+  if (!ctx || !model_name || !ot_path || !out) return fail(B2I_EINVAL, "b2i_model_load: null argument");
+  b2i_model_config cfg;
+  if (cfg_in) cfg = *cfg_in; else b2i_default_config(&cfg);
+  const std::string name(model_name);
+  if (name != "resnet18" && name != "alexnet")
+    return fail(B2I_EINVAL, "unknown model '" + name + "' (expected resnet18 or alexnet)");
+  if (cfg.precision != B2I_PREC_BF16 && cfg.precision != B2I_PREC_FP32) return fail(B2I_EINVAL, "bad precision");
+  if (cfg.max_batch < 1) return fail(B2I_EINVAL, "max_batch must be >= 1");
+  std::map<std::string, HostTensor> tensors;
+  std::string err;
+  if (!read_ot_archive(ot_path, &tensors, &err)) return fail(B2I_EIO, err);
+  NetSpec net;
+  const bool ok = name == "resnet18" ? build_resnet18(tensors, &net, &err)
+                                     : build_alexnet(tensors, cfg.alexnet_geometry, &net, &err);
+  if (!ok) return fail(B2I_EIO, err);
+  tensors.clear();
+
+  EngineConfig ec;
+  ec.precision = cfg.precision;
+  ec.max_batch = cfg.max_batch;
+  ec.micro_batch = cfg.micro_batch;
+  ec.alexnet_geometry = cfg.alexnet_geometry;
+  ec.conv_amode = cfg.conv_mode;
+  ec.b_tma = cfg.weights_tma;
+  if (cfg.tile_n_max > 0) ec.bn_max = cfg.tile_n_max;
+  ec.keep_tensors = cfg.keep_tensors;
+
+  auto m = std::make_unique<b2i_model>();
+  m->ctx = ctx;
+  m->name = name;
+  m->flops = net.flops_per_image;
+  m->max_batch = cfg.max_batch;
+  m->slots.resize(ctx->devices.size());
+  for (size_t i = 0; i < ctx->devices.size(); ++i) {
+    DevSlot& s = m->slots[i];
+    s.dm = std::make_unique<DeviceModel>();
+    if (!s.dm->init(ctx->devices[i], net, ec, &err)) {
+      for (auto& t : m->slots) free_slot(t);
+      return fail(B2I_ECUDA, err);
+    }
+    s.chunk = s.dm->micro_batch();
+    const size_t in_bytes = static_cast<size_t>(s.chunk) * B2I_IMAGE_BYTES;
+    const size_t nk = static_cast<size_t>(cfg.max_batch) * 8;
+    cudaError_t e = cudaSuccess;
+    auto chk = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    chk(cudaStreamCreateWithFlags(&s.copy_st, cudaStreamNonBlocking));
+    chk(cudaStreamCreateWithFlags(&s.comp_st, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      chk(cudaEventCreateWithFlags(&s.copied[b], cudaEventDisableTiming));
+      chk(cudaEventCreateWithFlags(&s.done[b], cudaEventDisableTiming));
+      chk(cudaMallocHost(reinterpret_cast<void**>(&s.h_stage[b]), in_bytes));
+      chk(cudaMalloc(reinterpret_cast<void**>(&s.d_in[b]), in_bytes));
+    }
+    chk(cudaMalloc(reinterpret_cast<void**>(&s.d_idx), nk * 4));
+    chk(cudaMalloc(reinterpret_cast<void**>(&s.d_prob), nk * 4));
+    chk(cudaMalloc(reinterpret_cast<void**>(&s.d_logits), static_cast<size_t>(cfg.max_batch) * B2I_CLASSES * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&s.h_idx), nk * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&s.h_prob), nk * 4));
+    if (e != cudaSuccess) {
+      for (auto& t : m->slots) free_slot(t);
+      return cuda_fail(e, "staging allocation");
+    }
+  }
+  *out = m.release();
+  return B2I_OK;
+}
+
+void b2i_model_free(b2i_model* m) {
+  if (!m) return;
+  for (auto& s : m->slots) free_slot(s);
+  delete m;
+}
+
+double b2i_model_flops_per_image(const b2i_model* m) { return m ? m->flops : 0; }
+int b2i_model_launches_per_microbatch(const b2i_model* m) {
+  return m && !m->slots.empty() ? static_cast<int>(m->slots[0].dm->launches_per_microbatch()) : 0;
+}
+int b2i_model_num_devices(const b2i_model* m) { return m ? static_cast<int>(m->slots.size()) : 0; }
+long long b2i_model_weight_bytes(const b2i_model* m) {
+  return m && !m->slots.empty() ? static_cast<long long>(m->slots[0].dm->weight_bytes()) : 0;
+}
+long long b2i_model_activation_bytes(const b2i_model* m) {
+  return m && !m->slots.empty() ? static_cast<long long>(m->slots[0].dm->activation_bytes()) : 0;
+}
+
+int b2i_predict_u8_on(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
+                      int32_t* idx, float* prob, float* logits) {
+  if (!m) return fail(B2I_EINVAL, "null model");
+  if (n < 0 || (n > 0 && (!images || !idx || !prob))) return fail(B2I_EINVAL, "b2i_predict_u8: null buffer");
+  if (k < 1 || k > 8) return fail(B2I_EINVAL, "k must be in 1..8");
+  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size()))
+    return fail(B2I_EINVAL, "device range outside the model's context");
+  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch)
+    return fail(B2I_EINVAL, "batch " + std::to_string(n) + " exceeds " + std::to_string(n_dev) + " GPU(s) x max_batch " +
+                                std::to_string(m->max_batch));
+  if (n == 0) return B2I_OK;
+  std::lock_guard<std::mutex> lock(m->mu);
+  // contiguous shards: GPU g takes images [g*per, min(n, (g+1)*per))
+  const int per = (n + n_dev - 1) / n_dev;
+  std::vector<int> rc(n_dev, B2I_OK);
+  std::vector<std::string> errs(n_dev);
+  auto work = [&](int g) {
+    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
+    rc[g] = run_slot(m->slots[first_dev + g], images + static_cast<size_t>(lo) * B2I_IMAGE_BYTES, hi - lo, k,
+                     idx + static_cast<size_t>(lo) * k, prob + static_cast<size_t>(lo) * k,
+                     logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, &errs[g]);
+  };
+  if (n_dev == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
+    for (auto& t : th) t.join();
+  }
+  for (int g = 0; g < n_dev; ++g)
+    if (rc[g] != B2I_OK) return fail(rc[g], "GPU " + std::to_string(first_dev + g) + ": " + errs[g]);
+  return B2I_OK;
+}
+
+int b2i_predict_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
+                   float* logits) {
+  if (!m) return fail(B2I_EINVAL, "null model");
+  return b2i_predict_u8_on(m, 0, static_cast<int>(m->slots.size()), images, n, k, idx, prob, logits);
+}
+
+int b2i_forward_device(b2i_model* m, int dev, const void* d_images, int n, int k, void* d_idx,
+                       void* d_prob, void* d_logits, void* stream) {
+  if (!m || dev < 0 || dev >= static_cast<int>(m->slots.size())) return fail(B2I_EINVAL, "bad model/device");
+  if (!d_images || !d_idx || !d_prob) return fail(B2I_EINVAL, "null device buffer");
+  std::string err;
+  if (!m->slots[dev].dm->forward(static_cast<const uint8_t*>(d_images), n, k, static_cast<int32_t*>(d_idx),
+                                 static_cast<float*>(d_prob), static_cast<float*>(d_logits),
+                                 static_cast<cudaStream_t>(stream), &err))
+    return fail(B2I_ECUDA, err);
+  return B2I_OK;
+}
+
+void* b2i_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+    g_err = "cudaMallocHost failed";
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+void b2i_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+long long b2i_model_read_tensor(b2i_model* m, int dev, int tensor_id, int n, float* out, long long cap) {
+  if (!m || dev < 0 || dev >= static_cast<int>(m->slots.size()) || !out) return fail(B2I_EINVAL, "bad argument");
+  std::vector<float> v;
+  std::string err;
+  if (!m->slots[dev].dm->read_tensor(tensor_id, n, &v, &err)) return fail(B2I_ECUDA, err);
+  if (static_cast<long long>(v.size()) > cap) return fail(B2I_EINVAL, "output buffer too small");
+  std::memcpy(out, v.data(), v.size() * 4);
+  return static_cast<long long>(v.size());
+}
+int b2i_model_num_tensors(const b2i_model* m) { return m && !m->slots.empty() ? m->slots[0].dm->num_tensors() : 0; }
+int b2i_model_tensor_shape(const b2i_model* m, int id, int* h, int* w, int* c) {
+  if (!m || m->slots.empty() || id < 0 || id >= m->slots[0].dm->num_tensors()) return fail(B2I_EINVAL, "bad tensor id");
+  const TensorShape s = m->slots[0].dm->tensor_shape(id);
+  if (h) *h = s.H;
+  if (w) *w = s.W;
+  if (c) *c = s.C;
+  return B2I_OK;
+}
+
+int b2i_resize_crop_u8(b2i_ctx* ctx, int dev, const uint8_t* image, int h, int w, uint8_t* out224) {
+  if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devices.size()) || !image || !out224 || h < 1 || w < 1)
+    return fail(B2I_EINVAL, "b2i_resize_crop_u8: bad argument");
+  CAPI_CUDA(cudaSetDevice(ctx->devices[dev]));
+  std::string err;
+  if (!resize_crop_224_host(image, h, w, out224, nullptr, &err)) return fail(B2I_ECUDA, err);
+  return B2I_OK;
+}
+
+// ------------------------------------------------------------------ single-kernel entry points
+static int ctx_dev(b2i_ctx* ctx, int dev) {
+  if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devices.size())) return fail(B2I_EINVAL, "bad context/device");
+  CAPI_CUDA(cudaSetDevice(ctx->devices[dev]));
+  return B2I_OK;
+}
+
+int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weights_tma, int tile_n,
+                  const float* x, int N, int H, int W, int C, const float* w, const float* bias,
+                  const float* bn, int Cout, int R, int S, int stride, int pad,
+                  const float* residual, int relu, float* out) {
+  if (int rc = ctx_dev(ctx, dev)) return rc;
+  if (!x || !w || !out || N < 1 || C < 1 || Cout < 1) return fail(B2I_EINVAL, "b2i_op_conv2d: bad argument");
+  ConvSpec cs;
+  build_conv_spec(&cs, "op", w, bias, bn, bn ? bn + Cout : nullptr, bn ? bn + 2 * Cout : nullptr,
+                  bn ? bn + 3 * Cout : nullptr, Cout, C, R, S, stride, pad);
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  if (OH < 1 || OW < 1) return fail(B2I_EINVAL, "empty output");
+  // channel-pad the input
+  const size_t npix = static_cast<size_t>(N) * H * W;
+  std::vector<float> xp(npix * cs.Cin_pad, 0.f);
+  for (size_t p = 0; p < npix; ++p) std::memcpy(&xp[p * cs.Cin_pad], &x[p * C], static_cast<size_t>(C) * 4);
+  DevBuf dx, dw, db, dr, dout;
+  CAPI_CUDA(upload(&dx, xp.data(), xp.size(), precision));
+  CAPI_CUDA(upload(&dw, cs.w.data(), cs.w.size(), precision));
+  CAPI_CUDA(upload(&db, cs.bias.data(), cs.bias.size(), B2I_PREC_FP32));
+  const size_t nout = static_cast<size_t>(N) * OH * OW * Cout;
+  const bool bf16 = precision == B2I_PREC_BF16;
+  const bool out32 = bf16 && (Cout % 32 != 0);
+  if (out32 && residual) return fail(B2I_EINVAL, "bf16 conv with a residual needs Cout % 32 == 0");
+  if (residual) CAPI_CUDA(upload(&dr, residual, nout, precision));
+  CAPI_CUDA(dout.alloc(nout * 4));
+  CAPI_CUDA(cudaMemset(dout.p, 0xFF, nout * (bf16 && !out32 ? 2 : 4)));  // NaN canary
+  ConvArgs a;
+  ConvGeom& g = a.g;
+  g.N = N; g.H = H; g.W = W; g.C = cs.Cin_pad; g.OH = OH; g.OW = OW; g.R = R; g.S = S; g.Sp = cs.Sp;
+  g.stride = stride; g.pad = pad; g.Cout = Cout; g.Cout_pad = cs.Cout_pad; g.K = cs.K; g.M = N * OH * OW;
+  a.x = dx.p; a.w = dw.p; a.bias = static_cast<const float*>(db.p); a.residual = residual ? dr.p : nullptr;
+  a.out = dout.p; a.ldo = Cout; a.relu = relu; a.out_fp32 = out32 ? 1 : 0;
+  int bnv = tile_n > 0 ? tile_n : 128;
+  bnv = std::min(bnv, 256) / 32 * 32;
+  while (bnv > 32 && cs.Cout_pad % bnv) bnv -= 32;
+  a.BN = bnv;
+  a.stages = conv_umma_pick_stages(bnv);
+  a.amode = cs.smallc ? A_SMALLC : (conv_mode == 1 ? A_IM2COL : A_GATHER);
+  a.b_tma = (a.amode == A_IM2COL) ? 1 : weights_tma;
+  if (!bf16) {
+    CAPI_CUDA(launch_conv_fp32(a, nullptr));
+  } else {
+    CUtensorMap tmA, tmB;
+    const char* terr = "";
+    if (a.b_tma && make_tmap_weights(&tmB, dw.p, cs.Cout_pad, cs.K, a.BN, &terr)) return fail(B2I_ECUDA, terr);
+    if (a.amode == A_IM2COL && make_tmap_im2col(&tmA, dx.p, g, N, &terr)) return fail(B2I_ECUDA, terr);
+    CAPI_CUDA(launch_conv_umma(a, a.amode == A_IM2COL ? &tmA : nullptr, a.b_tma ? &tmB : nullptr, nullptr));
+  }
+  CAPI_CUDA(cudaDeviceSynchronize());
+  CAPI_CUDA(download(dout.p, out, nout, out32 ? B2I_PREC_FP32 : precision));
+  return B2I_OK;
+}
+
+int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float* x, int M, int K,
+                  const float* w, const float* bias, int Cout, int relu, float* out) {
+  if (int rc = ctx_dev(ctx, dev)) return rc;
+  if (!x || !w || !out || M < 1 || K < 1 || Cout < 1) return fail(B2I_EINVAL, "b2i_op_linear: bad argument");
+  ConvSpec cs;
+  build_conv_spec(&cs, "op", w, bias, nullptr, nullptr, nullptr, nullptr, Cout, K, 1, 1, 1, 0);
+  // K may have been padded to a multiple of 64 (and to 4 when K < 8): pad x to cs.K columns
+  std::vector<float> xp(static_cast<size_t>(M) * cs.K, 0.f);
+  for (int m = 0; m < M; ++m) std::memcpy(&xp[static_cast<size_t>(m) * cs.K], &x[static_cast<size_t>(m) * K], static_cast<size_t>(K) * 4);
+  if (cs.smallc) return fail(B2I_EINVAL, "b2i_op_linear: K must be >= 8");
+  DevBuf dx, dw, db, dout;
+  CAPI_CUDA(upload(&dx, xp.data(), xp.size(), precision));
+  CAPI_CUDA(upload(&dw, cs.w.data(), cs.w.size(), precision));
+  CAPI_CUDA(upload(&db, cs.bias.data(), cs.bias.size(), B2I_PREC_FP32));
+  const size_t nout = static_cast<size_t>(M) * Cout;
+  CAPI_CUDA(dout.alloc(nout * 4));
+  ConvArgs a;
+  ConvGeom& g = a.g;
+  g.N = M; g.H = g.W = 1; g.C = cs.K; g.OH = g.OW = 1; g.R = g.S = g.Sp = 1; g.stride = 1; g.pad = 0;
+  g.Cout = Cout; g.Cout_pad = cs.Cout_pad; g.K = cs.K; g.M = M;
+  a.x = dx.p; a.w = dw.p; a.bias = static_cast<const float*>(db.p); a.residual = nullptr; a.out = dout.p;
+  a.ldo = Cout; a.relu = relu; a.out_fp32 = 1;
+  int bnv = tile_n > 0 ? tile_n : 128;
+  bnv = std::min(bnv, 256) / 32 * 32;
+  while (bnv > 32 && cs.Cout_pad % bnv) bnv -= 32;
+  a.BN = bnv; a.stages = conv_umma_pick_stages(bnv); a.amode = A_TILED; a.b_tma = 1;
+  if (precision == B2I_PREC_FP32) {
+    CAPI_CUDA(launch_conv_fp32(a, nullptr));
+  } else {
+    CUtensorMap tmA, tmB;
+    const char* terr = "";
+    if (make_tmap_weights(&tmB, dw.p, cs.Cout_pad, cs.K, a.BN, &terr)) return fail(B2I_ECUDA, terr);
+    if (make_tmap_rows(&tmA, dx.p, M, cs.K, 128, &terr)) return fail(B2I_ECUDA, terr);
+    CAPI_CUDA(launch_conv_umma(a, &tmA, &tmB, nullptr));
+  }
+  CAPI_CUDA(cudaDeviceSynchronize());
+  CAPI_CUDA(cudaMemcpy(out, dout.p, nout * 4, cudaMemcpyDeviceToHost));
+  return B2I_OK;
+}
+
+int b2i_op_maxpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, int H, int W, int C,
+                   int k, int stride, int pad, float* out) {
+  if (int rc = ctx_dev(ctx, dev)) return rc;
+  const int OH = (H + 2 * pad - k) / stride + 1, OW = (W + 2 * pad - k) / stride + 1;
+  DevBuf dx, dout;
+  const size_t nin = static_cast<size_t>(N) * H * W * C, nout = static_cast<size_t>(N) * OH * OW * C;
+  CAPI_CUDA(upload(&dx, x, nin, precision));
+  CAPI_CUDA(dout.alloc(nout * 4));
+  CAPI_CUDA(launch_maxpool(dx.p, dout.p, precision == B2I_PREC_FP32 ? DT_F32 : DT_BF16, N, H, W, C, k, stride, pad, OH, OW, nullptr));
+  CAPI_CUDA(cudaDeviceSynchronize());
+  CAPI_CUDA(download(dout.p, out, nout, precision));
+  return B2I_OK;
+}
+
+int b2i_op_adaptive_avgpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, int H,
+                            int W, int C, int OH, int OW, float* out) {
+  if (int rc = ctx_dev(ctx, dev)) return rc;
+  DevBuf dx, dout;
+  const size_t nin = static_cast<size_t>(N) * H * W * C, nout = static_cast<size_t>(N) * OH * OW * C;
+  CAPI_CUDA(upload(&dx, x, nin, precision));
+  CAPI_CUDA(dout.alloc(nout * 4));
+  CAPI_CUDA(launch_adaptive_avgpool(dx.p, dout.p, precision == B2I_PREC_FP32 ? DT_F32 : DT_BF16, N, H, W, C, OH, OW, nullptr));
+  CAPI_CUDA(cudaDeviceSynchronize());
+  CAPI_CUDA(download(dout.p, out, nout, precision));
+  return B2I_OK;
+}
+
+int b2i_op_normalize(b2i_ctx* ctx, int dev, int precision, const uint8_t* images, int n, float* out) {
+  if (int rc = ctx_dev(ctx, dev)) return rc;
+  if (!images || !out || n < 1) return fail(B2I_EINVAL, "b2i_op_normalize: bad argument");
+  DevBuf din, dout;
+  const size_t nin = static_cast<size_t>(n) * B2I_IMAGE_BYTES, nout = static_cast<size_t>(n) * 224 * 224 * 4;
+  CAPI_CUDA(din.alloc(nin));
+  CAPI_CUDA(cudaMemcpy(din.p, images, nin, cudaMemcpyHostToDevice));
+  CAPI_CUDA(dout.alloc(nout * 4));
+  CAPI_CUDA(launch_normalize_u8(static_cast<const uint8_t*>(din.p), dout.p, precision == B2I_PREC_FP32 ? DT_F32 : DT_BF16,
+                                static_cast<long long>(n) * 224 * 224, nullptr));
+  CAPI_CUDA(cudaDeviceSynchronize());
+  CAPI_CUDA(download(dout.p, out, nout, precision));
+  return B2I_OK;
+}
+
+int b2i_op_softmax_topk(b2i_ctx* ctx, int dev, const float* logits, int rows, int classes, int k,
+                        int32_t* idx, float* prob) {
+  if (int rc = ctx_dev(ctx, dev)) return rc;
+  if (!logits || !idx || !prob || rows < 1) return fail(B2I_EINVAL, "b2i_op_softmax_topk: bad argument");
+  DevBuf dl, di, dp;
+  CAPI_CUDA(dl.alloc(static_cast<size_t>(rows) * classes * 4));
+  CAPI_CUDA(cudaMemcpy(dl.p, logits, static_cast<size_t>(rows) * classes * 4, cudaMemcpyHostToDevice));
+  CAPI_CUDA(di.alloc(static_cast<size_t>(rows) * k * 4));
+  CAPI_CUDA(dp.alloc(static_cast<size_t>(rows) * k * 4));
+  CAPI_CUDA(launch_softmax_topk(static_cast<const float*>(dl.p), rows, classes, classes, k,
+                                static_cast<int32_t*>(di.p), static_cast<float*>(dp.p), nullptr));
+  CAPI_CUDA(cudaDeviceSynchronize());
+  CAPI_CUDA(cudaMemcpy(idx, di.p, static_cast<size_t>(rows) * k * 4, cudaMemcpyDeviceToHost));
+  CAPI_CUDA(cudaMemcpy(prob, dp.p, static_cast<size_t>(rows) * k * 4, cudaMemcpyDeviceToHost));
+  return B2I_OK;
+}
+
+}  // extern "C"

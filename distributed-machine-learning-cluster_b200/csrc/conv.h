@@ -1,0 +1,62 @@
+// Convolution / FC as implicit GEMM: shared parameter block and launch entry points.
+//
+// GEMM view: M = N*OH*OW output pixels, N = Cout, K = R*S*C.
+// Activations are NHWC; weights are [Cout_pad][K] (K-major) with K ordered (r, s, c) so a
+// 64-wide K block of a C>=64 layer is one filter tap and 64 consecutive channels.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2i {
+
+enum AMode : int {
+  A_GATHER = 0,   // cp.async gather of 16-byte channel chunks, any geometry with C % 64 == 0
+  A_IM2COL = 1,   // TMA im2col-mode tensor map, C % 64 == 0
+  A_TILED = 2,    // plain 2-D TMA over an [M][K] matrix (FC layers)
+  A_SMALLC = 3,   // cp.async gather of 8-byte pixels for C == 4 (first layer, K = R*Sp*4)
+};
+
+struct ConvGeom {
+  int N, H, W, C;       // input, NHWC; C already padded (4 for the first layer, else multiple of 64)
+  int OH, OW;           // output spatial
+  int R, S, Sp;         // filter window; Sp = S padded (A_SMALLC only, else Sp == S)
+  int stride, pad;
+  int Cout;             // real output channels (stores are bounded by it)
+  int Cout_pad;         // rows in the weight matrix (multiple of BN)
+  int K;                // padded GEMM K, multiple of 64
+  int M;                // N*OH*OW for the CURRENT batch
+};
+
+struct ConvArgs {
+  ConvGeom g;
+  const void* x;        // bf16 NHWC (or [M][K] for A_TILED); fp32 in the fp32 kernel
+  const void* w;        // [Cout_pad][K]
+  const float* bias;    // [Cout_pad] folded BN shift / conv bias
+  const void* residual; // optional, same layout/dtype as out
+  void* out;            // [M][ldo]
+  int ldo;              // output row stride in elements
+  int relu;
+  int out_fp32;         // bf16 kernel only: write fp32 (logits)
+  int BN;               // tile N (multiple of 32, <= 256)
+  int stages;
+  int amode;
+  int b_tma;            // 1: weights through TMA, 0: cp.async gather (A_GATHER / A_SMALLC only)
+};
+
+// bf16 tcgen05 path.  tmA / tmB may be null when the corresponding operand is gathered.
+cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
+                             cudaStream_t st);
+size_t conv_umma_smem_bytes(int BN, int stages);
+int conv_umma_pick_stages(int BN);
+
+// fp32 FFMA path (the 1e-4 parity mode; also the on-device cross-check for the tcgen05 path).
+cudaError_t launch_conv_fp32(const ConvArgs& a, cudaStream_t st);
+
+// Tensor-map builders (driver entry points resolved at run time; no link against libcuda).
+// Return 0 on success, else a CUresult / negative code; message in *err.
+int make_tmap_weights(CUtensorMap* tm, const void* w, int Cout_pad, int K, int BN, const char** err);
+int make_tmap_im2col(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax, const char** err);
+int make_tmap_rows(CUtensorMap* tm, const void* a, int rows, int K, int box_rows, const char** err);
+
+}  // namespace b2i

@@ -1,0 +1,456 @@
+// bf16 implicit-GEMM convolution / FC on the 5th-gen tensor cores (tcgen05 + TMEM), sm_100a only.
+//
+// Replaces the libtorch-CPU conv2d / linear calls the reference reaches through
+// `forward_t` (reference src/services.rs:493, model graphs in tch::vision::{resnet,alexnet},
+// SURVEY.md 2.3 / Appendix C).  Eval-mode BatchNorm is folded into the weights at load time, so
+// the epilogue is  out = relu?( acc + bias (+ residual) )  with one bf16 rounding per layer.
+//
+// One CTA computes one 128 x BN output tile (128 output pixels x BN output channels):
+//   warps 0-3  producer (gather modes: cp.async im2col gather into 128B-swizzled smem) and,
+//              after the main loop, epilogue (TMEM -> registers -> bias/residual/ReLU -> global)
+//   warp  4    TMA producer: im2col-mode / tiled tensor maps for A, tiled map for the weights
+//   warp  5    TMEM allocation + single-thread tcgen05.mma issue, tcgen05.commit -> mbarriers
+// Operand tiles are K-major rows of 64 bf16 (128 bytes) with the 128-byte swizzle, which is what
+// both TMA (CU_TENSOR_MAP_SWIZZLE_128B) and the hand gather produce and what the UMMA shared-memory
+// descriptors in ptx.cuh declare.
+#include "conv.h"
+#include "ptx.cuh"
+
+namespace b2i {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int A_TILE_BYTES = BM * BK * 2;
+constexpr int MAX_STAGES = 8;
+constexpr int NTHREADS = 192;
+constexpr int LAG = 2;  // cp.async groups kept in flight per gather thread (needs stages >= 3)
+
+struct KP {
+  int H, W, C, OH, OW, R, S, Sp, stride, pad;
+  int Cout, K, M, BN, stages, num_kb, tiles_n, ldo, relu, out_fp32;
+  uint32_t tmem_cols;
+  const __nv_bfloat16* x;
+  const __nv_bfloat16* w;
+  const float* bias;
+  const __nv_bfloat16* residual;
+  void* out;
+};
+
+template <int AMODE, bool B_TMA>
+__global__ void __launch_bounds__(NTHREADS)
+conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const KP p) {
+  constexpr bool A_IS_TMA = (AMODE == A_IM2COL || AMODE == A_TILED);
+  static_assert(!(A_IS_TMA && !B_TMA), "TMA A with gathered B is not a supported combination");
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 1];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tile_n = blockIdx.x % p.tiles_n;
+  const int tile_m = blockIdx.x / p.tiles_n;
+  const int m0 = tile_m * BM;
+  const int n0 = tile_n * p.BN;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_tile_bytes = static_cast<uint32_t>(p.BN) * 128u;
+  const uint32_t stage_bytes = A_TILE_BYTES + b_tile_bytes;
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
+  const uint32_t tmem_full_bar = bar0 + 8u * (2 * MAX_STAGES);
+
+  if (threadIdx.x == 0) {
+    const uint32_t full_count = (A_IS_TMA ? 0u : 128u) + (B_TMA ? 1u : 0u);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full_bar(s), full_count);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 4 && lane == 0) {
+    if (A_IS_TMA) tma_prefetch_desc(&tmA);
+    if (B_TMA) tma_prefetch_desc(&tmB);
+  }
+  if (warp == 5) tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp < 4) {
+    // ------------------------------------------------------------------ gather producer
+    if (!A_IS_TMA) {
+      const int t = threadIdx.x;
+      const int chunk = t & 7;   // 16-byte chunk inside the 128-byte row
+      const int r0 = t >> 3;     // rows r0 + 16*i
+      const uint32_t swz = static_cast<uint32_t>(chunk ^ (r0 & 7)) << 4;
+      int ih0[8], iw0[8];
+      const __nv_bfloat16* rowbase[8];
+      const int ohw = p.OH * p.OW;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int m = m0 + r0 + 16 * i;
+        if (m < p.M) {
+          const int n = m / ohw;
+          const int rem = m - n * ohw;
+          const int oh = rem / p.OW;
+          const int ow = rem - oh * p.OW;
+          ih0[i] = oh * p.stride - p.pad;
+          iw0[i] = ow * p.stride - p.pad;
+          rowbase[i] = p.x + static_cast<size_t>(n) * p.H * p.W * p.C;
+        } else {
+          ih0[i] = -(1 << 28);  // every tap lands out of bounds -> zero fill
+          iw0[i] = 0;
+          rowbase[i] = p.x;
+        }
+      }
+      const int cpb = (AMODE == A_GATHER) ? (p.C >> 6) : 1;  // 64-channel blocks per tap
+      const int b_passes = p.BN >> 4;
+      int s_w = 0, ph_w = 0;  // stage / phase of the k-block being issued
+      int s_a = 0;            // stage of the k-block being published
+      for (int it = 0; it < p.num_kb + LAG; ++it) {
+        if (it < p.num_kb) {
+          mbar_wait(empty_bar(s_w), ph_w ^ 1);
+          const uint32_t a_s = smem_base + s_w * stage_bytes;
+          if (AMODE == A_GATHER) {
+            const int tap = it / cpb;
+            const int c0 = (it - tap * cpb) << 6;
+            const int r = tap / p.S;
+            const int s = tap - r * p.S;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int ih = ih0[i] + r;
+              const int iw = iw0[i] + s;
+              const bool ok = (ih >= 0) && (ih < p.H) && (iw >= 0) && (iw < p.W);
+              const __nv_bfloat16* src =
+                  ok ? rowbase[i] + (static_cast<size_t>(ih) * p.W + iw) * p.C + c0 + chunk * 8
+                     : p.x;
+              cp_async16(a_s + static_cast<uint32_t>(r0 + 16 * i) * 128u + swz, src, ok ? 16u : 0u);
+            }
+          } else {  // A_SMALLC: C == 4, one 8-byte pixel per tap, two taps per 16-byte chunk
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int tap = it * 16 + chunk * 2 + h;
+              const int r = tap / p.Sp;
+              const int s = tap - r * p.Sp;
+              const bool tap_ok = (r < p.R) && (s < p.S);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const int ih = ih0[i] + r;
+                const int iw = iw0[i] + s;
+                const bool ok = tap_ok && (ih >= 0) && (ih < p.H) && (iw >= 0) && (iw < p.W);
+                const __nv_bfloat16* src =
+                    ok ? rowbase[i] + (static_cast<size_t>(ih) * p.W + iw) * 4 : p.x;
+                cp_async8(a_s + static_cast<uint32_t>(r0 + 16 * i) * 128u + swz + 8u * h, src,
+                          ok ? 8u : 0u);
+              }
+            }
+          }
+          if (!B_TMA) {
+            const uint32_t b_s = a_s + A_TILE_BYTES;
+            const __nv_bfloat16* wsrc =
+                p.w + static_cast<size_t>(n0 + r0) * p.K + static_cast<size_t>(it) * BK + chunk * 8;
+            for (int i = 0; i < b_passes; ++i) {
+              cp_async16(b_s + static_cast<uint32_t>(r0 + 16 * i) * 128u + swz,
+                         wsrc + static_cast<size_t>(16 * i) * p.K, 16u);
+            }
+          }
+          if (++s_w == p.stages) { s_w = 0; ph_w ^= 1; }
+        }
+        cp_async_commit();
+        if (it >= LAG) {
+          cp_async_wait<LAG>();       // k-block (it - LAG) has landed for this thread
+          fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor-core proxy
+          mbar_arrive(full_bar(s_a));
+          if (++s_a == p.stages) s_a = 0;
+        }
+      }
+    }
+
+    // ------------------------------------------------------------------ epilogue
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int m = m0 + warp * 32 + lane;
+    const bool row_ok = m < p.M;
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+    const int n_chunks = p.BN >> 5;
+    for (int c = 0; c < n_chunks; ++c) {
+      uint32_t v[32];
+      tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+      tmem_ld_wait();
+      if (!row_ok) continue;
+      const int nb = n0 + c * 32;
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + nb + j);
+      if (p.out_fp32) {
+        float* o = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (nb + 32 <= p.Cout && (p.ldo & 3) == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.Cout) o[j] = f[j];
+        }
+      } else {
+        if (nb >= p.Cout) continue;
+        const size_t off = static_cast<size_t>(m) * p.ldo + nb;
+        if (p.residual) {
+          const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint4 rv = __ldg(rp + q);
+            const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              f[q * 8 + e * 2] += bf16_lo(rr[e]);
+              f[q * 8 + e * 2 + 1] += bf16_hi(rr[e]);
+            }
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 ov;
+          ov.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
+          ov.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
+          ov.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
+          ov.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
+          op[q] = ov;
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ------------------------------------------------------------------ TMA producer
+    if (B_TMA && lane == 0) {
+      int iw_base = 0, ih_base = 0, n_base = 0;
+      if (AMODE == A_IM2COL) {
+        const int ohw = p.OH * p.OW;
+        n_base = m0 / ohw;
+        const int rem = m0 - n_base * ohw;
+        const int oh = rem / p.OW;
+        const int ow = rem - oh * p.OW;
+        ih_base = oh * p.stride - p.pad;
+        iw_base = ow * p.stride - p.pad;
+      }
+      const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
+      const uint32_t tx = b_tile_bytes + (A_IS_TMA ? A_TILE_BYTES : 0);
+      int s = 0, ph = 0;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(empty_bar(s), ph ^ 1);
+        const uint32_t a_s = smem_base + s * stage_bytes;
+        mbar_expect_tx(full_bar(s), tx);
+        if (AMODE == A_IM2COL) {
+          const int tap = kb / cpb;
+          const int c0 = (kb - tap * cpb) << 6;
+          const int r = tap / p.S;
+          const int sx = tap - r * p.S;
+          tma_load_im2col_4d(a_s, &tmA, full_bar(s), c0, iw_base, ih_base, n_base,
+                             static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
+        } else if (AMODE == A_TILED) {
+          tma_load_2d(a_s, &tmA, full_bar(s), kb * BK, m0);
+        }
+        tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+        if (++s == p.stages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ MMA issuer (warp 5)
+    const uint32_t idesc = umma_idesc_bf16(BM, p.BN);
+    int s = 0, ph = 0;
+    for (int kb = 0; kb < p.num_kb; ++kb) {
+      mbar_wait(full_bar(s), ph);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t a_s = smem_base + s * stage_bytes;
+        const uint64_t adesc = umma_smem_desc_sw128(a_s);
+        const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          // advancing 16 bf16 (32 bytes) along K inside the swizzle atom: +2 in 16-byte units
+          umma_bf16(tmem_base, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(empty_bar(s));  // smem slot reusable once these MMAs have read it
+        if (kb == p.num_kb - 1) umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+      if (++s == p.stages) { s = 0; ph ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+template <int AMODE, bool B_TMA>
+cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
+                     cudaStream_t st) {
+  static bool attr_set[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto kern = conv_umma_kernel<AMODE, B_TMA>;
+  if (dev < 16 && !attr_set[dev]) {
+    cudaError_t e =
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  const ConvGeom& g = a.g;
+  KP p;
+  p.H = g.H; p.W = g.W; p.C = g.C; p.OH = g.OH; p.OW = g.OW; p.R = g.R; p.S = g.S; p.Sp = g.Sp;
+  p.stride = g.stride; p.pad = g.pad; p.Cout = g.Cout; p.K = g.K; p.M = g.M; p.BN = a.BN;
+  p.stages = a.stages; p.num_kb = g.K / BK; p.tiles_n = g.Cout_pad / a.BN; p.ldo = a.ldo;
+  p.relu = a.relu; p.out_fp32 = a.out_fp32;
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(a.BN)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.x = static_cast<const __nv_bfloat16*>(a.x);
+  p.w = static_cast<const __nv_bfloat16*>(a.w);
+  p.bias = a.bias;
+  p.residual = static_cast<const __nv_bfloat16*>(a.residual);
+  p.out = a.out;
+  const int tiles_m = (g.M + BM - 1) / BM;
+  const size_t smem = conv_umma_smem_bytes(a.BN, a.stages);
+  static const CUtensorMap dummy = {};
+  kern<<<dim3(static_cast<unsigned>(tiles_m * p.tiles_n)), dim3(NTHREADS), smem, st>>>(
+      tmA ? *tmA : dummy, tmB ? *tmB : dummy, p);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+size_t conv_umma_smem_bytes(int BN, int stages) {
+  return static_cast<size_t>(stages) * (A_TILE_BYTES + BN * 128) + 1024;
+}
+
+// Two CTAs per SM when three stages fit in half the shared memory (epilogue of one tile then
+// overlaps the main loop of the other); otherwise one CTA with as many stages as fit.
+int conv_umma_pick_stages(int BN) {
+  const int stage = A_TILE_BYTES + BN * 128;
+  const int half = 112 * 1024;
+  int s;
+  if (3 * stage <= half) s = half / stage;
+  else s = (220 * 1024) / stage;
+  if (s > 6) s = 6;
+  if (s < 3) s = 3;
+  return s;
+}
+
+cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
+                             cudaStream_t st) {
+  const ConvGeom& g = a.g;
+  if (a.BN < 32 || a.BN > 256 || (a.BN & 31) || g.Cout_pad % a.BN || g.K % BK || a.stages < 3 ||
+      a.stages > MAX_STAGES || g.M <= 0)
+    return cudaErrorInvalidValue;
+  if (!a.out_fp32 && ((a.ldo & 7) || (g.Cout & 31))) return cudaErrorInvalidValue;
+  switch (a.amode) {
+    case A_GATHER:
+      if (g.C % 64 || g.K != g.R * g.S * g.C) return cudaErrorInvalidValue;
+      return a.b_tma ? launch_t<A_GATHER, true>(a, nullptr, tmB, st)
+                     : launch_t<A_GATHER, false>(a, nullptr, nullptr, st);
+    case A_SMALLC:
+      if (g.C != 4 || g.K < g.R * g.Sp * 4) return cudaErrorInvalidValue;
+      return a.b_tma ? launch_t<A_SMALLC, true>(a, nullptr, tmB, st)
+                     : launch_t<A_SMALLC, false>(a, nullptr, nullptr, st);
+    case A_IM2COL:
+      if (g.C % 64 || g.K != g.R * g.S * g.C || !tmA || !tmB) return cudaErrorInvalidValue;
+      return launch_t<A_IM2COL, true>(a, tmA, tmB, st);
+    case A_TILED:
+      if (!tmA || !tmB) return cudaErrorInvalidValue;
+      return launch_t<A_TILED, true>(a, tmA, tmB, st);
+  }
+  return cudaErrorInvalidValue;
+}
+
+// ---------------------------------------------------------------------------- tensor maps
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const int*, const int*,
+                                   cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+void* driver_fn(const char* name) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  return fn;
+}
+}  // namespace
+
+int make_tmap_rows(CUtensorMap* tm, const void* a, int rows, int K, int box_rows,
+                   const char** err) {
+  static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
+  if (!fn) { *err = "cuTensorMapEncodeTiled entry point not found"; return -1; }
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(K) * 2};
+  cuuint32_t box[2] = {BK, static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(a), dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { *err = "cuTensorMapEncodeTiled failed"; return static_cast<int>(r); }
+  return 0;
+}
+
+int make_tmap_weights(CUtensorMap* tm, const void* w, int Cout_pad, int K, int BN,
+                      const char** err) {
+  return make_tmap_rows(tm, w, Cout_pad, K, BN, err);
+}
+
+int make_tmap_im2col(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax,
+                     const char** err) {
+  static EncodeIm2colFn fn =
+      reinterpret_cast<EncodeIm2colFn>(driver_fn("cuTensorMapEncodeIm2col"));
+  if (!fn) { *err = "cuTensorMapEncodeIm2col entry point not found"; return -1; }
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(g.C), static_cast<cuuint64_t>(g.W),
+                        static_cast<cuuint64_t>(g.H), static_cast<cuuint64_t>(Nmax)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(g.C) * 2,
+                           static_cast<cuuint64_t>(g.W) * g.C * 2,
+                           static_cast<cuuint64_t>(g.H) * g.W * g.C * 2};
+  // Bounding box of filter-window origins: [-pad, dim + pad - (window - 1)) per spatial axis.
+  int lower[2] = {-g.pad, -g.pad};
+  int upper[2] = {g.pad - (g.S - 1), g.pad - (g.R - 1)};
+  cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(g.stride), static_cast<cuuint32_t>(g.stride), 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides,
+                  lower, upper, /*channelsPerPixel=*/BK, /*pixelsPerColumn=*/BM, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { *err = "cuTensorMapEncodeIm2col failed"; return static_cast<int>(r); }
+  // Drivers up to CUDA 13.1 mis-encode im2col maps over tensors smaller than 128 KiB; the
+  // publicly documented fix-up is to clear bit 21 of the second descriptor word.
+  int drv = 0;
+  cudaDriverGetVersion(&drv);
+  const size_t bytes = static_cast<size_t>(Nmax) * g.H * g.W * g.C * 2;
+  if (drv <= 13010 && bytes < 131072)
+    reinterpret_cast<uint64_t*>(tm)[1] &= ~(1ull << 21);
+  return 0;
+}
+
+}  // namespace b2i

@@ -1,0 +1,497 @@
+// See engine.h.
+#include "engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace b2i {
+
+namespace {
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+inline uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return static_cast<uint16_t>(u >> 16);
+}
+inline float bf16_to_f32(uint16_t h) {
+  uint32_t u = static_cast<uint32_t>(h) << 16;
+  float f;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+
+const HostTensor* find(const std::map<std::string, HostTensor>& t, const std::string& name,
+                       std::string* err) {
+  auto it = t.find(name);
+  if (it == t.end()) {
+    *err = "weight archive is missing tensor '" + name + "'";
+    return nullptr;
+  }
+  return &it->second;
+}
+
+bool shape_is(const HostTensor& h, std::initializer_list<int64_t> want) {
+  return h.shape.size() == want.size() && std::equal(want.begin(), want.end(), h.shape.begin());
+}
+
+std::string shape_str(const HostTensor& h) {
+  std::string s = "[";
+  for (size_t i = 0; i < h.shape.size(); ++i) s += (i ? "," : "") + std::to_string(h.shape[i]);
+  return s + "]";
+}
+
+// conv (no bias) + BN, the ResNet building block
+bool add_conv_bn(const std::map<std::string, HostTensor>& t, const std::string& conv,
+                 const std::string& bn, int Cout, int Cin, int k, int stride, int pad,
+                 NetSpec* net, std::string* err) {
+  const HostTensor* w = find(t, conv + ".weight", err);
+  const HostTensor* g = find(t, bn + ".weight", err);
+  const HostTensor* b = find(t, bn + ".bias", err);
+  const HostTensor* m = find(t, bn + ".running_mean", err);
+  const HostTensor* v = find(t, bn + ".running_var", err);
+  if (!w || !g || !b || !m || !v) return false;
+  if (!shape_is(*w, {Cout, Cin, k, k})) {
+    *err = conv + ".weight has shape " + shape_str(*w) + ", expected [" + std::to_string(Cout) +
+           "," + std::to_string(Cin) + "," + std::to_string(k) + "," + std::to_string(k) + "]";
+    return false;
+  }
+  for (const HostTensor* p : {g, b, m, v})
+    if (!shape_is(*p, {Cout})) { *err = bn + " parameter has shape " + shape_str(*p); return false; }
+  net->convs.emplace_back();
+  build_conv_spec(&net->convs.back(), conv, w->data.data(), nullptr, g->data.data(),
+                  b->data.data(), m->data.data(), v->data.data(), Cout, Cin, k, k, stride, pad);
+  return true;
+}
+
+bool add_conv_bias(const std::map<std::string, HostTensor>& t, const std::string& name, int Cout,
+                   int Cin, int k, int stride, int pad, int chw_c, NetSpec* net,
+                   std::string* err) {
+  const HostTensor* w = find(t, name + ".weight", err);
+  const HostTensor* b = find(t, name + ".bias", err);
+  if (!w || !b) return false;
+  const bool ok = (k == 0) ? shape_is(*w, {Cout, Cin}) : shape_is(*w, {Cout, Cin, k, k});
+  if (!ok || !shape_is(*b, {Cout})) {
+    *err = name + " has unexpected shape " + shape_str(*w) + " / " + shape_str(*b);
+    return false;
+  }
+  net->convs.emplace_back();
+  const int kk = k == 0 ? 1 : k;
+  build_conv_spec(&net->convs.back(), name, w->data.data(), b->data.data(), nullptr, nullptr,
+                  nullptr, nullptr, Cout, Cin, kk, kk, stride, pad, chw_c);
+  return true;
+}
+
+int new_tensor(NetSpec* net, int H, int W, int C) {
+  TensorShape s;
+  s.H = H; s.W = W; s.C = C;
+  net->tensors.push_back(s);
+  return static_cast<int>(net->tensors.size()) - 1;
+}
+
+int conv_out(int in, int k, int stride, int pad) { return (in + 2 * pad - k) / stride + 1; }
+
+// Appends a conv op reading tensor `in`; returns the output tensor id.
+int push_conv(NetSpec* net, int conv_idx, int in, int res, bool relu) {
+  const ConvSpec& c = net->convs[conv_idx];
+  const TensorShape ti = net->tensors[in];
+  const int OH = conv_out(ti.H, c.R, c.stride, c.pad), OW = conv_out(ti.W, c.S, c.stride, c.pad);
+  OpSpec op;
+  op.kind = OpSpec::CONV;
+  op.in = in; op.res = res; op.conv = conv_idx; op.relu = relu;
+  op.out = new_tensor(net, OH, OW, c.Cout);
+  net->ops.push_back(op);
+  net->flops_per_image += 2.0 * OH * OW * c.Cout * c.Cin * c.R * c.S;
+  return op.out;
+}
+
+int push_fc(NetSpec* net, int conv_idx, int in, bool relu, bool logits) {
+  const ConvSpec& c = net->convs[conv_idx];
+  OpSpec op;
+  op.kind = OpSpec::CONV;
+  op.in = in; op.conv = conv_idx; op.relu = relu; op.fc = true; op.logits = logits;
+  op.out = new_tensor(net, 1, 1, c.Cout);
+  if (logits) net->logits_tensor = op.out;
+  net->ops.push_back(op);
+  net->flops_per_image += 2.0 * c.Cout * c.Cin;
+  return op.out;
+}
+
+int push_pool(NetSpec* net, OpSpec::Kind kind, int in, int k, int stride, int pad, int OH, int OW) {
+  OpSpec op;
+  op.kind = kind;
+  op.in = in; op.k = k; op.stride = stride; op.pad = pad;
+  op.out = new_tensor(net, OH, OW, net->tensors[in].C);
+  net->ops.push_back(op);
+  return op.out;
+}
+
+}  // namespace
+
+void build_conv_spec(ConvSpec* cs, const std::string& name, const float* w, const float* bias,
+                     const float* g, const float* b, const float* m, const float* v, int Cout,
+                     int Cin, int R, int S, int stride, int pad, int chw_c) {
+  cs->name = name;
+  cs->Cin = Cin; cs->Cout = Cout; cs->R = R; cs->S = S; cs->Sp = S; cs->stride = stride;
+  cs->pad = pad;
+  cs->smallc = Cin <= 4;  // first layers (RGB): one 8-byte pixel per filter tap
+  cs->Cin_pad = cs->smallc ? 4 : round_up(Cin, 64);
+  cs->Cout_pad = round_up(Cout, 64);
+  cs->K = round_up(R * cs->Sp * cs->Cin_pad, 64);
+  cs->w.assign(static_cast<size_t>(cs->Cout_pad) * cs->K, 0.f);
+  cs->bias.assign(cs->Cout_pad, 0.f);
+  const int hw = chw_c > 0 ? Cin / chw_c : 1;
+  for (int co = 0; co < Cout; ++co) {
+    float scale = 1.f, shift = bias ? bias[co] : 0.f;
+    if (g) {
+      // eval-mode batch_norm: y = (x - mean) / sqrt(var + eps) * gamma + beta, eps = 1e-5
+      const double inv = 1.0 / std::sqrt(static_cast<double>(v[co]) + 1e-5);
+      scale = static_cast<float>(g[co] * inv);
+      shift = static_cast<float>(b[co] - m[co] * g[co] * inv + (bias ? bias[co] * g[co] * inv : 0.0));
+    }
+    cs->bias[co] = shift;
+    float* dst = cs->w.data() + static_cast<size_t>(co) * cs->K;
+    for (int c = 0; c < Cin; ++c)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s) {
+          const float val = w[((static_cast<size_t>(co) * Cin + c) * R + r) * S + s] * scale;
+          int kc = c;
+          if (chw_c > 0) kc = (c % hw) * chw_c + (c / hw);  // (c', hw') -> hw'*C + c'
+          dst[(r * cs->Sp + s) * cs->Cin_pad + kc] = val;
+        }
+  }
+}
+
+bool build_resnet18(const std::map<std::string, HostTensor>& t, NetSpec* net, std::string* err) {
+  net->model = "resnet18";
+  const int in0 = new_tensor(net, 224, 224, 4);
+  {
+    OpSpec op;
+    op.kind = OpSpec::NORMALIZE;
+    op.out = in0;
+    net->ops.push_back(op);
+  }
+  if (!add_conv_bn(t, "conv1", "bn1", 64, 3, 7, 2, 3, net, err)) return false;
+  int cur = push_conv(net, 0, in0, -1, true);
+  cur = push_pool(net, OpSpec::MAXPOOL, cur, 3, 2, 1, 56, 56);
+  int cin = 64;
+  const int widths[4] = {64, 128, 256, 512};
+  for (int L = 0; L < 4; ++L) {
+    const int cout = widths[L];
+    for (int B = 0; B < 2; ++B) {
+      const int stride = (L > 0 && B == 0) ? 2 : 1;
+      const std::string p = "layer" + std::to_string(L + 1) + "." + std::to_string(B);
+      int identity = cur;
+      if (stride != 1 || cin != cout) {
+        if (!add_conv_bn(t, p + ".downsample.0", p + ".downsample.1", cout, cin, 1, stride, 0, net, err))
+          return false;
+        identity = push_conv(net, static_cast<int>(net->convs.size()) - 1, cur, -1, false);
+      }
+      if (!add_conv_bn(t, p + ".conv1", p + ".bn1", cout, cin, 3, stride, 1, net, err)) return false;
+      const int mid = push_conv(net, static_cast<int>(net->convs.size()) - 1, cur, -1, true);
+      if (!add_conv_bn(t, p + ".conv2", p + ".bn2", cout, cout, 3, 1, 1, net, err)) return false;
+      cur = push_conv(net, static_cast<int>(net->convs.size()) - 1, mid, identity, true);
+      cin = cout;
+    }
+  }
+  cur = push_pool(net, OpSpec::AVGPOOL, cur, 0, 0, 0, 1, 1);
+  if (!add_conv_bias(t, "fc", 1000, 512, 0, 1, 0, 0, net, err)) return false;
+  push_fc(net, static_cast<int>(net->convs.size()) - 1, cur, false, true);
+  return true;
+}
+
+bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, NetSpec* net,
+                   std::string* err) {
+  net->model = "alexnet";
+  const int in0 = new_tensor(net, 224, 224, 4);
+  {
+    OpSpec op;
+    op.kind = OpSpec::NORMALIZE;
+    op.out = in0;
+    net->ops.push_back(op);
+  }
+  auto last = [&]() { return static_cast<int>(net->convs.size()) - 1; };
+  auto pool = [&](int in) {
+    const TensorShape s = net->tensors[in];
+    return push_pool(net, OpSpec::MAXPOOL, in, 3, 2, 0, conv_out(s.H, 3, 2, 0), conv_out(s.W, 3, 2, 0));
+  };
+  if (!add_conv_bias(t, "features.0", 64, 3, 11, 4, 2, 0, net, err)) return false;
+  int cur = pool(push_conv(net, last(), in0, -1, true));
+  // features.3: tch 0.4.1 builds it as (k5, pad 1, stride 2); torchvision as (k5, pad 2, stride 1).
+  // Same weight shape either way.
+  const int p3 = geometry == ALEX_TORCHVISION ? 2 : 1, s3 = geometry == ALEX_TORCHVISION ? 1 : 2;
+  if (!add_conv_bias(t, "features.3", 192, 64, 5, s3, p3, 0, net, err)) return false;
+  cur = pool(push_conv(net, last(), cur, -1, true));
+  if (!add_conv_bias(t, "features.6", 384, 192, 3, 1, 1, 0, net, err)) return false;
+  cur = push_conv(net, last(), cur, -1, true);
+  if (!add_conv_bias(t, "features.8", 256, 384, 3, 1, 1, 0, net, err)) return false;
+  cur = push_conv(net, last(), cur, -1, true);
+  if (!add_conv_bias(t, "features.10", 256, 256, 3, 1, 1, 0, net, err)) return false;
+  cur = pool(push_conv(net, last(), cur, -1, true));
+  const TensorShape s = net->tensors[cur];
+  if (s.H != 6 || s.W != 6) cur = push_pool(net, OpSpec::AVGPOOL, cur, 0, 0, 0, 6, 6);
+  // classifier.1 consumes a (C,H,W) flatten in the reference; activations here are (H,W,C).
+  if (!add_conv_bias(t, "classifier.1", 4096, 9216, 0, 1, 0, 256, net, err)) return false;
+  cur = push_fc(net, last(), cur, true, false);
+  if (!add_conv_bias(t, "classifier.4", 4096, 4096, 0, 1, 0, 0, net, err)) return false;
+  cur = push_fc(net, last(), cur, true, false);
+  if (!add_conv_bias(t, "classifier.6", 1000, 4096, 0, 1, 0, 0, net, err)) return false;
+  push_fc(net, last(), cur, false, true);
+  return true;
+}
+
+// ------------------------------------------------------------------------------- DeviceModel
+#define B2I_CUDA(call)                                                                    \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      *err = std::string(#call) + ": " + cudaGetErrorString(e_);                          \
+      return false;                                                                       \
+    }                                                                                     \
+  } while (0)
+
+DeviceModel::~DeviceModel() {
+  if (device_ < 0) return;
+  cudaSetDevice(device_);
+  for (void* p : bufs_) cudaFree(p);
+  for (void* p : owned_) cudaFree(p);
+}
+
+bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, std::string* err) {
+  device_ = device;
+  cfg_ = cfg;
+  classes_ = net.classes;
+  logits_tensor_ = net.logits_tensor;
+  if (cfg_.max_batch < 1) { *err = "max_batch must be >= 1"; return false; }
+  mb_ = cfg_.micro_batch > 0 ? std::min(cfg_.micro_batch, cfg_.max_batch) : cfg_.max_batch;
+  esize_ = cfg_.precision == PREC_FP32 ? 4 : 2;
+  B2I_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  B2I_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    *err = "device " + std::to_string(device) + " is sm_" + std::to_string(prop.major) +
+           std::to_string(prop.minor) + "; this library carries sm_100a kernels only";
+    return false;
+  }
+  tshape_ = net.tensors;
+
+  // ---- activation buffers: greedy reuse by liveness (last reader), sizes per micro-batch
+  const int T = static_cast<int>(tshape_.size());
+  std::vector<int> last_use(T, -1);
+  for (size_t i = 0; i < net.ops.size(); ++i) {
+    const OpSpec& o = net.ops[i];
+    if (o.in >= 0) last_use[o.in] = static_cast<int>(i);
+    if (o.res >= 0) last_use[o.res] = static_cast<int>(i);
+  }
+  last_use[logits_tensor_] = 1 << 30;
+  tensor_buf_.assign(T, -1);
+  std::vector<int> free_list;
+  auto tensor_bytes = [&](int id) {
+    const size_t es = (id == logits_tensor_) ? 4 : esize_;
+    return tshape_[id].elems() * static_cast<size_t>(mb_) * es;
+  };
+  for (size_t i = 0; i < net.ops.size(); ++i) {
+    const OpSpec& o = net.ops[i];
+    const size_t need = tensor_bytes(o.out);
+    int pick = -1;
+    if (!cfg_.keep_tensors && o.out != logits_tensor_) {
+      for (size_t f = 0; f < free_list.size(); ++f) {
+        const int b = free_list[f];
+        if (buf_bytes_[b] >= need && (pick < 0 || buf_bytes_[b] < buf_bytes_[pick])) pick = b;
+      }
+      if (pick >= 0) free_list.erase(std::find(free_list.begin(), free_list.end(), pick));
+    }
+    if (pick < 0) {
+      buf_bytes_.push_back(need);
+      pick = static_cast<int>(buf_bytes_.size()) - 1;
+    }
+    tensor_buf_[o.out] = pick;
+    // inputs whose last reader is this op become reusable for LATER ops (never for this op's output)
+    for (int id : {o.in, o.res})
+      if (id >= 0 && last_use[id] == static_cast<int>(i) && id != logits_tensor_) {
+        const int b = tensor_buf_[id];
+        if (std::find(free_list.begin(), free_list.end(), b) == free_list.end()) free_list.push_back(b);
+      }
+  }
+  bufs_.assign(buf_bytes_.size(), nullptr);
+  for (size_t b = 0; b < buf_bytes_.size(); ++b) {
+    B2I_CUDA(cudaMalloc(&bufs_[b], buf_bytes_[b]));
+    B2I_CUDA(cudaMemset(bufs_[b], 0, buf_bytes_[b]));
+    act_bytes_ += buf_bytes_[b];
+  }
+
+  // ---- weights + per-op launch plan
+  for (const OpSpec& o : net.ops) {
+    DevOp d;
+    d.spec = o;
+    if (o.kind == OpSpec::CONV) {
+      const ConvSpec& c = net.convs[o.conv];
+      const TensorShape ti = tshape_[o.in], to = tshape_[o.out];
+      ConvGeom& g = d.g;
+      if (o.fc) {
+        g.H = g.W = 1; g.C = c.K; g.OH = g.OW = 1; g.R = g.S = g.Sp = 1; g.stride = 1; g.pad = 0;
+        if (static_cast<int>(ti.elems()) != c.K) {
+          *err = c.name + ": FC input has " + std::to_string(ti.elems()) + " features, weights expect " +
+                 std::to_string(c.K);
+          return false;
+        }
+      } else {
+        g.H = ti.H; g.W = ti.W; g.C = c.Cin_pad; g.OH = to.H; g.OW = to.W;
+        g.R = c.R; g.S = c.S; g.Sp = c.Sp; g.stride = c.stride; g.pad = c.pad;
+        if (ti.C != c.Cin_pad) {
+          *err = c.name + ": input tensor has " + std::to_string(ti.C) + " channels, layer expects " +
+                 std::to_string(c.Cin_pad);
+          return false;
+        }
+      }
+      g.N = mb_; g.Cout = c.Cout; g.Cout_pad = c.Cout_pad; g.K = c.K; g.M = 0;
+      // tile-N: largest multiple of 32 <= bn_max dividing Cout_pad
+      int bn = std::min(cfg_.bn_max, 256) / 32 * 32;
+      while (bn > 32 && c.Cout_pad % bn) bn -= 32;
+      d.BN = bn;
+      d.stages = conv_umma_pick_stages(bn);
+      d.b_tma = cfg_.b_tma;
+      if (o.fc) d.amode = A_TILED;
+      else if (c.smallc) d.amode = A_SMALLC;
+      else d.amode = (cfg_.conv_amode == A_GATHER) ? A_GATHER : A_IM2COL;
+      if (d.amode == A_IM2COL || d.amode == A_TILED) d.b_tma = 1;
+
+      const size_t wn = c.w.size();
+      if (cfg_.precision == PREC_FP32) {
+        B2I_CUDA(cudaMalloc(&d.w, wn * 4));
+        B2I_CUDA(cudaMemcpy(d.w, c.w.data(), wn * 4, cudaMemcpyHostToDevice));
+        weight_bytes_ += wn * 4;
+      } else {
+        std::vector<uint16_t> wb(wn);
+        for (size_t i = 0; i < wn; ++i) wb[i] = f32_to_bf16_rne(c.w[i]);
+        B2I_CUDA(cudaMalloc(&d.w, wn * 2));
+        B2I_CUDA(cudaMemcpy(d.w, wb.data(), wn * 2, cudaMemcpyHostToDevice));
+        weight_bytes_ += wn * 2;
+      }
+      owned_.push_back(d.w);
+      void* bp = nullptr;
+      B2I_CUDA(cudaMalloc(&bp, c.bias.size() * 4));
+      B2I_CUDA(cudaMemcpy(bp, c.bias.data(), c.bias.size() * 4, cudaMemcpyHostToDevice));
+      owned_.push_back(bp);
+      d.bias = static_cast<float*>(bp);
+
+      if (cfg_.precision == PREC_BF16) {
+        const char* terr = "";
+        if (d.b_tma) {
+          if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
+          d.has_tmB = true;
+        }
+        void* xin = bufs_[tensor_buf_[o.in]];
+        if (d.amode == A_IM2COL) {
+          if (make_tmap_im2col(&d.tmA, xin, g, mb_, &terr)) { *err = c.name + ": " + terr; return false; }
+          d.has_tmA = true;
+        } else if (d.amode == A_TILED) {
+          if (make_tmap_rows(&d.tmA, xin, mb_, c.K, 128, &terr)) { *err = c.name + ": " + terr; return false; }
+          d.has_tmA = true;
+        }
+      }
+    }
+    ops_.push_back(d);
+  }
+  return true;
+}
+
+bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_idx, float* d_prob,
+                                 float* d_logits, cudaStream_t st, std::string* err) {
+  const int dt = cfg_.precision == PREC_FP32 ? DT_F32 : DT_BF16;
+  auto buf = [&](int tensor) { return tensor >= 0 ? bufs_[tensor_buf_[tensor]] : nullptr; };
+  for (DevOp& d : ops_) {
+    const OpSpec& o = d.spec;
+    switch (o.kind) {
+      case OpSpec::NORMALIZE:
+        B2I_CUDA(launch_normalize_u8(d_u8, buf(o.out), dt, static_cast<long long>(nb) * 224 * 224, st));
+        break;
+      case OpSpec::MAXPOOL: {
+        const TensorShape ti = tshape_[o.in], to = tshape_[o.out];
+        B2I_CUDA(launch_maxpool(buf(o.in), buf(o.out), dt, nb, ti.H, ti.W, ti.C, o.k, o.stride,
+                                o.pad, to.H, to.W, st));
+        break;
+      }
+      case OpSpec::AVGPOOL: {
+        const TensorShape ti = tshape_[o.in], to = tshape_[o.out];
+        B2I_CUDA(launch_adaptive_avgpool(buf(o.in), buf(o.out), dt, nb, ti.H, ti.W, ti.C, to.H,
+                                         to.W, st));
+        break;
+      }
+      case OpSpec::CONV: {
+        ConvArgs a;
+        a.g = d.g;
+        a.g.N = nb;
+        a.g.M = nb * d.g.OH * d.g.OW;
+        a.x = buf(o.in);
+        a.w = d.w;
+        a.bias = d.bias;
+        a.residual = buf(o.res);
+        a.out = buf(o.out);
+        a.ldo = o.logits ? classes_ : d.g.Cout;
+        a.relu = o.relu ? 1 : 0;
+        a.out_fp32 = o.logits ? 1 : 0;
+        a.BN = d.BN;
+        a.stages = d.stages;
+        a.amode = d.amode;
+        a.b_tma = d.b_tma;
+        if (cfg_.precision == PREC_FP32) {
+          B2I_CUDA(launch_conv_fp32(a, st));
+        } else {
+          B2I_CUDA(launch_conv_umma(a, d.has_tmA ? &d.tmA : nullptr, d.has_tmB ? &d.tmB : nullptr, st));
+        }
+        break;
+      }
+    }
+  }
+  const float* lg = static_cast<const float*>(buf(logits_tensor_));
+  B2I_CUDA(launch_softmax_topk(lg, nb, classes_, classes_, k, d_idx, d_prob, st));
+  if (d_logits)
+    B2I_CUDA(cudaMemcpyAsync(d_logits, lg, static_cast<size_t>(nb) * classes_ * 4,
+                             cudaMemcpyDeviceToDevice, st));
+  return true;
+}
+
+bool DeviceModel::forward(const uint8_t* d_u8, int n, int k, int32_t* d_idx, float* d_prob,
+                          float* d_logits, cudaStream_t st, std::string* err) {
+  if (n < 0 || n > cfg_.max_batch) {
+    *err = "batch " + std::to_string(n) + " exceeds the model's max_batch " + std::to_string(cfg_.max_batch);
+    return false;
+  }
+  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return false; }
+  B2I_CUDA(cudaSetDevice(device_));
+  for (int off = 0; off < n; off += mb_) {
+    const int nb = std::min(mb_, n - off);
+    if (!run_microbatch(d_u8 + static_cast<size_t>(off) * 224 * 224 * 3, nb, k,
+                        d_idx + static_cast<size_t>(off) * k, d_prob + static_cast<size_t>(off) * k,
+                        d_logits ? d_logits + static_cast<size_t>(off) * classes_ : nullptr, st, err))
+      return false;
+  }
+  return true;
+}
+
+bool DeviceModel::read_tensor(int id, int n, std::vector<float>* out, std::string* err) {
+  if (id < 0 || id >= static_cast<int>(tshape_.size()) || n < 1 || n > mb_) {
+    *err = "read_tensor: bad tensor id or batch";
+    return false;
+  }
+  B2I_CUDA(cudaSetDevice(device_));
+  B2I_CUDA(cudaDeviceSynchronize());
+  const size_t ne = tshape_[id].elems() * n;
+  out->resize(ne);
+  const void* src = bufs_[tensor_buf_[id]];
+  if (id == logits_tensor_ || cfg_.precision == PREC_FP32) {
+    B2I_CUDA(cudaMemcpy(out->data(), src, ne * 4, cudaMemcpyDeviceToHost));
+  } else {
+    std::vector<uint16_t> tmp(ne);
+    B2I_CUDA(cudaMemcpy(tmp.data(), src, ne * 2, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < ne; ++i) (*out)[i] = bf16_to_f32(tmp[i]);
+  }
+  return true;
+}
+
+}  // namespace b2i

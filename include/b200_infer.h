@@ -1,0 +1,155 @@
+/* b200_infer.h — C ABI of the B200-native inference path.
+ *
+ * Drop-in boundary for the five tch calls the reference makes under `Member::predict`
+ * (reference src/services.rs:492-494) and for the model construction + weight load in
+ * `MemberState::shared` (reference src/services.rs:513-524; dead twin src/model_utils.rs:24-49).
+ * Plain pointers and sizes only; every buffer is caller-owned; no exceptions cross this line.
+ * All entry points return 0 on success and a negative B2I_E* code on failure, with a
+ * thread-local message available from b2i_last_error().
+ *
+ * There is NO CPU fallback: every compute entry point needs an sm_100 GPU and fails with
+ * B2I_ENODEV / B2I_ECUDA otherwise.
+ */
+#ifndef B200_INFER_H_
+#define B200_INFER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2I_OK 0
+#define B2I_EINVAL (-1)  /* bad argument (unknown model name, k out of range, null pointer ...) */
+#define B2I_EIO (-2)     /* weight archive missing / malformed (the reference panics here: services.rs:516,522) */
+#define B2I_ECUDA (-3)   /* CUDA runtime / driver error */
+#define B2I_ENODEV (-4)  /* no usable sm_100 device */
+#define B2I_ENOMEM (-5)
+
+#define B2I_PREC_BF16 0 /* tcgen05 bf16 in, fp32 accumulate; logits within 2e-2 of the fp32 reference */
+#define B2I_PREC_FP32 1 /* FFMA fp32; logits within 1e-4 */
+
+#define B2I_ALEXNET_TCH 0         /* features.3 = k5 pad1 stride2, as tch 0.4.1 builds it */
+#define B2I_ALEXNET_TORCHVISION 1 /* features.3 = k5 pad2 stride1 */
+
+#define B2I_IMAGE_BYTES (224 * 224 * 3)
+#define B2I_CLASSES 1000
+
+typedef struct b2i_ctx b2i_ctx;     /* a set of GPUs; replaces tch::Device::Cpu (services.rs:514,520) */
+typedef struct b2i_model b2i_model; /* replaces Mutex<Box<dyn ModuleT>> (services.rs:455-456) */
+
+typedef struct b2i_model_config {
+  int precision;        /* B2I_PREC_* */
+  int max_batch;        /* largest n one predict call may pass PER GPU (buffers are sized for it) */
+  int micro_batch;      /* images per kernel sequence, 0 = max_batch */
+  int alexnet_geometry; /* B2I_ALEXNET_* */
+  int conv_mode;        /* -1 auto; 0 cp.async gather; 1 TMA im2col (bf16 path, C % 64 == 0 layers) */
+  int weights_tma;      /* 1: weight tiles through TMA (default), 0: cp.async (gather modes only) */
+  int tile_n_max;       /* largest output-channel tile, multiple of 32 in [32,256]; 0 = default */
+  int keep_tensors;     /* 1: no activation-buffer reuse, so b2i_model_read_tensor sees every layer */
+} b2i_model_config;
+
+/* Thread-local description of the last failure on the calling thread. Never NULL. */
+const char* b2i_last_error(void);
+
+/* Number of CUDA devices visible (0 when there is no driver). */
+int b2i_device_count(void);
+
+/* Context over `n_devices` GPU ordinals. Replaces `VarStore::new(Device::Cpu)` (services.rs:514). */
+int b2i_init(const int* device_ids, int n_devices, b2i_ctx** out);
+void b2i_shutdown(b2i_ctx* ctx);
+
+/* Fills cfg with the defaults (bf16, max_batch 256, tch AlexNet geometry, auto conv mode). */
+void b2i_default_config(b2i_model_config* cfg);
+
+/* Parse a `.ot` archive and report its tensors without touching a GPU (CPU-only; used by tests
+ * and by callers that want to validate a file first). names_out receives '\n'-separated
+ * "name:d0xd1x..." lines, truncated to cap bytes. Returns the tensor count or a negative code. */
+int b2i_ot_inspect(const char* path, char* names_out, size_t cap);
+/* Copy one tensor of the archive as fp32 (CPU-only). Returns numel or a negative code. */
+long long b2i_ot_read_tensor(const char* path, const char* name, float* out, long long cap_elems);
+
+/* model_name is "resnet18" or "alexnet" (anything else -> B2I_EINVAL, the reference returns None:
+ * services.rs:477-481). Builds the network, folds BatchNorm, uploads weights to every GPU of ctx.
+ * Replaces resnet::resnet18 / alexnet::alexnet + vs.load (services.rs:513-524). */
+int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
+                   const b2i_model_config* cfg, b2i_model** out);
+void b2i_model_free(b2i_model* m);
+
+/* Static facts: algorithmic FLOPs per image, kernel launches per micro-batch, bytes resident. */
+double b2i_model_flops_per_image(const b2i_model* m);
+int b2i_model_launches_per_microbatch(const b2i_model* m);
+int b2i_model_num_devices(const b2i_model* m);
+long long b2i_model_weight_bytes(const b2i_model* m);
+long long b2i_model_activation_bytes(const b2i_model* m);
+
+/* The batched form of the reference's per-image  forward_t(..) .softmax(-1) ; imagenet::top(..,k)
+ * (services.rs:493-494), on HOST buffers:
+ *   images : u8 [n][224][224][3] (HWC, RGB), already resized + centre-cropped
+ *   idx    : int32 [n][k]   class indices, highest probability first (synset_words.txt order)
+ *   prob   : float [n][k]   softmax probabilities
+ *   logits : float [n][1000] or NULL
+ * The batch is split contiguously over the model's GPUs (image i of GPU g's slice keeps its global
+ * position), each GPU stages through pinned double buffers on its own streams, and only idx/prob
+ * (and logits when asked) come back; there is no inter-GPU traffic. n may be anything from 0 to
+ * num_devices * max_batch. Blocking; thread-safe (calls on one model are serialised, different
+ * models run concurrently). */
+int b2i_predict_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
+                   float* logits);
+
+/* Same, restricted to the GPUs [first_dev, first_dev + n_dev) of the model's context: the
+ * dual-job fair share (reference src/services.rs:199-211) hands each job half of the devices. */
+int b2i_predict_u8_on(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
+                      int32_t* idx, float* prob, float* logits);
+
+/* Device-resident form for one GPU of the model (dev = index inside the context): all pointers are
+ * device pointers on that GPU, work is enqueued on `cuda_stream` (a cudaStream_t, may be NULL for
+ * the default stream) and the call returns without synchronising. Used by the benchmark to time
+ * the kernel sequence with inputs already in HBM. */
+int b2i_forward_device(b2i_model* m, int dev, const void* d_images_u8, int n, int k, void* d_idx,
+                       void* d_prob, void* d_logits, void* cuda_stream);
+
+/* Resize + centre-crop of one decoded image, the first half of
+ * imagenet::load_image_and_resize(path, 224, 224) (services.rs:492):
+ * u8 [h][w][3] -> u8 [224][224][3] on the GPU `dev` of ctx. */
+int b2i_resize_crop_u8(b2i_ctx* ctx, int dev, const uint8_t* image, int h, int w, uint8_t* out224);
+
+/* Pinned host memory for the staging-free fast path of b2i_predict_u8. */
+void* b2i_host_alloc(size_t bytes);
+void b2i_host_free(void* p);
+
+/* Copy activation tensor `tensor_id` (0 = normalised input, then one per layer in execution order)
+ * of the last predict on GPU `dev` as fp32 NHWC. Needs keep_tensors = 1. Returns numel or < 0. */
+long long b2i_model_read_tensor(b2i_model* m, int dev, int tensor_id, int n, float* out,
+                                long long cap_elems);
+int b2i_model_num_tensors(const b2i_model* m);
+int b2i_model_tensor_shape(const b2i_model* m, int tensor_id, int* h, int* w, int* c);
+
+/* ---- single-kernel entry points on HOST buffers (parity tests drive each kernel through these;
+ * fp32 NHWC in and out, converted to the kernel's dtype inside). ---------------------------- */
+
+/* conv2d (+ optional eval-BatchNorm fold, bias, residual, ReLU). x: [N][H][W][C]; w: OIHW
+ * [Cout][C][R][S]; bn: NULL or [4][Cout] = gamma, beta, running_mean, running_var; residual/out:
+ * [N][OH][OW][Cout]. conv_mode: 0 gather, 1 TMA im2col (bf16, C % 64 == 0); C < 8 always uses the
+ * small-channel gather. tile_n 0 = default. */
+int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weights_tma, int tile_n,
+                  const float* x, int N, int H, int W, int C, const float* w, const float* bias,
+                  const float* bn, int Cout, int R, int S, int stride, int pad,
+                  const float* residual, int relu, float* out);
+/* linear (+bias, ReLU): x [M][K], w [Cout][K], out [M][Cout]. */
+int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float* x, int M, int K,
+                  const float* w, const float* bias, int Cout, int relu, float* out);
+int b2i_op_maxpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, int H, int W, int C,
+                   int k, int stride, int pad, float* out);
+int b2i_op_adaptive_avgpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, int H,
+                            int W, int C, int OH, int OW, float* out);
+int b2i_op_normalize(b2i_ctx* ctx, int dev, int precision, const uint8_t* images, int n,
+                     float* out_nhwc4);
+int b2i_op_softmax_topk(b2i_ctx* ctx, int dev, const float* logits, int rows, int classes, int k,
+                        int32_t* idx, float* prob);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_INFER_H_ */
