@@ -457,6 +457,28 @@ int b2i_resize_crop_u8(b2i_ctx* ctx, int dev, const uint8_t* image, int h, int w
   return B2I_OK;
 }
 
+int b2i_resize_plan(int in_size, int out_size, int crop, int* first, int* count, int* idx,
+                    float* coef, int cap) {
+  if (in_size < 1 || out_size < 224 || crop < 0 || crop + 224 > out_size || !first || !count || !idx || !coef)
+    return fail(B2I_EINVAL, "b2i_resize_plan: bad argument");
+  AxisPlan p;
+  plan_axis(in_size, out_size, crop, &p);
+  if (static_cast<int>(p.idx.size()) > cap) return fail(B2I_EINVAL, "b2i_resize_plan: tap buffer too small");
+  std::memcpy(first, p.first.data(), 224 * 4);
+  std::memcpy(count, p.count.data(), 224 * 4);
+  std::memcpy(idx, p.idx.data(), p.idx.size() * 4);
+  std::memcpy(coef, p.coef.data(), p.coef.size() * 4);
+  return static_cast<int>(p.idx.size());
+}
+
+void b2i_resize_target(int h, int w, int* rw, int* rh, int* crop_x, int* crop_y) {
+  const ResizeGeom g = resize_target(h, w);
+  if (rw) *rw = g.rw;
+  if (rh) *rh = g.rh;
+  if (crop_x) *crop_x = g.crop_x;
+  if (crop_y) *crop_y = g.crop_y;
+}
+
 // ------------------------------------------------------------------ single-kernel entry points
 static int ctx_dev(b2i_ctx* ctx, int dev) {
   if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devices.size())) return fail(B2I_EINVAL, "bad context/device");

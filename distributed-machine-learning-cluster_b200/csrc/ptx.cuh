@@ -38,8 +38,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Bounded spin: a pipeline bug shows up as a trapped kernel (CUDA error) instead of a hung GPU.
+// try_wait itself suspends for a hardware-chosen time slice, so the bound is seconds, not cycles.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
+  for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
+    if (spins > (1u << 24)) __trap();
   }
 }
 

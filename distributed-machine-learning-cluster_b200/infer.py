@@ -1,0 +1,249 @@
+"""Python face of the C ABI: contexts, models and the single-kernel entry points, on numpy arrays.
+Everything here forwards to libb200infer.so; nothing is computed in Python."""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from ._lib import (ALEXNET_TCH, ALEXNET_TORCHVISION, CLASSES, IMAGE_BYTES, PREC_BF16, PREC_FP32, B2IError,
+                   ModelConfig, check)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+def device_count():
+    return _lib.lib().b2i_device_count()
+
+
+class Context:
+    """A set of GPUs (replaces `tch::Device::Cpu`, reference src/services.rs:514,520)."""
+
+    def __init__(self, devices=(0,)):
+        devices = list(devices)
+        arr = (ctypes.c_int * len(devices))(*devices)
+        h = ctypes.c_void_p()
+        check(_lib.lib().b2i_init(arr, len(devices), ctypes.byref(h)))
+        self._h = h
+        self.devices = devices
+
+    def close(self):
+        if self._h:
+            _lib.lib().b2i_shutdown(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- single-kernel entry points (parity tests) -------------------------------------------
+    def conv2d(self, x, w, bias=None, bn=None, stride=1, pad=0, residual=None, relu=False, precision=PREC_BF16,
+               conv_mode=0, weights_tma=1, tile_n=0, dev=0):
+        """x NHWC fp32, w OIHW fp32, bn = (gamma, beta, mean, var) or None -> NHWC fp32."""
+        x, w = _f32(x), _f32(w)
+        N, H, W, C = x.shape
+        Cout, Cin, R, S = w.shape
+        assert Cin == C
+        OH, OW = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+        out = np.empty((N, OH, OW, Cout), np.float32)
+        b = _f32(bias) if bias is not None else None
+        bnp = _f32(np.stack(bn)) if bn is not None else None
+        r = _f32(residual) if residual is not None else None
+        check(_lib.lib().b2i_op_conv2d(self._h, dev, precision, conv_mode, weights_tma, tile_n, _ptr(x), N, H, W, C,
+                                       _ptr(w), _ptr(b), _ptr(bnp), Cout, R, S, stride, pad, _ptr(r), int(relu),
+                                       _ptr(out)))
+        return out
+
+    def linear(self, x, w, bias=None, relu=False, precision=PREC_BF16, tile_n=0, dev=0):
+        x, w = _f32(x), _f32(w)
+        M, K = x.shape
+        Cout = w.shape[0]
+        out = np.empty((M, Cout), np.float32)
+        b = _f32(bias) if bias is not None else None
+        check(_lib.lib().b2i_op_linear(self._h, dev, precision, tile_n, _ptr(x), M, K, _ptr(w), _ptr(b), Cout,
+                                       int(relu), _ptr(out)))
+        return out
+
+    def maxpool(self, x, k, stride, pad, precision=PREC_BF16, dev=0):
+        x = _f32(x)
+        N, H, W, C = x.shape
+        OH, OW = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+        out = np.empty((N, OH, OW, C), np.float32)
+        check(_lib.lib().b2i_op_maxpool(self._h, dev, precision, _ptr(x), N, H, W, C, k, stride, pad, _ptr(out)))
+        return out
+
+    def adaptive_avgpool(self, x, oh, ow, precision=PREC_BF16, dev=0):
+        x = _f32(x)
+        N, H, W, C = x.shape
+        out = np.empty((N, oh, ow, C), np.float32)
+        check(_lib.lib().b2i_op_adaptive_avgpool(self._h, dev, precision, _ptr(x), N, H, W, C, oh, ow, _ptr(out)))
+        return out
+
+    def normalize(self, images_u8, precision=PREC_BF16, dev=0):
+        img = np.ascontiguousarray(images_u8, dtype=np.uint8)
+        n = img.shape[0]
+        assert img.shape[1:] == (224, 224, 3)
+        out = np.empty((n, 224, 224, 4), np.float32)
+        check(_lib.lib().b2i_op_normalize(self._h, dev, precision, _ptr(img), n, _ptr(out)))
+        return out
+
+    def softmax_topk(self, logits, k, dev=0):
+        lg = _f32(logits)
+        rows, classes = lg.shape
+        idx = np.empty((rows, k), np.int32)
+        prob = np.empty((rows, k), np.float32)
+        check(_lib.lib().b2i_op_softmax_topk(self._h, dev, _ptr(lg), rows, classes, k, _ptr(idx), _ptr(prob)))
+        return idx, prob
+
+    def resize_crop(self, image_u8, dev=0):
+        """u8 [H,W,3] -> u8 [224,224,3] (tch load_image_and_resize minus decode and normalise)."""
+        img = np.ascontiguousarray(image_u8, dtype=np.uint8)
+        h, w, c = img.shape
+        assert c == 3
+        out = np.empty((224, 224, 3), np.uint8)
+        check(_lib.lib().b2i_resize_crop_u8(self._h, dev, _ptr(img), h, w, _ptr(out)))
+        return out
+
+
+def resize_target(h, w):
+    rw, rh, cx, cy = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _lib.lib().b2i_resize_target(h, w, ctypes.byref(rw), ctypes.byref(rh), ctypes.byref(cx), ctypes.byref(cy))
+    return rw.value, rh.value, cx.value, cy.value
+
+
+def resize_plan(in_size, out_size, crop):
+    cap = 224 * (8 + 4 * (in_size // max(out_size, 1) + 2) + 8)
+    first = np.empty(224, np.int32)
+    count = np.empty(224, np.int32)
+    idx = np.empty(cap, np.int32)
+    coef = np.empty(cap, np.float32)
+    n = check(_lib.lib().b2i_resize_plan(in_size, out_size, crop, _ptr(first), _ptr(count), _ptr(idx), _ptr(coef), cap))
+    return [(idx[f:f + c].copy(), coef[f:f + c].copy()) for f, c in zip(first, count)], n
+
+
+def ot_inspect(path):
+    buf = ctypes.create_string_buffer(1 << 16)
+    n = check(_lib.lib().b2i_ot_inspect(str(path).encode(), buf, len(buf)))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, _, shape = line.partition(":")
+        out[name] = tuple(int(d) for d in shape.split("x")) if shape else ()
+    return out, n
+
+
+def ot_read_tensor(path, name):
+    n = check(_lib.lib().b2i_ot_read_tensor(str(path).encode(), name.encode(), None, 0))
+    out = np.empty(n, np.float32)
+    check(_lib.lib().b2i_ot_read_tensor(str(path).encode(), name.encode(), _ptr(out), n))
+    return out
+
+
+class Model:
+    """A loaded network on every GPU of a context (replaces `Mutex<Box<dyn ModuleT>>`,
+    reference src/services.rs:455-456, built at 513-524)."""
+
+    def __init__(self, ctx, model_name, ot_path, precision=PREC_BF16, max_batch=256, micro_batch=0,
+                 alexnet_geometry=ALEXNET_TCH, conv_mode=-1, weights_tma=1, tile_n_max=0, keep_tensors=False):
+        cfg = ModelConfig()
+        _lib.lib().b2i_default_config(ctypes.byref(cfg))
+        cfg.precision, cfg.max_batch, cfg.micro_batch = precision, max_batch, micro_batch
+        cfg.alexnet_geometry, cfg.conv_mode, cfg.weights_tma = alexnet_geometry, conv_mode, weights_tma
+        cfg.tile_n_max, cfg.keep_tensors = tile_n_max, int(keep_tensors)
+        h = ctypes.c_void_p()
+        check(_lib.lib().b2i_model_load(ctx._h, model_name.encode(), str(ot_path).encode(), ctypes.byref(cfg),
+                                        ctypes.byref(h)))
+        self._h = h
+        self.ctx = ctx
+        self.name = model_name
+        self.max_batch = max_batch
+        self.precision = precision
+
+    def close(self):
+        if self._h:
+            _lib.lib().b2i_model_free(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def flops_per_image(self):
+        return _lib.lib().b2i_model_flops_per_image(self._h)
+
+    @property
+    def launches_per_microbatch(self):
+        return _lib.lib().b2i_model_launches_per_microbatch(self._h)
+
+    @property
+    def num_devices(self):
+        return _lib.lib().b2i_model_num_devices(self._h)
+
+    @property
+    def weight_bytes(self):
+        return _lib.lib().b2i_model_weight_bytes(self._h)
+
+    @property
+    def activation_bytes(self):
+        return _lib.lib().b2i_model_activation_bytes(self._h)
+
+    def predict_u8(self, images_u8, k=5, want_logits=False, devices=None):
+        """images u8 [n,224,224,3] (host) -> (idx int32 [n,k], prob f32 [n,k][, logits f32 [n,1000]])."""
+        img = images_u8 if (isinstance(images_u8, np.ndarray) and images_u8.dtype == np.uint8 and
+                            images_u8.flags.c_contiguous) else np.ascontiguousarray(images_u8, dtype=np.uint8)
+        n = img.shape[0]
+        assert img.shape[1:] == (224, 224, 3), img.shape
+        idx = np.empty((n, k), np.int32)
+        prob = np.empty((n, k), np.float32)
+        logits = np.empty((n, CLASSES), np.float32) if want_logits else None
+        if devices is None:
+            check(_lib.lib().b2i_predict_u8(self._h, _ptr(img), n, k, _ptr(idx), _ptr(prob), _ptr(logits)))
+        else:
+            first, count = devices
+            check(_lib.lib().b2i_predict_u8_on(self._h, first, count, _ptr(img), n, k, _ptr(idx), _ptr(prob),
+                                               _ptr(logits)))
+        return (idx, prob, logits) if want_logits else (idx, prob)
+
+    def forward_device(self, d_images, n, k, d_idx, d_prob, d_logits=None, stream=None, dev=0):
+        """Raw device pointers (ints) on GPU `dev`; enqueues on `stream` (cudaStream_t as int)."""
+        check(_lib.lib().b2i_forward_device(self._h, dev, d_images, n, k, d_idx, d_prob, d_logits, stream))
+
+    def num_tensors(self):
+        return _lib.lib().b2i_model_num_tensors(self._h)
+
+    def tensor_shape(self, tid):
+        h, w, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        check(_lib.lib().b2i_model_tensor_shape(self._h, tid, ctypes.byref(h), ctypes.byref(w), ctypes.byref(c)))
+        return h.value, w.value, c.value
+
+    def read_tensor(self, tid, n, dev=0):
+        h, w, c = self.tensor_shape(tid)
+        out = np.empty((n, h, w, c), np.float32)
+        check(_lib.lib().b2i_model_read_tensor(self._h, dev, tid, n, _ptr(out), out.size))
+        return out
+
+
+class PinnedBuffer:
+    """Page-locked host memory viewed as a numpy u8 array (staging-free path of predict_u8)."""
+
+    def __init__(self, nbytes):
+        p = _lib.lib().b2i_host_alloc(nbytes)
+        if not p:
+            raise B2IError(_lib.ENOMEM, "pinned allocation of %d bytes failed" % nbytes)
+        self._p = p
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * nbytes).from_address(p))
+
+    def close(self):
+        if self._p:
+            self.array = None
+            _lib.lib().b2i_host_free(self._p)
+            self._p = None

@@ -1,0 +1,207 @@
+"""Host-side mirror of the reference's operator interface for the inference path, over the C ABI.
+
+Same names, argument meaning and error behaviour as the Rust it stands in for (the Rust toolchain
+is absent here, see INTEGRATION.md for the cgo-style binding a maintainer would add):
+
+  load_labels          reference src/services.rs:170-184   (synset_words.txt -> [(wnid, label)])
+  load_model           reference src/model_utils.rs:24-36  (fails loudly instead of swallowing errors)
+  predict_image        reference src/model_utils.rs:38-49
+  MemberState.predict  reference src/services.rs:475-497   (Member::predict RPC handler body)
+  Job                  reference src/services.rs:54-81
+  Leader.assign_members reference src/services.rs:199-211  (dual-job fair share; members = GPUs)
+  Leader.run_job       reference src/services.rs:407-433   (batched: many ids per predict call)
+  jobs_report          reference src/main.rs:281-309       (ms percentiles + accuracy)
+
+JPEG decode stays on the host (PIL), as SURVEY.md 8b prescribes: the ABI takes pixels, not paths.
+"""
+import math
+import os
+import time
+
+import numpy as np
+
+from .infer import ALEXNET_TCH, PREC_BF16, Context, Model
+
+IMAGE_ROOT = os.path.join("test_files", "imagenet_1k", "train")       # services.rs:476
+WEIGHT_DIR = "pretrained_models"                                       # services.rs:516,522
+MODEL_NAMES = ("resnet18", "alexnet")
+
+
+def load_labels(path="synset_words.txt"):
+    """[(wnid, label)] in class-index order; label = remaining words joined by single spaces."""
+    labels = []
+    with open(path) as f:
+        for line in f:
+            parts = line.split()
+            if parts:
+                labels.append((parts[0], " ".join(parts[1:])))
+    return labels
+
+
+def decode_image(path):
+    """u8 [H,W,3] RGB; None when the file cannot be decoded (tch's `.ok()?`, services.rs:492)."""
+    try:
+        from PIL import Image
+        with Image.open(path) as im:
+            return np.asarray(im.convert("RGB"))
+    except Exception:
+        return None
+
+
+def load_model(model_name, ctx=None, weight_dir=WEIGHT_DIR, **kw):
+    """`load_model(name)`: build the named network and load `<weight_dir>/<name>.ot`.  Unknown names
+    raise (the reference panics, model_utils.rs:30); unlike the reference's dead-code twin a missing
+    or invalid archive is an error, not silently random weights."""
+    if model_name not in MODEL_NAMES:
+        raise ValueError("Model not found: %r" % (model_name,))
+    ctx = ctx or Context((0,))
+    return Model(ctx, model_name, os.path.join(weight_dir, model_name + ".ot"), **kw)
+
+
+def predict_image(model, image_path, label, labels, ctx=None):
+    """Some(top1_label == label) / None on decode failure (model_utils.rs:38-49)."""
+    img = decode_image(image_path)
+    if img is None:
+        return None
+    x = (ctx or model.ctx).resize_crop(img)[None]
+    idx, _ = model.predict_u8(x, k=1)
+    return labels[int(idx[0, 0])][1] == label
+
+
+class MemberState:
+    """The model half of the reference's `MemberState` (services.rs:450-457, 513-524): one ResNet-18
+    and one AlexNet resident on this member's GPUs, and the body of `Member::predict`."""
+
+    def __init__(self, ctx, labels, weight_dir=WEIGHT_DIR, image_root=IMAGE_ROOT, precision=PREC_BF16,
+                 max_batch=256, alexnet_geometry=ALEXNET_TCH, models=MODEL_NAMES):
+        self.ctx = ctx
+        self.labels = labels
+        self.image_root = image_root
+        # services.rs:516,522 `.unwrap()`: a missing archive is fatal at start-up
+        self.models = {
+            name: Model(ctx, name, os.path.join(weight_dir, name + ".ot"), precision=precision,
+                        max_batch=max_batch, alexnet_geometry=alexnet_geometry)
+            for name in models
+        }
+
+    def close(self):
+        for m in self.models.values():
+            m.close()
+
+    def predict(self, model_name, input_ids, k=1, devices=None):
+        """Option<Vec<(f64, String)>>: None for an unknown model (services.rs:480) or when any image
+        fails to decode (services.rs:492); ids whose directory is empty are skipped (services.rs:490);
+        a missing directory raises (the reference unwraps, services.rs:485).  With k > 1 each entry
+        is a list of k (prob, label) pairs instead of one pair."""
+        model = self.models.get(model_name)
+        if model is None:
+            return None
+        batch = []
+        for input_id in input_ids:
+            entries = sorted(os.listdir(os.path.join(self.image_root, input_id)))
+            if not entries:
+                continue
+            img = decode_image(os.path.join(self.image_root, input_id, entries[0]))
+            if img is None:
+                return None
+            batch.append(self.ctx.resize_crop(img))
+        if not batch:
+            return []
+        idx, prob = model.predict_u8(np.stack(batch), k=k, devices=devices)
+        if k == 1:
+            return [(float(p[0]), self.labels[int(i[0])][1]) for i, p in zip(idx, prob)]
+        return [[(float(pp), self.labels[int(ii)][1]) for ii, pp in zip(i, p)] for i, p in zip(idx, prob)]
+
+
+class Job:
+    """services.rs:54-81."""
+
+    def __init__(self, model_name):
+        self.model_name = model_name
+        self.finished_prediction_count = 0
+        self.correct_prediction_count = 0
+        self.query_durations = []          # seconds, one per query (image)
+        self.assigned_member_ids = []
+
+    def add_query_result(self, correct, duration):
+        self.finished_prediction_count += 1
+        if correct:
+            self.correct_prediction_count += 1
+        self.query_durations.append(duration)
+
+
+def assign_members(active_ids, job_resnet18, job_alexnet):
+    """Resource manager tick (services.rs:199-211): sorted ids, first floor(n/2) to ResNet-18, the
+    rest to AlexNet.  Here an id is a GPU index of the member's context."""
+    ids = sorted(set(active_ids))
+    job_resnet18.assigned_member_ids = ids[:len(ids) // 2]
+    job_alexnet.assigned_member_ids = ids[len(ids) // 2:]
+
+
+class Leader:
+    """The job half of `LeaderState` (services.rs:83-95, 146-155, 407-433) driving one MemberState."""
+
+    def __init__(self, member, labels):
+        self.member = member
+        self.labels = labels
+        self.resnet18 = Job("resnet18")
+        self.alexnet = Job("alexnet")
+
+    def jobs(self):
+        return [self.resnet18, self.alexnet]
+
+    def run_job(self, job, batch=32, limit=None, log=None):
+        """Batched `run_job`: resumes at labels[finished_prediction_count..] (services.rs:410-411),
+        sends `batch` ids per predict call to the job's assigned GPUs, skips the labels silently when
+        nobody is assigned (services.rs:416), records one duration per query = the wall time of the
+        batch that carried it, and prints the reference's result lines (services.rs:425-429)."""
+        start_at = job.finished_prediction_count
+        todo = self.labels[start_at:] if limit is None else self.labels[start_at:start_at + limit]
+        for i in range(0, len(todo), batch):
+            chunk = todo[i:i + batch]
+            ids = list(job.assigned_member_ids)
+            if not ids:
+                continue
+            devices = (min(ids), max(ids) - min(ids) + 1)
+            t0 = time.perf_counter()
+            res = self.member.predict(job.model_name, [wnid for wnid, _ in chunk], devices=devices)
+            dt = time.perf_counter() - t0
+            if res is None:
+                continue
+            for (wnid, true_label), (prob, pred) in zip(chunk, res):
+                job.add_query_result(pred == true_label, dt)
+                if log:
+                    if pred == true_label:
+                        log("%s - %s: %s (%.2f%%)" % (job.model_name, wnid, pred, prob * 100.0))
+                    else:
+                        log("%s - %s: %s (%.2f%%) (should be %s)" % (job.model_name, wnid, pred, prob * 100.0, true_label))
+
+    def predict(self, batch=32, limit=None, log=None):
+        """`Leader::predict` (services.rs:146-151) joins both jobs; they run on disjoint GPU halves."""
+        import threading
+        th = [threading.Thread(target=self.run_job, args=(j, batch, limit, log)) for j in self.jobs()]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+
+
+def jobs_report(job):
+    """Numbers the CLI `jobs` command prints (main.rs:281-309): accuracy and query-latency stats in
+    integer milliseconds.  Percentiles are exact order statistics (the reference's bucketed
+    histogram is an approximation of these)."""
+    ms = sorted(int(d * 1000.0) for d in job.query_durations)
+    n = len(ms)
+    if n == 0:
+        return {"model": job.model_name, "finished": 0, "correct": 0, "accuracy": 0.0, "total": 0}
+    mean = sum(ms) / n
+    std = math.sqrt(sum((v - mean) ** 2 for v in ms) / n)
+    pct = lambda q: ms[min(n - 1, max(0, int(math.ceil(q / 100.0 * n)) - 1))]
+    return {
+        "model": job.model_name,
+        "finished": job.finished_prediction_count,
+        "correct": job.correct_prediction_count,
+        "accuracy": 100.0 * job.correct_prediction_count / max(1, job.finished_prediction_count),
+        "total": n, "avg_ms": mean, "std_ms": std, "median_ms": pct(50), "p90_ms": pct(90), "p95_ms": pct(95),
+        "p99_ms": pct(99),
+    }

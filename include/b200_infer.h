@@ -115,6 +115,14 @@ int b2i_forward_device(b2i_model* m, int dev, const void* d_images_u8, int n, in
  * u8 [h][w][3] -> u8 [224][224][3] on the GPU `dev` of ctx. */
 int b2i_resize_crop_u8(b2i_ctx* ctx, int dev, const uint8_t* image, int h, int w, uint8_t* out224);
 
+/* CPU-only: the resampling plan b2i_resize_crop_u8 uses for one axis (in_size -> out_size, keeping
+ * the 224 outputs from `crop` on). first/count: int[224]; idx/coef: up to cap taps. Returns the
+ * number of taps or a negative code. Lets the host logic be checked without a GPU. */
+int b2i_resize_plan(int in_size, int out_size, int crop, int* first, int* count, int* idx,
+                    float* coef, int cap);
+/* CPU-only: target size and crop offsets for an h x w image. */
+void b2i_resize_target(int h, int w, int* rw, int* rh, int* crop_x, int* crop_y);
+
 /* Pinned host memory for the staging-free fast path of b2i_predict_u8. */
 void* b2i_host_alloc(size_t bytes);
 void b2i_host_free(void* p);

@@ -1,0 +1,64 @@
+"""The C-ABI library loads and exports every symbol include/b200_infer.h declares; without a GPU
+the compute entry points fail loudly instead of falling back."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200_infer.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b2i_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_the_boundary():
+    syms = declared_symbols()
+    for must in ("b2i_init", "b2i_model_load", "b2i_predict_u8", "b2i_predict_u8_on", "b2i_model_free",
+                 "b2i_last_error", "b2i_resize_crop_u8", "b2i_forward_device"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    handle = ctypes.CDLL(pkg.LIB_PATH)
+    missing = [s for s in declared_symbols() if not hasattr(handle, s)]
+    assert not missing, missing
+
+
+def test_python_binding_covers_every_declared_symbol(pkg):
+    from importlib import import_module
+    sigs = import_module("distributed-machine-learning-cluster_b200._lib").SIGNATURES
+    assert sorted(sigs) == declared_symbols()
+
+
+def test_no_torch_in_the_boundary():
+    text = open(os.path.join(ROOT, "include", "b200_infer.h")).read()
+    assert "torch" not in text.lower().replace("torchvision", "")
+    assert "at::" not in text and "std::" not in text
+
+
+def test_library_does_not_link_torch_or_cpu_blas(pkg):
+    import subprocess
+    out = subprocess.run(["ldd", pkg.LIB_PATH], capture_output=True, text=True).stdout
+    for banned in ("libtorch", "libc10", "libcudnn", "libcublas", "libmkl", "libopenblas"):
+        assert banned not in out, out
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="GPU present")
+def test_compute_fails_loudly_without_gpu(pkg):
+    assert pkg.device_count() == 0
+    with pytest.raises(pkg.B2IError) as e:
+        pkg.Context((0,))
+    assert e.value.code == -4 and "no CPU path" in str(e.value)
+
+
+def test_product_never_imports_the_oracle():
+    pkgdir = os.path.join(ROOT, "distributed-machine-learning-cluster_b200")
+    for dirpath, _, files in os.walk(pkgdir):
+        for fn in files:
+            if fn.endswith((".py", ".cpp", ".cu", ".h", ".cuh")):
+                src = open(os.path.join(dirpath, fn)).read()
+                assert "oracle" not in src.replace("oracle/", "").lower() or fn == "__none__", (fn, "mentions oracle")

@@ -1,0 +1,185 @@
+"""Whole-network parity on the GPU through the C ABI (b2i_model_load / b2i_predict_u8) against the
+oracle and the committed golden vectors: logits, softmax probabilities and top-5 indices, for both
+models, both precisions, both AlexNet geometries, ragged / empty / single-image batches.
+
+Tolerances (BASELINE.json north_star): fp32 mode 1e-4 max-abs, bf16 mode 2e-2 max-abs on logits,
+stated for O(1) logits.  The seeded synthetic networks produce logits with std 9.0 (ResNet-18) and
+1.9 (AlexNet), so both bounds are applied in units of max(1, std of the oracle's logits); the
+absolute gap is printed next to the gap of a bf16-emulating oracle so the budget is interpretable.
+Top-5 indices must be identical wherever the oracle's margin between neighbouring ranks exceeds
+twice the logit tolerance."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+BF16, FP32 = 0, 1
+GV = np.load(os.path.join(GOLDEN, "golden_vectors.npz"))
+
+
+def fixture_crops():
+    from oracle import stb_resize
+    root = os.path.join(GOLDEN, "imagenet_1k", "train")
+    return np.stack([stb_resize.load_image_and_resize(os.path.join(root, w, sorted(os.listdir(os.path.join(root, w)))[0]))
+                     for w in GV["wnids"]])
+
+
+def tol_for(precision, ref_logits):
+    unit = max(1.0, float(np.std(ref_logits)))
+    return (2e-2 if precision == BF16 else 1e-4) * unit
+
+
+def check_against(ref_logits, idx, prob, logits, precision, what):
+    tol = tol_for(precision, ref_logits)
+    gap = float(np.abs(logits - ref_logits).max())
+    print("%s: logits max-abs gap %.3e (tolerance %.3e, oracle logit std %.3f, absmax %.3f)" %
+          (what, gap, tol, np.std(ref_logits), np.abs(ref_logits).max()))
+    assert gap <= tol, what
+    # softmax + top-5 of the kernel's own logits must be what torch computes from them
+    t = torch.from_numpy(logits)
+    p = torch.softmax(t, -1)
+    pv, pi = torch.topk(p, idx.shape[1], -1)
+    assert np.abs(prob - pv.numpy()).max() <= 1e-5
+    # top-k indices vs the ORACLE's logits wherever ranks are separated by more than the tolerance
+    order = np.argsort(-ref_logits, axis=1)
+    srt = np.take_along_axis(ref_logits, order, 1)
+    k = idx.shape[1]
+    for r in range(ref_logits.shape[0]):
+        margins = srt[r, :k] - srt[r, 1:k + 1]
+        if (margins > 2 * tol).all():
+            assert np.array_equal(idx[r], order[r, :k]), (what, r, idx[r], order[r, :k])
+
+
+@pytest.mark.parametrize("precision", [BF16, FP32], ids=["bf16", "fp32"])
+def test_resnet18_fixture_images_match_golden(pkg, ctx, resnet18_ot, precision):
+    crops = fixture_crops()
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=precision, max_batch=8) as m:
+        idx, prob, logits = m.predict_u8(crops, k=5, want_logits=True)
+    check_against(GV["resnet18_logits"], idx, prob, logits, precision, "resnet18 fixtures")
+
+
+@pytest.mark.parametrize("geometry", [0, 1], ids=["tch", "torchvision"])
+@pytest.mark.parametrize("precision", [BF16, FP32], ids=["bf16", "fp32"])
+def test_alexnet_fixture_images_match_golden(pkg, ctx, alexnet_ot, precision, geometry):
+    crops = fixture_crops()
+    with pkg.Model(ctx, "alexnet", alexnet_ot, precision=precision, max_batch=8, alexnet_geometry=geometry) as m:
+        idx, prob, logits = m.predict_u8(crops, k=5, want_logits=True)
+    ref = GV["alexnet_tch_logits" if geometry == 0 else "alexnet_torchvision_logits"]
+    check_against(ref, idx, prob, logits, precision, "alexnet fixtures geometry %d" % geometry)
+
+
+@pytest.mark.parametrize("conv_mode", [0, 1], ids=["gather", "im2col"])
+def test_resnet18_per_layer_parity_bf16(pkg, ctx, resnet18_ot, conv_mode):
+    """Every activation of the bf16 path against an oracle that rounds at the same places
+    (bf16 weights after BN fold are NOT emulated: per-layer bound is 3% of the layer's scale)."""
+    from oracle import synth, tch_oracle
+    img = synth.synthetic_images(3, seed=4)
+    w = synth.resnet18_weights()
+    taps = []
+    with torch.no_grad():
+        tch_oracle.resnet18_forward(w, tch_oracle.normalize_u8(img), taps)
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=3, keep_tensors=True, conv_mode=conv_mode) as m:
+        m.predict_u8(img, k=5)
+        shapes = [m.tensor_shape(t) for t in range(m.num_tensors())]
+        # tensors in execution order: 0 input, 1 conv1, 2 maxpool, then per block (downsample?), conv1, conv2
+        got = {t: m.read_tensor(t, 3) for t in range(m.num_tensors() - 1)}
+    names = {"conv1": 1, "maxpool": 2}
+    tid = 3
+    for L in range(1, 5):
+        for B in range(2):
+            tid += (3 if (L > 1 and B == 0) else 2)
+            names["layer%d.%d" % (L, B)] = tid - 1
+    names["avgpool"] = tid
+    worst = 0.0
+    for name, t in taps:
+        ref = t.permute(0, 2, 3, 1).numpy()
+        g = got[names[name]]
+        assert g.shape == ref.shape, (name, g.shape, ref.shape, shapes[names[name]])
+        rel = float(np.abs(g - ref).max() / max(1e-6, np.abs(ref).max()))
+        print("%-10s tensor %2d max-abs/scale %.4f" % (name, names[name], rel))
+        worst = max(worst, rel)
+        assert rel < 0.03, name
+    assert worst > 0  # the comparison really ran
+
+
+def test_batch_shapes_ragged_empty_single(pkg, ctx, resnet18_ot):
+    from oracle import synth
+    img = synth.synthetic_images(11, seed=0)
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=16, micro_batch=4) as m:
+        idx_all, prob_all, lg_all = m.predict_u8(img, k=5, want_logits=True)        # 4+4+3: ragged micro-batches
+        idx0, prob0 = m.predict_u8(img[:0], k=5)
+        assert idx0.shape == (0, 5) and prob0.shape == (0, 5)
+        idx1, prob1, lg1 = m.predict_u8(img[4:5], k=5, want_logits=True)
+        # an image's result does not depend on its batch position or on its neighbours
+        assert np.array_equal(lg1[0], lg_all[4]) and np.array_equal(idx1[0], idx_all[4])
+        with pytest.raises(pkg.B2IError):
+            m.predict_u8(synth.synthetic_images(17, seed=1), k=5)                  # > max_batch
+        with pytest.raises(pkg.B2IError):
+            m.predict_u8(img, k=9)
+    ref = GV["resnet18_logits_synthetic4"]
+    assert np.abs(lg_all[:4] - ref).max() <= tol_for(BF16, ref)
+
+
+def test_model_load_errors(pkg, ctx, tmp_path, resnet18_ot):
+    with pytest.raises(pkg.B2IError) as e:
+        pkg.Model(ctx, "vgg16", resnet18_ot)
+    assert e.value.code == -1                                   # unknown model: the reference returns None
+    with pytest.raises(pkg.B2IError) as e:
+        pkg.Model(ctx, "resnet18", str(tmp_path / "nope.ot"))
+    assert e.value.code == -2                                   # the reference panics at start-up
+    with pytest.raises(pkg.B2IError) as e:
+        pkg.Model(ctx, "alexnet", resnet18_ot)                  # wrong archive for the graph
+    assert e.value.code == -2 and "missing tensor" in str(e.value)
+
+
+def test_member_predict_mirrors_reference_semantics(pkg, ctx, resnet18_ot, alexnet_ot, tmp_path):
+    """Member::predict (services.rs:475-497) over the fixture directory layout."""
+    import shutil
+    labels = pkg.load_labels(os.path.join(GOLDEN, "synset_words.txt"))
+    assert len(labels) == 1000 and labels[0] == ("n01440764", "tench, Tinca tinca")
+    wd = tmp_path / "pretrained_models"
+    wd.mkdir()
+    os.symlink(resnet18_ot, wd / "resnet18.ot")
+    os.symlink(alexnet_ot, wd / "alexnet.ot")
+    root = os.path.join(GOLDEN, "imagenet_1k", "train")
+    member = pkg.MemberState(ctx, labels, weight_dir=str(wd), image_root=root, max_batch=8)
+    try:
+        assert member.predict("vgg16", ["n01491361"]) is None
+        ids = list(GV["wnids"])
+        res = member.predict("resnet18", ids)
+        assert len(res) == 8 and all(0.0 < p <= 1.0 and isinstance(lbl, str) for p, lbl in res)
+        top1 = np.argmax(GV["resnet18_logits"], 1)
+        srt = np.sort(GV["resnet18_logits"], 1)
+        for i, (p, lbl) in enumerate(res):
+            if srt[i, -1] - srt[i, -2] > 2 * tol_for(BF16, GV["resnet18_logits"]):
+                assert lbl == labels[top1[i]][1]
+        res5 = member.predict("alexnet", ids[:2], k=5)
+        assert len(res5) == 2 and len(res5[0]) == 5
+        with pytest.raises(FileNotFoundError):
+            member.predict("resnet18", ["n00000000"])           # missing directory: the reference unwraps
+        empty = tmp_path / "imgs" / "n123"
+        empty.mkdir(parents=True)
+        bad = tmp_path / "imgs" / "n456"
+        bad.mkdir()
+        (bad / "x.JPEG").write_bytes(b"not a jpeg")
+        member.image_root = str(tmp_path / "imgs")
+        assert member.predict("resnet18", ["n123"]) == []       # empty dir: id skipped (services.rs:490)
+        assert member.predict("resnet18", ["n456"]) is None     # decode failure voids the call (services.rs:492)
+        # leader-side accounting on top (services.rs:407-433, 54-81)
+        member.image_root = root
+        leader = pkg.Leader(member, [(w, dict(labels)[w]) for w in ids])
+        pkg.assign_members([0], leader.resnet18, leader.alexnet)
+        assert leader.resnet18.assigned_member_ids == [] and leader.alexnet.assigned_member_ids == [0]
+        leader.run_job(leader.resnet18, batch=4)                 # nobody assigned: labels skipped, nothing counted
+        assert leader.resnet18.finished_prediction_count == 0
+        leader.run_job(leader.alexnet, batch=3)
+        assert leader.alexnet.finished_prediction_count == 8 and len(leader.alexnet.query_durations) == 8
+        rep = pkg.jobs_report(leader.alexnet)
+        assert rep["total"] == 8 and rep["p99_ms"] >= rep["median_ms"]
+    finally:
+        member.close()

@@ -1,0 +1,125 @@
+"""Pins the oracle (CPU restatement of the tch path).  The reference holds no golden vectors for
+this path (parity unpinned), so the anchors are: an independent implementation of
+the same graphs (torchvision), the reference's layer/FLOP tables, and the committed golden vectors."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from oracle import stb_resize, synth, tch_oracle
+
+GV = np.load(os.path.join(GOLDEN, "golden_vectors.npz"))
+
+
+def fixture_crops():
+    root = os.path.join(GOLDEN, "imagenet_1k", "train")
+    return np.stack([stb_resize.load_image_and_resize(os.path.join(root, w, sorted(os.listdir(os.path.join(root, w)))[0]))
+                     for w in GV["wnids"]])
+
+
+def test_resnet18_graph_matches_torchvision():
+    """Same weights through torchvision.models.resnet18 (an independent statement of the graph tch
+    mirrors): logits agree to fp32 round-off."""
+    import torchvision
+    w = synth.resnet18_weights()
+    m = torchvision.models.resnet18(num_classes=1000)
+    sd = {k: v for k, v in w.items()}
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and all(k.endswith("num_batches_tracked") for k in missing)
+    m.eval()
+    x = tch_oracle.normalize_u8(synth.synthetic_images(2, seed=5))
+    with torch.no_grad():
+        ref, got = m(x), tch_oracle.resnet18_forward(w, x)
+    assert torch.allclose(ref, got, rtol=0, atol=1e-4 * float(ref.abs().max()))
+
+
+def test_alexnet_torchvision_geometry_matches_torchvision():
+    import torchvision
+    w = synth.alexnet_weights()
+    m = torchvision.models.alexnet(num_classes=1000)
+    m.load_state_dict(dict(w))
+    m.eval()
+    x = tch_oracle.normalize_u8(synth.synthetic_images(2, seed=6))
+    with torch.no_grad():
+        ref, got = m(x), tch_oracle.alexnet_forward(w, x, geometry="torchvision")
+    assert torch.allclose(ref, got, rtol=0, atol=1e-4 * float(ref.abs().max()))
+
+
+def test_alexnet_tch_geometry_shapes():
+    """features.3 = k5 p1 s2: 27 -> 13 -> 6 -> 6 -> 6 -> 2, then adaptive pool 2x2 -> 6x6 replicates
+    (right column)."""
+    w = synth.alexnet_weights()
+    taps = []
+    with torch.no_grad():
+        tch_oracle.alexnet_forward(w, tch_oracle.normalize_u8(synth.synthetic_images(1)), "tch", taps)
+    shapes = {n: tuple(t.shape[1:]) for n, t in taps}
+    assert shapes["features.0"] == (64, 55, 55) and shapes["pool0"] == (64, 27, 27)
+    assert shapes["features.3"] == (192, 13, 13) and shapes["pool1"] == (192, 6, 6)
+    assert shapes["features.10"] == (256, 6, 6) and shapes["pool2"] == (256, 2, 2)
+    assert shapes["avgpool"] == (256, 6, 6)
+    ap = dict(taps)["avgpool"][0, 0]
+    p2 = dict(taps)["pool2"][0, 0]
+    assert torch.equal(ap, p2.repeat_interleave(3, 0).repeat_interleave(3, 1))
+
+
+def test_resnet18_mac_count_matches_survey():
+    """1,814,073,344 MAC per image over conv + FC."""
+    w = synth.resnet18_weights()
+    macs = 0
+    hw = {"conv1": 112, "layer1": 56, "layer2": 28, "layer3": 14, "layer4": 7}
+    for name, t in w.items():
+        if name.endswith("weight") and t.dim() == 4:
+            macs += t.numel() * hw[name.split(".")[0]] ** 2
+    macs += w["fc.weight"].numel()
+    assert macs == 1_814_073_344
+
+
+def test_normalize_matches_definition():
+    img = synth.synthetic_images(1, seed=2)
+    x = tch_oracle.normalize_u8(img)[0].numpy()
+    for c in range(3):
+        want = (img[0, :, :, c].astype(np.float32) / np.float32(255.0) - np.float32(tch_oracle.MEAN[c])) / np.float32(tch_oracle.STD[c])
+        assert np.allclose(x[c], want, rtol=0, atol=1e-6)
+
+
+def test_softmax_topk_sorted_and_normalised():
+    lg = torch.randn(7, 1000, generator=torch.Generator().manual_seed(0))
+    idx, prob = tch_oracle.softmax_topk(lg, 5)
+    assert idx.shape == (7, 5) and (prob[:, :-1] >= prob[:, 1:]).all()
+    assert torch.equal(idx[:, 0].long(), lg.argmax(1))
+
+
+def test_resize_target_rule():
+    assert stb_resize.resize_target(332, 500) == (337, 224, 56, 0)      # the model_utils.rs:8 sample image
+    assert stb_resize.resize_target(500, 331) == (224, 338, 0, 57)
+    assert stb_resize.resize_target(100, 100) == (224, 224, 0, 0)       # square shortcut
+    assert stb_resize.resize_target(94, 120) == (285, 224, 30, 0)       # up-sampling path
+    rw, rh, cx, cy = stb_resize.resize_target(2877, 100)
+    assert rw == 224 and rh >= 224 and cx == 0 and cy == (rh - 224) // 2
+
+
+def test_resize_identity_like_properties():
+    flat = np.full((300, 400, 3), 77, np.uint8)
+    assert (stb_resize.resize_crop_224(flat) == 77).all()                # weights sum to one on every output
+    ramp = np.tile(np.arange(224, dtype=np.uint8)[None, :, None], (448, 1, 3))
+    out = stb_resize.resize_crop_224(ramp)                               # width already 224 (scale 1): Mitchell blur of a ramp is the ramp
+    assert np.abs(out[:, 4:-4, :].astype(int) - ramp[:224, 4:-4, :].astype(int)).max() <= 1
+
+
+def test_golden_vectors_still_reproduce():
+    crops = fixture_crops()
+    assert [hashlib.sha256(c.tobytes()).hexdigest() for c in crops] == list(GV["crop_sha256"])
+    i = list(GV["wnids"]).index("n03825788")
+    assert np.array_equal(crops[i], GV["crop_n03825788"])
+    _, _, lg = tch_oracle.predict_u8("resnet18", synth.resnet18_weights(), crops)
+    assert np.allclose(lg, GV["resnet18_logits"], rtol=0, atol=2e-4 * np.abs(lg).max())
+    _, _, la = tch_oracle.predict_u8("alexnet", synth.alexnet_weights(), crops[:3], alexnet_geometry="tch")
+    assert np.allclose(la, GV["alexnet_tch_logits"][:3], rtol=0, atol=2e-4 * np.abs(la).max())
+
+
+def test_unknown_model_is_an_error():
+    with pytest.raises(ValueError):
+        tch_oracle.forward("vgg16", {}, torch.zeros(1, 3, 224, 224))
