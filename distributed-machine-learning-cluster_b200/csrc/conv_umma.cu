@@ -311,7 +311,7 @@ cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMa
   auto kern = conv_umma_kernel<AMODE, B_TMA>;
   if (dev < 16 && !attr_set[dev]) {
     cudaError_t e =
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);  // 227 KB minus the static barriers
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
