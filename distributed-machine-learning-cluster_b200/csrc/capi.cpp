@@ -418,6 +418,28 @@ int b2i_forward_device(b2i_model* m, int dev, const void* d_images, int n, int k
   return B2I_OK;
 }
 
+int b2i_model_profile(b2i_model* m, int dev, const void* d_images, int n, int k, void* d_idx,
+                      void* d_prob, void* stream, float* ms, int cap, char* labels_out,
+                      size_t labels_cap) {
+  if (!m || dev < 0 || dev >= static_cast<int>(m->slots.size()) || !d_images || !d_idx || !d_prob || !ms)
+    return fail(B2I_EINVAL, "b2i_model_profile: bad argument");
+  std::vector<float> v;
+  std::vector<std::string> names;
+  std::string err;
+  if (!m->slots[dev].dm->profile(static_cast<const uint8_t*>(d_images), n, k, static_cast<int32_t*>(d_idx),
+                                 static_cast<float*>(d_prob), static_cast<cudaStream_t>(stream), &v, &names, &err))
+    return fail(B2I_ECUDA, err);
+  if (static_cast<int>(v.size()) > cap) return fail(B2I_EINVAL, "ms buffer too small");
+  std::memcpy(ms, v.data(), v.size() * 4);
+  if (labels_out && labels_cap) {
+    std::string s;
+    for (auto& nm : names) s += nm + "\n";
+    std::strncpy(labels_out, s.c_str(), labels_cap - 1);
+    labels_out[labels_cap - 1] = 0;
+  }
+  return static_cast<int>(v.size());
+}
+
 void* b2i_host_alloc(size_t bytes) {
   void* p = nullptr;
   if (cudaMallocHost(&p, bytes) != cudaSuccess) {

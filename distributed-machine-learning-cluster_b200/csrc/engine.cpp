@@ -396,7 +396,14 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       }
     }
     ops_.push_back(d);
+    switch (o.kind) {
+      case OpSpec::NORMALIZE: op_names_.push_back("normalize"); break;
+      case OpSpec::MAXPOOL: op_names_.push_back("maxpool"); break;
+      case OpSpec::AVGPOOL: op_names_.push_back("avgpool"); break;
+      case OpSpec::CONV: op_names_.push_back((o.fc ? "fc:" : "conv:") + net.convs[o.conv].name); break;
+    }
   }
+  op_names_.push_back("softmax_topk");
   return true;
 }
 
@@ -404,6 +411,11 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
                                  float* d_logits, cudaStream_t st, std::string* err) {
   const int dt = cfg_.precision == PREC_FP32 ? DT_F32 : DT_BF16;
   auto buf = [&](int tensor) { return tensor >= 0 ? bufs_[tensor_buf_[tensor]] : nullptr; };
+  size_t ev = 0;
+  auto mark = [&]() {
+    if (prof_events_ && ev < prof_events_->size()) cudaEventRecord((*prof_events_)[ev++], st);
+  };
+  mark();
   for (DevOp& d : ops_) {
     const OpSpec& o = d.spec;
     switch (o.kind) {
@@ -447,9 +459,11 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         break;
       }
     }
+    mark();
   }
   const float* lg = static_cast<const float*>(buf(logits_tensor_));
   B2I_CUDA(launch_softmax_topk(lg, nb, classes_, classes_, k, d_idx, d_prob, st));
+  mark();
   if (d_logits)
     B2I_CUDA(cudaMemcpyAsync(d_logits, lg, static_cast<size_t>(nb) * classes_ * 4,
                              cudaMemcpyDeviceToDevice, st));
@@ -472,6 +486,27 @@ bool DeviceModel::forward(const uint8_t* d_u8, int n, int k, int32_t* d_idx, flo
       return false;
   }
   return true;
+}
+
+bool DeviceModel::profile(const uint8_t* d_u8, int n, int k, int32_t* d_idx, float* d_prob,
+                          cudaStream_t st, std::vector<float>* ms, std::vector<std::string>* labels,
+                          std::string* err) {
+  if (n < 1 || n > mb_) { *err = "profile: batch must be within one micro-batch"; return false; }
+  B2I_CUDA(cudaSetDevice(device_));
+  std::vector<cudaEvent_t> evs(ops_.size() + 2);
+  for (auto& e : evs) B2I_CUDA(cudaEventCreate(&e));
+  prof_events_ = &evs;
+  const bool ok = run_microbatch(d_u8, n, k, d_idx, d_prob, nullptr, st, err);
+  prof_events_ = nullptr;
+  if (ok) {
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { *err = std::string("profile sync: ") + cudaGetErrorString(e); }
+    ms->assign(evs.size() - 1, 0.f);
+    for (size_t i = 0; i + 1 < evs.size(); ++i) cudaEventElapsedTime(&(*ms)[i], evs[i], evs[i + 1]);
+    *labels = op_names_;
+  }
+  for (auto& e : evs) cudaEventDestroy(e);
+  return ok;
 }
 
 bool DeviceModel::read_tensor(int id, int n, std::vector<float>* out, std::string* err) {

@@ -87,6 +87,10 @@ class DeviceModel {
   //   u8: [n,224,224,3]; idx/prob: [n,k]; logits: [n,classes] or null.
   bool forward(const uint8_t* d_u8, int n, int k, int32_t* d_idx, float* d_prob, float* d_logits,
                cudaStream_t st, std::string* err);
+  // One micro-batch with a CUDA-event pair around every launch: per-launch milliseconds, in
+  // execution order (ops..., softmax+top-k), plus a label per launch. Synchronises.
+  bool profile(const uint8_t* d_u8, int n, int k, int32_t* d_idx, float* d_prob, cudaStream_t st,
+               std::vector<float>* ms, std::vector<std::string>* labels, std::string* err);
   // Copy of an intermediate activation (debug / per-layer parity): tensor id -> fp32 NHWC host.
   bool read_tensor(int tensor_id, int n, std::vector<float>* out, std::string* err);
 
@@ -112,6 +116,8 @@ class DeviceModel {
   };
   bool run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_idx, float* d_prob,
                       float* d_logits, cudaStream_t st, std::string* err);
+  std::vector<cudaEvent_t>* prof_events_ = nullptr;  // when set, run_microbatch records after every launch
+  std::vector<std::string> op_names_;
 
   int device_ = -1;
   EngineConfig cfg_;

@@ -217,6 +217,14 @@ class Model:
         """Raw device pointers (ints) on GPU `dev`; enqueues on `stream` (cudaStream_t as int)."""
         check(_lib.lib().b2i_forward_device(self._h, dev, d_images, n, k, d_idx, d_prob, d_logits, stream))
 
+    def profile(self, d_images, n, k, d_idx, d_prob, stream=None, dev=0):
+        """[(launch name, milliseconds)] for one micro-batch, CUDA events around every launch."""
+        ms = np.zeros(256, np.float32)
+        names = ctypes.create_string_buffer(1 << 14)
+        cnt = check(_lib.lib().b2i_model_profile(self._h, dev, d_images, n, k, d_idx, d_prob, stream, _ptr(ms), 256,
+                                                 names, len(names)))
+        return list(zip(names.value.decode().splitlines(), ms[:cnt].tolist()))
+
     def num_tensors(self):
         return _lib.lib().b2i_model_num_tensors(self._h)
 

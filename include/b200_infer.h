@@ -110,6 +110,14 @@ int b2i_predict_u8_on(b2i_model* m, int first_dev, int n_dev, const uint8_t* ima
 int b2i_forward_device(b2i_model* m, int dev, const void* d_images_u8, int n, int k, void* d_idx,
                        void* d_prob, void* d_logits, void* cuda_stream);
 
+/* One forward over n <= micro_batch images on GPU `dev` with a CUDA-event pair around every kernel
+ * launch (events on `cuda_stream`). ms[i] = duration of launch i in execution order, labels_out =
+ * '\n'-separated launch names ("conv:layer1.0.conv1", "maxpool", ...). Returns the number of
+ * launches or a negative code. Used by bench.py for the per-kernel share of a step. */
+int b2i_model_profile(b2i_model* m, int dev, const void* d_images_u8, int n, int k, void* d_idx,
+                      void* d_prob, void* cuda_stream, float* ms, int cap, char* labels_out,
+                      size_t labels_cap);
+
 /* Resize + centre-crop of one decoded image, the first half of
  * imagenet::load_image_and_resize(path, 224, 224) (services.rs:492):
  * u8 [h][w][3] -> u8 [224][224][3] on the GPU `dev` of ctx. */
