@@ -303,7 +303,8 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   ec.max_batch = cfg.max_batch;
   ec.micro_batch = cfg.micro_batch;
   ec.alexnet_geometry = cfg.alexnet_geometry;
-  ec.conv_amode = cfg.conv_mode;
+  ec.conv_amode = cfg.conv_mode == 2 ? 1 : cfg.conv_mode;
+  ec.persistent = cfg.conv_mode == 2 ? 0 : 1;
   ec.b_tma = cfg.weights_tma;
   if (cfg.tile_n_max > 0) ec.bn_max = cfg.tile_n_max;
   ec.keep_tensors = cfg.keep_tensors;
@@ -545,7 +546,8 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   while (bnv > 32 && cs.Cout_pad % bnv) bnv -= 32;
   a.BN = bnv;
   a.stages = conv_umma_pick_stages(bnv);
-  a.amode = cs.smallc ? A_SMALLC : (conv_mode == 1 ? A_IM2COL : A_GATHER);
+  a.amode = cs.smallc ? A_SMALLC : (conv_mode >= 1 ? A_IM2COL : A_GATHER);
+  a.persistent = conv_mode == 2 ? 0 : 1;
   a.b_tma = (a.amode == A_IM2COL) ? 1 : weights_tma;
   if (!bf16) {
     CAPI_CUDA(launch_conv_fp32(a, nullptr));

@@ -29,19 +29,20 @@ struct ConvGeom {
 };
 
 struct ConvArgs {
-  ConvGeom g;
-  const void* x;        // bf16 NHWC (or [M][K] for A_TILED); fp32 in the fp32 kernel
-  const void* w;        // [Cout_pad][K]
-  const float* bias;    // [Cout_pad] folded BN shift / conv bias
-  const void* residual; // optional, same layout/dtype as out
-  void* out;            // [M][ldo]
-  int ldo;              // output row stride in elements
-  int relu;
-  int out_fp32;         // bf16 kernel only: write fp32 (logits)
-  int BN;               // tile N (multiple of 32, <= 256)
-  int stages;
-  int amode;
-  int b_tma;            // 1: weights through TMA, 0: cp.async gather (A_GATHER / A_SMALLC only)
+  ConvGeom g{};
+  const void* x = nullptr;        // bf16 NHWC (or [M][K] for A_TILED); fp32 in the fp32 kernel
+  const void* w = nullptr;        // [Cout_pad][K]
+  const float* bias = nullptr;    // [Cout_pad] folded BN shift / conv bias
+  const void* residual = nullptr; // optional, same layout/dtype as out
+  void* out = nullptr;            // [M][ldo]
+  int ldo = 0;                    // output row stride in elements
+  int relu = 0;
+  int out_fp32 = 0;               // bf16 kernel only: write fp32 (logits)
+  int BN = 128;                   // tile N (multiple of 32, <= 256)
+  int stages = 3;                 // one-tile-per-CTA kernel only; the persistent kernel sizes its own ring
+  int amode = A_GATHER;
+  int b_tma = 1;                  // 1: weights through TMA, 0: cp.async gather (A_GATHER / A_SMALLC only)
+  int persistent = 1;             // TMA modes: persistent CTA-per-SM kernel with double-buffered TMEM
 };
 
 // bf16 tcgen05 path.  tmA / tmB may be null when the corresponding operand is gathered.

@@ -29,7 +29,7 @@ constexpr int LAG = 2;  // cp.async groups kept in flight per gather thread (nee
 
 struct KP {
   int H, W, C, OH, OW, R, S, Sp, stride, pad;
-  int Cout, K, M, BN, stages, num_kb, tiles_n, ldo, relu, out_fp32;
+  int Cout, K, M, BN, stages, num_kb, tiles_n, tiles_m, ldo, relu, out_fp32;
   uint32_t tmem_cols;
   const __nv_bfloat16* x;
   const __nv_bfloat16* w;
@@ -37,6 +37,60 @@ struct KP {
   const __nv_bfloat16* residual;
   void* out;
 };
+
+
+// One output row x 32 consecutive channels: acc + bias (+ residual) -> ReLU -> store.
+__device__ __forceinline__ void epilogue_chunk(const KP& p, int m, int nb, const uint32_t (&v)[32]) {
+  float f[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + nb + j);
+  if (p.out_fp32) {
+    float* o = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+    if (nb + 32 <= p.Cout && (p.ldo & 3) == 0) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nb + j < p.Cout) o[j] = f[j];
+    }
+    return;
+  }
+  if (nb >= p.Cout) return;
+  const size_t off = static_cast<size_t>(m) * p.ldo + nb;
+  if (p.residual) {
+    const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint4 rv = __ldg(rp + q);
+      const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        f[q * 8 + e * 2] += bf16_lo(rr[e]);
+        f[q * 8 + e * 2 + 1] += bf16_hi(rr[e]);
+      }
+    }
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+  uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint4 ov;
+    ov.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
+    ov.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
+    ov.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
+    ov.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
+    op[q] = ov;
+  }
+}
 
 template <int AMODE, bool B_TMA>
 __global__ void __launch_bounds__(NTHREADS)
@@ -184,57 +238,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t v[32];
       tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
       tmem_ld_wait();
-      if (!row_ok) continue;
-      const int nb = n0 + c * 32;
-      float f[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + nb + j);
-      if (p.out_fp32) {
-        float* o = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        if (nb + 32 <= p.Cout && (p.ldo & 3) == 0) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.Cout) o[j] = f[j];
-        }
-      } else {
-        if (nb >= p.Cout) continue;
-        const size_t off = static_cast<size_t>(m) * p.ldo + nb;
-        if (p.residual) {
-          const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint4 rv = __ldg(rp + q);
-            const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              f[q * 8 + e * 2] += bf16_lo(rr[e]);
-              f[q * 8 + e * 2 + 1] += bf16_hi(rr[e]);
-            }
-          }
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 ov;
-          ov.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
-          ov.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
-          ov.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
-          ov.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
-          op[q] = ov;
-        }
-      }
+      if (row_ok) epilogue_chunk(p, m, n0 + c * 32, v);
     }
   } else if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
@@ -302,6 +306,208 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent variant for the TMA-fed modes: one CTA per SM walks a static round-robin list of
+// output tiles.  The TMA warp streams k-blocks of successive tiles through one shared-memory ring
+// without draining between tiles, the MMA thread alternates between two TMEM accumulators, and the
+// four epilogue warps drain accumulator (i & 1) while the tensor core fills the other one.
+//   warp 0: TMA producer   warp 1: TMEM alloc + MMA issue   warps 2-5: epilogue
+constexpr int PTHREADS = 192;
+
+template <int AMODE>
+__global__ void __launch_bounds__(PTHREADS, 1)
+conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
+                            const __grid_constant__ CUtensorMap tmB, const KP p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_tile_bytes = static_cast<uint32_t>(p.BN) * 128u;
+  const uint32_t stage_bytes = A_TILE_BYTES + b_tile_bytes;
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
+  auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + b); };
+  auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
+  const int total_tiles = p.tiles_m * p.tiles_n;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full_bar(b), 1);
+      mbar_init(acc_empty_bar(b), 4);  // one arrival per epilogue warp
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
+      const int ohw = p.OH * p.OW;
+      const uint32_t tx = b_tile_bytes + A_TILE_BYTES;
+      int s = 0, ph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m0 = (t / p.tiles_n) * BM;
+        const int n0 = (t % p.tiles_n) * p.BN;
+        int iw_base = 0, ih_base = 0, n_base = 0;
+        if (AMODE == A_IM2COL) {
+          n_base = m0 / ohw;
+          const int rem = m0 - n_base * ohw;
+          const int oh = rem / p.OW;
+          const int ow = rem - oh * p.OW;
+          ih_base = oh * p.stride - p.pad;
+          iw_base = ow * p.stride - p.pad;
+        }
+        int tap = 0, cblk = 0, r = 0, sx = 0;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(empty_bar(s), ph ^ 1);
+          const uint32_t a_s = smem_base + s * stage_bytes;
+          mbar_expect_tx(full_bar(s), tx);
+          if (AMODE == A_IM2COL) {
+            tma_load_im2col_4d(a_s, &tmA, full_bar(s), cblk << 6, iw_base, ih_base, n_base,
+                               static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
+            if (++cblk == cpb) {
+              cblk = 0;
+              ++tap;
+              if (++sx == p.S) { sx = 0; ++r; }
+            }
+          } else {
+            tma_load_2d(a_s, &tmA, full_bar(s), kb * BK, m0);
+          }
+          tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+        (void)tap;
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = umma_idesc_bf16(BM, p.BN);
+    int s = 0, ph = 0, i = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+      const int buf = i & 1;
+      mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(full_bar(s), ph);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_s = smem_base + s * stage_bytes;
+          const uint64_t adesc = umma_smem_desc_sw128(a_s);
+          const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(empty_bar(s));
+          if (kb == p.num_kb - 1) umma_commit(acc_full_bar(buf));
+        }
+        __syncwarp();
+        if (++s == p.stages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    const int n_chunks = p.BN >> 5;
+    int i = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+      const int buf = i & 1;
+      const int m0 = (t / p.tiles_n) * BM;
+      const int n0 = (t % p.tiles_n) * p.BN;
+      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
+      tc_fence_after();
+      const int m = m0 + q * 32 + lane;
+      const bool row_ok = m < p.M;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
+      for (int c = 0; c < n_chunks; ++c) {
+        uint32_t v[32];
+        tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+        tmem_ld_wait();
+        if (c == n_chunks - 1) {
+          // every lane's TMEM reads are complete: hand the accumulator back before the stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_empty_bar(buf));
+        }
+        if (row_ok) epilogue_chunk(p, m, n0 + c * 32, v);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+int persistent_stages(int BN) {
+  int s = (210 * 1024) / (A_TILE_BYTES + BN * 128);
+  if (s > MAX_STAGES) s = MAX_STAGES;
+  return s;
+}
+
+void fill_kp(KP* p, const ConvArgs& a) {
+  const ConvGeom& g = a.g;
+  p->H = g.H; p->W = g.W; p->C = g.C; p->OH = g.OH; p->OW = g.OW; p->R = g.R; p->S = g.S;
+  p->Sp = g.Sp; p->stride = g.stride; p->pad = g.pad; p->Cout = g.Cout; p->K = g.K; p->M = g.M;
+  p->BN = a.BN; p->stages = a.stages; p->num_kb = g.K / BK; p->tiles_n = g.Cout_pad / a.BN;
+  p->tiles_m = (g.M + BM - 1) / BM;
+  p->ldo = a.ldo; p->relu = a.relu; p->out_fp32 = a.out_fp32;
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(a.BN)) cols <<= 1;
+  p->tmem_cols = cols;
+  p->x = static_cast<const __nv_bfloat16*>(a.x);
+  p->w = static_cast<const __nv_bfloat16*>(a.w);
+  p->bias = a.bias;
+  p->residual = static_cast<const __nv_bfloat16*>(a.residual);
+  p->out = a.out;
+}
+
+template <int AMODE>
+cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
+                              cudaStream_t st) {
+  static bool attr_set[16] = {};
+  static int sm_count[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 16) return cudaErrorInvalidDevice;
+  auto kern = conv_umma_persistent_kernel<AMODE>;
+  if (!attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  KP p;
+  fill_kp(&p, a);
+  p.stages = persistent_stages(a.BN);
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;  // two accumulators
+  p.tmem_cols = cols;
+  const int total = p.tiles_m * p.tiles_n;
+  const int grid = total < sm_count[dev] ? total : sm_count[dev];
+  const size_t smem = conv_umma_smem_bytes(a.BN, p.stages);
+  kern<<<dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, p);
+  return cudaGetLastError();
+}
+
 template <int AMODE, bool B_TMA>
 cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
                      cudaStream_t st) {
@@ -315,21 +521,9 @@ cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMa
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  const ConvGeom& g = a.g;
   KP p;
-  p.H = g.H; p.W = g.W; p.C = g.C; p.OH = g.OH; p.OW = g.OW; p.R = g.R; p.S = g.S; p.Sp = g.Sp;
-  p.stride = g.stride; p.pad = g.pad; p.Cout = g.Cout; p.K = g.K; p.M = g.M; p.BN = a.BN;
-  p.stages = a.stages; p.num_kb = g.K / BK; p.tiles_n = g.Cout_pad / a.BN; p.ldo = a.ldo;
-  p.relu = a.relu; p.out_fp32 = a.out_fp32;
-  uint32_t cols = 32;
-  while (cols < static_cast<uint32_t>(a.BN)) cols <<= 1;
-  p.tmem_cols = cols;
-  p.x = static_cast<const __nv_bfloat16*>(a.x);
-  p.w = static_cast<const __nv_bfloat16*>(a.w);
-  p.bias = a.bias;
-  p.residual = static_cast<const __nv_bfloat16*>(a.residual);
-  p.out = a.out;
-  const int tiles_m = (g.M + BM - 1) / BM;
+  fill_kp(&p, a);
+  const int tiles_m = p.tiles_m;
   const size_t smem = conv_umma_smem_bytes(a.BN, a.stages);
   static const CUtensorMap dummy = {};
   kern<<<dim3(static_cast<unsigned>(tiles_m * p.tiles_n)), dim3(NTHREADS), smem, st>>>(
@@ -374,10 +568,12 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
                      : launch_t<A_SMALLC, false>(a, nullptr, nullptr, st);
     case A_IM2COL:
       if (g.C % 64 || g.K != g.R * g.S * g.C || !tmA || !tmB) return cudaErrorInvalidValue;
-      return launch_t<A_IM2COL, true>(a, tmA, tmB, st);
+      return a.persistent ? launch_persistent<A_IM2COL>(a, tmA, tmB, st)
+                          : launch_t<A_IM2COL, true>(a, tmA, tmB, st);
     case A_TILED:
       if (!tmA || !tmB) return cudaErrorInvalidValue;
-      return launch_t<A_TILED, true>(a, tmA, tmB, st);
+      return a.persistent ? launch_persistent<A_TILED>(a, tmA, tmB, st)
+                          : launch_t<A_TILED, true>(a, tmA, tmB, st);
   }
   return cudaErrorInvalidValue;
 }

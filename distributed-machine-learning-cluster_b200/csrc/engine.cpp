@@ -451,6 +451,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.stages = d.stages;
         a.amode = d.amode;
         a.b_tma = d.b_tma;
+        a.persistent = cfg_.persistent;
         if (cfg_.precision == PREC_FP32) {
           B2I_CUDA(launch_conv_fp32(a, st));
         } else {

@@ -29,6 +29,7 @@ struct EngineConfig {
   int conv_amode = -1;          // -1 auto (im2col TMA where C % 64 == 0), else AMode for those layers
   int b_tma = 1;                // weights through TMA
   int bn_max = 128;             // largest tile-N the planner may choose
+  int persistent = 1;           // TMA-fed layers: persistent kernel (0 = one tile per CTA)
   int keep_tensors = 0;         // 1: every activation gets its own buffer (per-layer parity tests)
 };
 

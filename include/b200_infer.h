@@ -44,7 +44,8 @@ typedef struct b2i_model_config {
   int max_batch;        /* largest n one predict call may pass PER GPU (buffers are sized for it) */
   int micro_batch;      /* images per kernel sequence, 0 = max_batch */
   int alexnet_geometry; /* B2I_ALEXNET_* */
-  int conv_mode;        /* -1 auto; 0 cp.async gather; 1 TMA im2col (bf16 path, C % 64 == 0 layers) */
+  int conv_mode;        /* bf16 path, C % 64 == 0 layers: -1 auto (= 1); 0 cp.async gather, one tile per CTA;
+                           1 TMA im2col, persistent kernel; 2 TMA im2col, one tile per CTA */
   int weights_tma;      /* 1: weight tiles through TMA (default), 0: cp.async (gather modes only) */
   int tile_n_max;       /* largest output-channel tile, multiple of 32 in [32,256]; 0 = default */
   int keep_tensors;     /* 1: no activation-buffer reuse, so b2i_model_read_tensor sees every layer */
@@ -147,7 +148,7 @@ int b2i_model_tensor_shape(const b2i_model* m, int tensor_id, int* h, int* w, in
 
 /* conv2d (+ optional eval-BatchNorm fold, bias, residual, ReLU). x: [N][H][W][C]; w: OIHW
  * [Cout][C][R][S]; bn: NULL or [4][Cout] = gamma, beta, running_mean, running_var; residual/out:
- * [N][OH][OW][Cout]. conv_mode: 0 gather, 1 TMA im2col (bf16, C % 64 == 0); C < 8 always uses the
+ * [N][OH][OW][Cout]. conv_mode as in b2i_model_config (0, 1 or 2); C <= 4 always uses the
  * small-channel gather. tile_n 0 = default. */
 int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weights_tma, int tile_n,
                   const float* x, int N, int H, int W, int C, const float* w, const float* bias,
