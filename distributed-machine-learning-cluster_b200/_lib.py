@@ -23,6 +23,7 @@ class ModelConfig(ctypes.Structure):
         ("weights_tma", ctypes.c_int),
         ("tile_n_max", ctypes.c_int),
         ("keep_tensors", ctypes.c_int),
+        ("fused_stem", ctypes.c_int),
     ]
 
 

@@ -242,6 +242,7 @@ void b2i_default_config(b2i_model_config* cfg) {
   cfg->weights_tma = 1;
   cfg->tile_n_max = 0;
   cfg->keep_tensors = 0;
+  cfg->fused_stem = 1;
 }
 
 int b2i_ot_inspect(const char* path, char* names_out, size_t cap) {
@@ -293,7 +294,8 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   std::string err;
   if (!read_ot_archive(ot_path, &tensors, &err)) return fail(B2I_EIO, err);
   NetSpec net;
-  const bool ok = name == "resnet18" ? build_resnet18(tensors, &net, &err)
+  const bool fused = cfg.fused_stem != 0 && cfg.precision == B2I_PREC_BF16;
+  const bool ok = name == "resnet18" ? build_resnet18(tensors, fused, &net, &err)
                                      : build_alexnet(tensors, cfg.alexnet_geometry, &net, &err);
   if (!ok) return fail(B2I_EIO, err);
   tensors.clear();
@@ -308,6 +310,7 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   ec.b_tma = cfg.weights_tma;
   if (cfg.tile_n_max > 0) ec.bn_max = cfg.tile_n_max;
   ec.keep_tensors = cfg.keep_tensors;
+  ec.fused_stem = fused ? 1 : 0;
 
   auto m = std::make_unique<b2i_model>();
   m->ctx = ctx;

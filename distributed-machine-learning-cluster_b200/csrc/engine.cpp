@@ -48,7 +48,7 @@ std::string shape_str(const HostTensor& h) {
 // conv (no bias) + BN, the ResNet building block
 bool add_conv_bn(const std::map<std::string, HostTensor>& t, const std::string& conv,
                  const std::string& bn, int Cout, int Cin, int k, int stride, int pad,
-                 NetSpec* net, std::string* err) {
+                 NetSpec* net, std::string* err, int s_pad = 0) {
   const HostTensor* w = find(t, conv + ".weight", err);
   const HostTensor* g = find(t, bn + ".weight", err);
   const HostTensor* b = find(t, bn + ".bias", err);
@@ -64,7 +64,7 @@ bool add_conv_bn(const std::map<std::string, HostTensor>& t, const std::string& 
     if (!shape_is(*p, {Cout})) { *err = bn + " parameter has shape " + shape_str(*p); return false; }
   net->convs.emplace_back();
   build_conv_spec(&net->convs.back(), conv, w->data.data(), nullptr, g->data.data(),
-                  b->data.data(), m->data.data(), v->data.data(), Cout, Cin, k, k, stride, pad);
+                  b->data.data(), m->data.data(), v->data.data(), Cout, Cin, k, k, stride, pad, 0, s_pad);
   return true;
 }
 
@@ -134,9 +134,9 @@ int push_pool(NetSpec* net, OpSpec::Kind kind, int in, int k, int stride, int pa
 
 void build_conv_spec(ConvSpec* cs, const std::string& name, const float* w, const float* bias,
                      const float* g, const float* b, const float* m, const float* v, int Cout,
-                     int Cin, int R, int S, int stride, int pad, int chw_c) {
+                     int Cin, int R, int S, int stride, int pad, int chw_c, int s_pad) {
   cs->name = name;
-  cs->Cin = Cin; cs->Cout = Cout; cs->R = R; cs->S = S; cs->Sp = S; cs->stride = stride;
+  cs->Cin = Cin; cs->Cout = Cout; cs->R = R; cs->S = S; cs->Sp = s_pad > S ? s_pad : S; cs->stride = stride;
   cs->pad = pad;
   cs->smallc = Cin <= 4;  // first layers (RGB): one 8-byte pixel per filter tap
   cs->Cin_pad = cs->smallc ? 4 : round_up(Cin, 64);
@@ -166,18 +166,31 @@ void build_conv_spec(ConvSpec* cs, const std::string& name, const float* w, cons
   }
 }
 
-bool build_resnet18(const std::map<std::string, HostTensor>& t, NetSpec* net, std::string* err) {
+bool build_resnet18(const std::map<std::string, HostTensor>& t, bool fused_stem, NetSpec* net,
+                    std::string* err) {
   net->model = "resnet18";
-  const int in0 = new_tensor(net, 224, 224, 4);
-  {
+  int cur;
+  if (fused_stem) {
+    // conv1 weights in the stem kernel's K order: (r, s padded to 8, c padded to 4) = 224 -> 256
+    if (!add_conv_bn(t, "conv1", "bn1", 64, 3, 7, 2, 3, net, err, /*s_pad=*/8)) return false;
+    OpSpec op;
+    op.kind = OpSpec::STEM;
+    op.conv = 0;
+    op.relu = true;
+    op.out = new_tensor(net, 56, 56, 64);
+    net->ops.push_back(op);
+    net->flops_per_image += 2.0 * 112 * 112 * 64 * 3 * 49;
+    cur = op.out;
+  } else {
+    const int in0 = new_tensor(net, 224, 224, 4);
     OpSpec op;
     op.kind = OpSpec::NORMALIZE;
     op.out = in0;
     net->ops.push_back(op);
+    if (!add_conv_bn(t, "conv1", "bn1", 64, 3, 7, 2, 3, net, err)) return false;
+    cur = push_conv(net, 0, in0, -1, true);
+    cur = push_pool(net, OpSpec::MAXPOOL, cur, 3, 2, 1, 56, 56);
   }
-  if (!add_conv_bn(t, "conv1", "bn1", 64, 3, 7, 2, 3, net, err)) return false;
-  int cur = push_conv(net, 0, in0, -1, true);
-  cur = push_pool(net, OpSpec::MAXPOOL, cur, 3, 2, 1, 56, 56);
   int cin = 64;
   const int widths[4] = {64, 128, 256, 512};
   for (int L = 0; L < 4; ++L) {
@@ -328,6 +341,24 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
   for (const OpSpec& o : net.ops) {
     DevOp d;
     d.spec = o;
+    if (o.kind == OpSpec::STEM) {
+      const ConvSpec& c = net.convs[o.conv];
+      if (cfg_.precision != PREC_BF16 || c.K != 256 || c.Cout != 64) { *err = "fused stem needs the bf16 path and conv1 as [64][256]"; return false; }
+      std::vector<uint16_t> wb(c.w.size());
+      for (size_t i = 0; i < wb.size(); ++i) wb[i] = f32_to_bf16_rne(c.w[i]);
+      B2I_CUDA(cudaMalloc(&d.w, wb.size() * 2));
+      B2I_CUDA(cudaMemcpy(d.w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
+      owned_.push_back(d.w);
+      weight_bytes_ += wb.size() * 2;
+      void* bp = nullptr;
+      B2I_CUDA(cudaMalloc(&bp, c.bias.size() * 4));
+      B2I_CUDA(cudaMemcpy(bp, c.bias.data(), c.bias.size() * 4, cudaMemcpyHostToDevice));
+      owned_.push_back(bp);
+      d.bias = static_cast<float*>(bp);
+      const char* terr = "";
+      if (make_tmap_weights(&d.tmB, d.w, 64, 256, 64, &terr)) { *err = std::string("stem: ") + terr; return false; }
+      d.has_tmB = true;
+    }
     if (o.kind == OpSpec::CONV) {
       const ConvSpec& c = net.convs[o.conv];
       const TensorShape ti = tshape_[o.in], to = tshape_[o.out];
@@ -398,6 +429,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
     ops_.push_back(d);
     switch (o.kind) {
       case OpSpec::NORMALIZE: op_names_.push_back("normalize"); break;
+      case OpSpec::STEM: op_names_.push_back("conv:stem(normalize+conv1+maxpool)"); break;
       case OpSpec::MAXPOOL: op_names_.push_back("maxpool"); break;
       case OpSpec::AVGPOOL: op_names_.push_back("avgpool"); break;
       case OpSpec::CONV: op_names_.push_back((o.fc ? "fc:" : "conv:") + net.convs[o.conv].name); break;
@@ -419,6 +451,9 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
   for (DevOp& d : ops_) {
     const OpSpec& o = d.spec;
     switch (o.kind) {
+      case OpSpec::STEM:
+        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias, nb, st));
+        break;
       case OpSpec::NORMALIZE:
         B2I_CUDA(launch_normalize_u8(d_u8, buf(o.out), dt, static_cast<long long>(nb) * 224 * 224, st));
         break;

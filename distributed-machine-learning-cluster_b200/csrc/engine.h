@@ -28,7 +28,8 @@ struct EngineConfig {
   int alexnet_geometry = ALEX_TCH;
   int conv_amode = -1;          // -1 auto (im2col TMA where C % 64 == 0), else AMode for those layers
   int b_tma = 1;                // weights through TMA
-  int bn_max = 128;             // largest tile-N the planner may choose
+  int bn_max = 256;             // largest tile-N the planner may choose
+  int fused_stem = 1;           // ResNet bf16: normalise + conv1 + max-pool as one kernel
   int persistent = 1;           // TMA-fed layers: persistent kernel (0 = one tile per CTA)
   int keep_tensors = 0;         // 1: every activation gets its own buffer (per-layer parity tests)
 };
@@ -49,12 +50,12 @@ struct ConvSpec {
 void build_conv_spec(ConvSpec* cs, const std::string& name, const float* w_oihw, const float* bias,
                      const float* bn_gamma, const float* bn_beta, const float* bn_mean,
                      const float* bn_var, int Cout, int Cin, int R, int S, int stride, int pad,
-                     int chw_to_hwc_channels = 0);
+                     int chw_to_hwc_channels = 0, int s_pad = 0);
 
 struct TensorShape { int H = 0, W = 0, C = 0; size_t elems() const { return size_t(H) * W * C; } };
 
 struct OpSpec {
-  enum Kind { NORMALIZE, CONV, MAXPOOL, AVGPOOL } kind = CONV;
+  enum Kind { NORMALIZE, CONV, MAXPOOL, AVGPOOL, STEM } kind = CONV;
   int in = -1, out = -1, res = -1;  // activation tensor ids
   int conv = -1;                    // index into NetSpec::convs
   bool relu = false, fc = false, logits = false;
@@ -71,7 +72,8 @@ struct NetSpec {
   double flops_per_image = 0;        // 2 * MACs of conv + FC, no padding counted
 };
 
-bool build_resnet18(const std::map<std::string, HostTensor>& t, NetSpec* net, std::string* err);
+bool build_resnet18(const std::map<std::string, HostTensor>& t, bool fused_stem, NetSpec* net,
+                    std::string* err);
 bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, NetSpec* net,
                    std::string* err);
 

@@ -49,6 +49,7 @@ typedef struct b2i_model_config {
   int weights_tma;      /* 1: weight tiles through TMA (default), 0: cp.async (gather modes only) */
   int tile_n_max;       /* largest output-channel tile, multiple of 32 in [32,256]; 0 = default */
   int keep_tensors;     /* 1: no activation-buffer reuse, so b2i_model_read_tensor sees every layer */
+  int fused_stem;       /* ResNet-18 bf16: 1 (default) = normalise + conv1 + max-pool in one kernel, 0 = three */
 } b2i_model_config;
 
 /* Thread-local description of the last failure on the calling thread. Never NULL. */

@@ -83,7 +83,8 @@ def test_resnet18_per_layer_parity_bf16(pkg, ctx, resnet18_ot, conv_mode):
     taps = []
     with torch.no_grad():
         tch_oracle.resnet18_forward(w, tch_oracle.normalize_u8(img), taps)
-    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=3, keep_tensors=True, conv_mode=conv_mode) as m:
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=3, keep_tensors=True, conv_mode=conv_mode,
+                   fused_stem=False) as m:
         m.predict_u8(img, k=5)
         shapes = [m.tensor_shape(t) for t in range(m.num_tensors())]
         # tensors in execution order: 0 input, 1 conv1, 2 maxpool, then per block (downsample?), conv1, conv2
@@ -105,6 +106,32 @@ def test_resnet18_per_layer_parity_bf16(pkg, ctx, resnet18_ot, conv_mode):
         worst = max(worst, rel)
         assert rel < 0.03, name
     assert worst > 0  # the comparison really ran
+
+
+def test_fused_stem_matches_unfused_and_oracle(pkg, ctx, resnet18_ot):
+    """normalise + conv1 + bn1 + relu + max-pool as ONE kernel: its pooled map against the oracle's
+    max-pool output and against the three-kernel path (same roundings, different K order)."""
+    from oracle import synth, tch_oracle
+    img = synth.synthetic_images(5, seed=8)
+    img[0, :7] = 0
+    img[1, :, -9:] = 255   # saturated borders exercise the zero-padding edges
+    taps = []
+    with torch.no_grad():
+        tch_oracle.resnet18_forward(synth.resnet18_weights(), tch_oracle.normalize_u8(img), taps)
+    ref = dict(taps)["maxpool"].permute(0, 2, 3, 1).numpy()
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=5, keep_tensors=True, fused_stem=True) as m:
+        _, _, lg_f = m.predict_u8(img, k=5, want_logits=True)
+        assert m.tensor_shape(0) == (56, 56, 64)
+        fused = m.read_tensor(0, 5)
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=5, keep_tensors=True, fused_stem=False) as m:
+        _, _, lg_u = m.predict_u8(img, k=5, want_logits=True)
+        unfused = m.read_tensor(2, 5)
+    scale = float(np.abs(ref).max())
+    print("stem: fused vs oracle %.4f, unfused vs oracle %.4f, fused vs unfused %.4f (of scale %.2f)" % (
+        np.abs(fused - ref).max() / scale, np.abs(unfused - ref).max() / scale, np.abs(fused - unfused).max() / scale, scale))
+    assert np.abs(fused - ref).max() <= 0.01 * scale
+    assert np.abs(fused - unfused).max() <= 2.0 ** -7 * scale      # at most one bf16 ulp flip at the top of the range
+    assert np.abs(lg_f - lg_u).max() <= tol_for(BF16, lg_u)
 
 
 def test_batch_shapes_ragged_empty_single(pkg, ctx, resnet18_ot):
