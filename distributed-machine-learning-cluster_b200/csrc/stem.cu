@@ -8,14 +8,18 @@
 // writes the 401 KB pooled map.
 //
 // One CTA (two co-resident per SM) produces a 7x7 pooled tile = a 15x15 patch of conv outputs
-// (1 halo row/column, recomputed), held as M = 256 GEMM rows (15 rows x 16 slots):
-//   P1  256 threads stage the 36x40-pixel input patch in shared memory as normalised bf16x4 pixels
-//   P2  each thread builds its im2col row for one 64-wide K block (2 filter rows x 8 taps x 4 ch)
-//       straight into the 128B-swizzled UMMA layout; 2-stage ring, mbarrier hand-off to the MMA warp
-//   MMA warp 8: 4 K blocks x 4 x (two M=128 halves) tcgen05.mma, N = 64, fp32 accumulators in TMEM
-//   P3  TMEM -> registers -> +bias, ReLU, bf16 -> shared staging tile
-//   P4  3x3/s2 max over the staging tile -> coalesced 16-byte stores of the pooled tile
-// Weights ([64][256] bf16, K order (r, s<8, c<4)) are loaded once per CTA by TMA.
+// (1 halo row/column, recomputed), computed as two M=128 MMAs (16 conv rows x 8 conv columns each):
+//   load   256 threads stage the 37x40-pixel input patch in shared memory as normalised bf16x4
+//          pixels (8 bytes), double buffered: the patch of tile i+1 is fetched while tile i computes
+//   MMA    warp 8 issues 2 x 14 tcgen05.mma (K = 16 = four taps each) whose A descriptors point
+//          STRAIGHT INTO THE PATCH: with 8-byte pixels and stride 2, the tap window of the next conv
+//          pixel starts 16 bytes further, which is exactly the canonical no-swizzle K-major core
+//          matrix (8 rows x 16 B); the next conv row is 640 B further (SBO), the next two taps 16 B
+//          (LBO), the next filter row 320 B (new descriptor).  No im2col matrix is ever materialised.
+//   drain  TMEM -> registers -> +bias, ReLU, bf16 -> shared staging tile (TMEM double buffered)
+//   pool   3x3/s2 max over the staging tile -> 16-byte stores of the pooled tile
+// Weights ([64][256] bf16, K order (r, s<8, c<4), rows r = 7 / taps s = 7 / channel 3 are zero) are
+// loaded once per CTA by TMA into the 128B-swizzled layout.
 #include "conv.h"
 #include "ops.h"
 #include "ptx.cuh"
@@ -25,13 +29,13 @@ namespace {
 
 constexpr int ST_BUILDERS = 256;
 constexpr int ST_THREADS = ST_BUILDERS + 32;
-constexpr int PATCH_H = 36, PATCH_W = 40;          // pixels of 8 bytes
-constexpr uint32_t A_STAGE_BYTES = 256 * 128;      // 256 rows x 64 bf16
-constexpr uint32_t A_RING_BYTES = 2 * A_STAGE_BYTES;
-constexpr uint32_t B_BYTES = 4 * 64 * 128;         // 4 K blocks x 64 out channels x 64 bf16
-constexpr uint32_t PATCH_BYTES = PATCH_H * PATCH_W * 8;
-constexpr uint32_t STEM_SMEM = A_RING_BYTES + B_BYTES + PATCH_BYTES + 1024;
-constexpr uint32_t TMEM_COLS = 128;                // two 128x64 fp32 accumulators
+constexpr int PATCH_H = 37, PATCH_W = 40;          // pixels of 8 bytes (bf16 r, g, b, 0)
+constexpr uint32_t PATCH_ROW_BYTES = PATCH_W * 8;  // 320
+constexpr uint32_t PATCH_BYTES = ((PATCH_H * PATCH_W * 8 + 127) / 128) * 128;
+constexpr uint32_t B_BYTES = 4 * 64 * 128;         // 4 K blocks x 64 out channels x 64 bf16, 128B swizzle
+constexpr uint32_t STAGE_BYTES = 256 * 128;        // conv outputs of one tile, bf16 [15x16 slots][64]
+constexpr uint32_t STEM_SMEM = B_BYTES + STAGE_BYTES + 2 * PATCH_BYTES + 1024;
+constexpr uint32_t TMEM_COLS = 256;                // 2 tiles in flight x two 128x64 fp32 accumulators
 
 struct StemParams {
   const uint8_t* in;
@@ -40,10 +44,22 @@ struct StemParams {
   int total_tiles;  // N * 64
 };
 
+// A-operand descriptor over the RAW patch (no swizzle, K-major): row i of an 8-row core matrix is
+// the next conv pixel along x = the next 16 bytes; 8-row groups (next conv row) are 2 patch rows
+// = 640 bytes apart; the next 16-byte K chunk (two more taps) is 16 bytes further.
+__device__ __forceinline__ uint64_t patch_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(16 >> 4) << 16;                      // leading (K) byte offset
+  d |= static_cast<uint64_t>((2 * PATCH_ROW_BYTES) >> 4) << 32;   // stride (M group) byte offset
+  d |= static_cast<uint64_t>(1) << 46;
+  return d;                                                        // layout type 0: no swizzle
+}
+
 __global__ void __launch_bounds__(ST_THREADS, 2)
 stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[6];  // full[2], empty[2], acc_full, w_full
+  __shared__ __align__(8) uint64_t bars[7];  // patch_full[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
   __shared__ float lut[3][256];               // (u/255 - mean)/std per channel, exact fp32 ops
 
@@ -51,22 +67,21 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   const int warp = tid >> 5;
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_ring = base;
-  const uint32_t b_smem = base + A_RING_BYTES;
-  const uint32_t patch = b_smem + B_BYTES;
-  uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));  // generic pointer to `base`
+  const uint32_t b_smem = base;
+  const uint32_t stage = base + B_BYTES;
+  const uint32_t patch0 = stage + STAGE_BYTES;
   const uint32_t bar0 = smem_u32(bars);
-  auto full_bar = [&](int s) { return bar0 + 8u * s; };
-  auto empty_bar = [&](int s) { return bar0 + 8u * (2 + s); };
-  const uint32_t acc_full = bar0 + 8u * 4;
-  const uint32_t w_full = bar0 + 8u * 5;
+  auto patch_full = [&](int b) { return bar0 + 8u * b; };
+  auto acc_full = [&](int b) { return bar0 + 8u * (2 + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (4 + b); };
+  const uint32_t w_full = bar0 + 8u * 6;
 
   if (tid == 0) {
-    mbar_init(full_bar(0), ST_BUILDERS);
-    mbar_init(full_bar(1), ST_BUILDERS);
-    mbar_init(empty_bar(0), 1);
-    mbar_init(empty_bar(1), 1);
-    mbar_init(acc_full, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(patch_full(b), ST_BUILDERS);
+      mbar_init(acc_full(b), 1);
+      mbar_init(acc_empty(b), 8);
+    }
     mbar_init(w_full, 1);
     mbar_fence_init();
   }
@@ -92,93 +107,106 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     }
     __syncwarp();
     const uint32_t idesc = umma_idesc_bf16(128, 64);
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-      for (int kb = 0; kb < 4; ++kb) {
-        const int s = kb & 1;
-        mbar_wait(full_bar(s), (kb >> 1) & 1);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_s = a_ring + s * A_STAGE_BYTES;
-          const uint64_t bdesc = umma_smem_desc_sw128(b_smem + kb * 8192u);
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint64_t adesc = umma_smem_desc_sw128(a_s + h * 16384u);
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_bf16(tmem_base + h * 64u, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(empty_bar(s));
-          if (kb == 3) umma_commit(acc_full);
-        }
-        __syncwarp();
-      }
-    }
-  } else {
-    // ------------------------------------------------------------------ builders / epilogue
-    const int m = tid;                 // GEMM row: conv pixel (ly, lx) = (m / 16, m % 16)
-    const int ly = (m >> 4) < 15 ? (m >> 4) : 14;  // slots 240..255 are padding rows: read row 14 again
-    const int lx = m & 15;
-    const uint32_t swz_row = static_cast<uint32_t>(m & 7);
-    const int h = warp >> 2, q = warp & 3;
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
-      const int n = t >> 6;
-      const int pty = (t >> 3) & 7, ptx = t & 7;
-      const int oh0 = 14 * pty - 1, ow0 = 14 * ptx - 1;   // first conv row / col of the patch
-      const int ih0 = 2 * oh0 - 3, iw0 = 2 * ow0 - 3;     // first input row / col
-      // P1: input patch -> normalised bf16x4 pixels (zero outside the image = conv zero padding)
-      const uint8_t* img = p.in + static_cast<size_t>(n) * (224 * 224 * 3);
-      for (int e = tid; e < PATCH_H * PATCH_W; e += ST_BUILDERS) {
-        const int py = e / PATCH_W, px = e - py * PATCH_W;
-        const int ih = ih0 + py, iw = iw0 + px;
-        uint2 v = make_uint2(0u, 0u);
-        if (ih >= 0 && ih < 224 && iw >= 0 && iw < 224) {
-          const uint8_t* s3 = img + (ih * 224 + iw) * 3;
-          v.x = pack_bf16x2(lut[0][__ldg(s3)], lut[1][__ldg(s3 + 1)]);
-          v.y = pack_bf16x2(lut[2][__ldg(s3 + 2)], 0.f);
-        }
-        *reinterpret_cast<uint2*>(gen_base + A_RING_BYTES + B_BYTES + e * 8) = v;
-      }
-      asm volatile("bar.sync 1, %0;" ::"n"(ST_BUILDERS) : "memory");
-      // P2: im2col rows, one 64-wide K block (filter rows 2kb, 2kb+1) per ring stage
-      for (int kb = 0; kb < 4; ++kb) {
-        const int s = kb & 1;
-        mbar_wait(empty_bar(s), ((kb >> 1) & 1) ^ 1);
-        const uint32_t dst_row = a_ring + s * A_STAGE_BYTES + static_cast<uint32_t>(m) * 128u;
-        const int nchunks = kb == 3 ? 4 : 8;  // filter row 7 does not exist: its weights are zero
+      const int b = i & 1;
+      mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
+      mbar_wait(patch_full(b), (i >> 1) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t pbase = patch0 + b * PATCH_BYTES;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (j < nchunks) {
-            const int r = 2 * kb + (j >> 2);
-            const uint32_t src = patch + static_cast<uint32_t>(((2 * ly + r) * PATCH_W + 2 * lx + 2 * (j & 3)) * 8);
-            uint32_t x0, x1, x2, x3;
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(src));
-            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(dst_row + ((static_cast<uint32_t>(j) ^ swz_row) << 4)),
-                         "r"(x0), "r"(x1), "r"(x2), "r"(x3) : "memory");
+        for (int h = 0; h < 2; ++h) {          // conv columns 0-7 / 8-15 of the 16x16 patch
+          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + h * 64);
+#pragma unroll
+          for (int j = 0; j < 14; ++j) {        // K step j: filter row j/2, taps 4*(j&1) .. +3
+            const uint32_t a_addr = pbase + static_cast<uint32_t>(h * 128 + (j >> 1) * PATCH_ROW_BYTES + (j & 1) * 32);
+            const uint64_t bdesc = umma_smem_desc_sw128(b_smem + (j >> 2) * 8192u) + 2u * (j & 3);
+            umma_bf16(d_tmem, patch_desc(a_addr), bdesc, idesc, j != 0 ? 1u : 0u);
           }
         }
-        fence_proxy_async_smem();
-        mbar_arrive(full_bar(s));
+        umma_commit(acc_full(b));
       }
-      // P3: accumulators -> +bias, ReLU, bf16 -> staging tile (aliases the A ring; all MMAs are done)
-      mbar_wait(acc_full, i & 1);
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------------ patch loaders / epilogue
+    const int h = warp >> 2, q = warp & 3;
+    uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));  // generic pointer to `base`
+
+    auto load_patch = [&](int t, int b) {
+      const int n = t >> 6;
+      const int pty = (t >> 3) & 7, ptx = t & 7;
+      const int ih0 = 28 * pty - 5, iw0 = 28 * ptx - 5;   // input row / col of patch pixel (0, 0)
+      const uint8_t* img = p.in + static_cast<size_t>(n) * (224 * 224 * 3);
+      constexpr int ROUNDS = (PATCH_H * PATCH_W + ST_BUILDERS - 1) / ST_BUILDERS;
+      uint32_t r0[ROUNDS], r1[ROUNDS], r2[ROUNDS];
+#pragma unroll
+      for (int k = 0; k < ROUNDS; ++k) {       // all global loads first: one exposed latency
+        const int e = tid + k * ST_BUILDERS;
+        const int py = e / PATCH_W, px = e - py * PATCH_W;
+        const int ih = ih0 + py, iw = iw0 + px;
+        r0[k] = 0xFFFFFFFFu;
+        r1[k] = r2[k] = 0;
+        if (e < PATCH_H * PATCH_W && ih >= 0 && ih < 224 && iw >= 0 && iw < 224) {
+          const uint8_t* s3 = img + (ih * 224 + iw) * 3;
+          r0[k] = __ldg(s3);
+          r1[k] = __ldg(s3 + 1);
+          r2[k] = __ldg(s3 + 2);
+        }
+      }
+      uint8_t* dst = gen_base + B_BYTES + STAGE_BYTES + b * PATCH_BYTES;
+#pragma unroll
+      for (int k = 0; k < ROUNDS; ++k) {
+        const int e = tid + k * ST_BUILDERS;
+        if (e < PATCH_H * PATCH_W) {
+          uint2 v = make_uint2(0u, 0u);        // outside the image: the conv's zero padding
+          if (r0[k] != 0xFFFFFFFFu) {
+            v.x = pack_bf16x2(lut[0][r0[k]], lut[1][r1[k]]);
+            v.y = pack_bf16x2(lut[2][r2[k]], 0.f);
+          }
+          *reinterpret_cast<uint2*>(dst + e * 8) = v;
+        }
+      }
+      fence_proxy_async_smem();                // generic-proxy stores -> visible to the tensor core
+      mbar_arrive(patch_full(b));
+    };
+
+    int i = 0;
+    if (static_cast<int>(blockIdx.x) < p.total_tiles) load_patch(blockIdx.x, 0);
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+      const int b = i & 1;
+      const int n = t >> 6;
+      const int pty = (t >> 3) & 7, ptx = t & 7;
+      const int oh0 = 14 * pty - 1, ow0 = 14 * ptx - 1;   // conv row / col of patch slot (0, 0)
+      // the MMAs of tile i-1 (which read the other patch buffer) finished before its acc_full,
+      // which these threads waited on last iteration: that buffer may be overwritten now
+      if (t + static_cast<int>(gridDim.x) < p.total_tiles) load_patch(t + gridDim.x, b ^ 1);
+
+      // accumulators -> +bias, ReLU, bf16 -> staging tile [ly*16 + lx][64], 16-byte chunks XOR-swizzled
+      mbar_wait(acc_full(b), (i >> 1) & 1);
       tc_fence_after();
       {
-        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(h * 64);
-        const int row = h * 128 + q * 32 + lane;
-        const uint32_t st_row = a_ring + static_cast<uint32_t>(row) * 128u;
-        const uint32_t sw = static_cast<uint32_t>(row & 7);
+        const int mrow = q * 32 + lane;                    // row inside this half's 128-row MMA
+        const int srow = (mrow >> 3) * 16 + h * 8 + (mrow & 7);
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 128 + h * 64);
+        const uint32_t st_row = stage + static_cast<uint32_t>(srow) * 128u;
+        const uint32_t sw = static_cast<uint32_t>(srow & 7);
+        uint32_t v0[32], v1[32];
+        tmem_ld32(t_row, v0);
+        tmem_ld32(t_row + 32u, v1);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty(b));          // TMEM buffer free for tile i+2
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-          uint32_t v[32];
-          tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
-          tmem_ld_wait();
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float f[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e)
-              f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + __ldg(p.bias + c * 32 + g * 8 + e), 0.f);
+              f[e] = fmaxf(__uint_as_float(c == 0 ? v0[g * 8 + e] : v1[g * 8 + e]) + __ldg(p.bias + c * 32 + g * 8 + e), 0.f);
             const uint32_t chunk = static_cast<uint32_t>(c * 4 + g);
             asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_row + ((chunk ^ sw) << 4)),
                          "r"(pack_bf16x2(f[0], f[1])), "r"(pack_bf16x2(f[2], f[3])),
@@ -186,15 +214,14 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
           }
         }
       }
-      tc_fence_before();
       asm volatile("bar.sync 1, %0;" ::"n"(ST_BUILDERS) : "memory");
-      // P4: 3x3 stride-2 max over the staging tile -> pooled 7x7x64
-      for (int item = tid; item < 49 * 8; item += ST_BUILDERS) {
-        const int pp = item >> 3, c8 = item & 7;
+      // 3x3 stride-2 max over the staging tile -> pooled 7x7x64, two 16-byte chunks per thread
+      if (tid < 49 * 4) {
+        const int pp = tid >> 2, c8 = (tid & 3) * 2;
         const int py = pp / 7, px = pp - py * 7;
-        float mx[8];
+        float mx[16];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) mx[e] = 0.f;  // post-ReLU values are >= 0 and the centre tap is always valid
+        for (int e = 0; e < 16; ++e) mx[e] = 0.f;  // post-ReLU values are >= 0 and the centre tap is always valid
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy) {
           const int cy = 2 * py + dy;
@@ -206,27 +233,28 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
             const int ow = ow0 + cx;
             if (ow < 0 || ow >= 112) continue;
             const int row = cy * 16 + cx;
-            const uint32_t a = a_ring + static_cast<uint32_t>(row) * 128u + ((static_cast<uint32_t>(c8) ^ (row & 7)) << 4);
-            uint32_t x0, x1, x2, x3;
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(a));
-            const uint32_t xs[4] = {x0, x1, x2, x3};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              mx[2 * e] = fmaxf(mx[2 * e], bf16_lo(xs[e]));
-              mx[2 * e + 1] = fmaxf(mx[2 * e + 1], bf16_hi(xs[e]));
+            for (int cc = 0; cc < 2; ++cc) {
+              const uint32_t a = stage + static_cast<uint32_t>(row) * 128u + ((static_cast<uint32_t>(c8 + cc) ^ (row & 7)) << 4);
+              uint32_t x0, x1, x2, x3;
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(a));
+              const uint32_t xs[4] = {x0, x1, x2, x3};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                mx[cc * 8 + 2 * e] = fmaxf(mx[cc * 8 + 2 * e], bf16_lo(xs[e]));
+                mx[cc * 8 + 2 * e + 1] = fmaxf(mx[cc * 8 + 2 * e + 1], bf16_hi(xs[e]));
+              }
             }
           }
         }
         const int ph = pty * 7 + py, pw = ptx * 7 + px;
-        uint4 o;
-        o.x = pack_bf16x2(mx[0], mx[1]);
-        o.y = pack_bf16x2(mx[2], mx[3]);
-        o.z = pack_bf16x2(mx[4], mx[5]);
-        o.w = pack_bf16x2(mx[6], mx[7]);
-        *reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + c8 * 8) = o;
+        uint4* o = reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + c8 * 8);
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc)
+          o[cc] = make_uint4(pack_bf16x2(mx[cc * 8 + 0], mx[cc * 8 + 1]), pack_bf16x2(mx[cc * 8 + 2], mx[cc * 8 + 3]),
+                             pack_bf16x2(mx[cc * 8 + 4], mx[cc * 8 + 5]), pack_bf16x2(mx[cc * 8 + 6], mx[cc * 8 + 7]));
       }
-      // the staging tile (= ring stage 0/1) and the patch are rewritten by the next tile
-      asm volatile("bar.sync 1, %0;" ::"n"(ST_BUILDERS) : "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(ST_BUILDERS) : "memory");  // staging tile is rewritten next iteration
     }
   }
 
