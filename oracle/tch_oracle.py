@@ -104,3 +104,59 @@ def predict_u8(model_name, w, images_u8, k=5, alexnet_geometry="tch", batch=64):
     logits = torch.cat(outs) if outs else torch.zeros(0, 1000)
     idx, prob = softmax_topk(logits, k)
     return idx.numpy(), prob.numpy(), logits.numpy()
+
+
+# ---------------------------------------------------------------------------------------------
+# bf16 evaluation of the same graphs: what the reference's arithmetic becomes when weights (after
+# the BatchNorm fold) and every stored activation are rounded to bf16 while sums stay fp32.  Used by
+# the GPU tests to separate "the kernel computes what it should" (tight bound against this) from
+# "bf16 storage costs this much against the fp32 reference" (the gap of this function itself).
+def _q(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def _fold(w, conv, bn):
+    inv = 1.0 / torch.sqrt(w[bn + ".running_var"].double() + BN_EPS)
+    scale = (w[bn + ".weight"].double() * inv)
+    wf = w[conv + ".weight"] * scale.float().view(-1, 1, 1, 1)
+    shift = (w[bn + ".bias"].double() - w[bn + ".running_mean"].double() * scale).float()
+    return _q(wf), shift
+
+
+def resnet18_forward_bf16(w, images_u8):
+    x = _q(normalize_u8(images_u8))
+    wf, b = _fold(w, "conv1", "bn1")
+    x = _q(F.relu(F.conv2d(x, wf, b, 2, 3)))
+    x = F.max_pool2d(x, 3, 2, 1)
+    cin = 64
+    for L, cout in enumerate((64, 128, 256, 512), start=1):
+        for B in range(2):
+            p = "layer%d.%d" % (L, B)
+            stride = 2 if (L > 1 and B == 0) else 1
+            idn = x
+            if stride != 1 or cin != cout:
+                wd, bd = _fold(w, p + ".downsample.0", p + ".downsample.1")
+                idn = _q(F.conv2d(x, wd, bd, stride, 0))
+            wa, ba = _fold(w, p + ".conv1", p + ".bn1")
+            t = _q(F.relu(F.conv2d(x, wa, ba, stride, 1)))
+            wb, bb = _fold(w, p + ".conv2", p + ".bn2")
+            x = _q(F.relu(F.conv2d(t, wb, bb, 1, 1) + idn))
+            cin = cout
+    x = _q(F.adaptive_avg_pool2d(x, (1, 1))).flatten(1)
+    return F.linear(x, _q(w["fc.weight"]), w["fc.bias"])
+
+
+def alexnet_forward_bf16(w, images_u8, geometry="tch"):
+    p3, s3 = (1, 2) if geometry == "tch" else (2, 1)
+    x = _q(normalize_u8(images_u8))
+    x = F.max_pool2d(_q(F.relu(F.conv2d(x, _q(w["features.0.weight"]), w["features.0.bias"], 4, 2))), 3, 2)
+    x = F.max_pool2d(_q(F.relu(F.conv2d(x, _q(w["features.3.weight"]), w["features.3.bias"], s3, p3))), 3, 2)
+    x = _q(F.relu(F.conv2d(x, _q(w["features.6.weight"]), w["features.6.bias"], 1, 1)))
+    x = _q(F.relu(F.conv2d(x, _q(w["features.8.weight"]), w["features.8.bias"], 1, 1)))
+    x = F.max_pool2d(_q(F.relu(F.conv2d(x, _q(w["features.10.weight"]), w["features.10.bias"], 1, 1))), 3, 2)
+    if x.shape[-1] != 6:
+        x = _q(F.adaptive_avg_pool2d(x, (6, 6)))
+    x = x.flatten(1)
+    x = _q(F.relu(F.linear(x, _q(w["classifier.1.weight"]), w["classifier.1.bias"])))
+    x = _q(F.relu(F.linear(x, _q(w["classifier.4.weight"]), w["classifier.4.bias"])))
+    return F.linear(x, _q(w["classifier.6.weight"]), w["classifier.6.bias"])
