@@ -58,6 +58,7 @@ SIGNATURES = {
     "b2i_forward_device": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "b2i_model_profile": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _c.c_char_p, _sz]),
     "b2i_resize_crop_u8": (_i, [_vp, _i, _vp, _i, _i, _vp]),
+    "b2i_resize_crop_u8_static": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp]),
     "b2i_resize_plan": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _i]),
     "b2i_resize_target": (None, [_i, _i, _ip, _ip, _ip, _ip]),
     "b2i_host_alloc": (_vp, [_sz]),

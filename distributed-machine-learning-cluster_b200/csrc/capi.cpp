@@ -483,6 +483,18 @@ int b2i_resize_crop_u8(b2i_ctx* ctx, int dev, const uint8_t* image, int h, int w
   return B2I_OK;
 }
 
+int b2i_resize_crop_u8_static(b2i_ctx* ctx, int dev, const void* d_image, int h, int w, void* d_out224,
+                              void* cuda_stream) {
+  if (!ctx || dev < 0 || dev >= static_cast<int>(ctx->devices.size()) || !d_image || !d_out224)
+    return fail(B2I_EINVAL, "b2i_resize_crop_u8_static: bad argument");
+  CAPI_CUDA(cudaSetDevice(ctx->devices[dev]));
+  std::string err;
+  if (!resize_crop_224_static(static_cast<const uint8_t*>(d_image), h, w, static_cast<uint8_t*>(d_out224),
+                              static_cast<cudaStream_t>(cuda_stream), &err))
+    return fail(err.find("exceeds the static scratch") != std::string::npos || err == "empty image" ? B2I_EINVAL : B2I_ECUDA, err);
+  return B2I_OK;
+}
+
 int b2i_resize_plan(int in_size, int out_size, int crop, int* first, int* count, int* idx,
                     float* coef, int cap) {
   if (in_size < 1 || out_size < 224 || crop < 0 || crop + 224 > out_size || !first || !count || !idx || !coef)

@@ -1,7 +1,9 @@
 // See resize.h.
 #include "resize.h"
 
+#include <algorithm>
 #include <cmath>
+#include <mutex>
 
 namespace b2i {
 
@@ -222,5 +224,98 @@ bool resize_crop_224_host(const uint8_t* image, int h, int w, uint8_t* out224, c
   if (e != cudaSuccess) { *err = std::string("resize kernels: ") + cudaGetErrorString(e); return false; }
   return true;
 }
+
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant.  Some hosts of this library may not allocate GPU memory at run time: a
+// serving process whose memory pool is carved up once at start-up, code running between stream
+// capture calls, or a tenant under a fixed memory budget.  For them the scratch of the resize (the
+// horizontally resampled rows and the two resampling plans) lives in one file-scope device array
+// instead of cudaMalloc'ed buffers.  Every GPU that loads the library carries the array until the
+// process exits.
+constexpr int kStaticMaxH = 1024;        // tallest input image the scratch holds
+constexpr int kStaticMaxTaps = 16384;    // resampling taps per axis (224 outputs x taps each)
+constexpr size_t kStaticTmpBytes = static_cast<size_t>(kStaticMaxH) * 224 * 3 * sizeof(float);
+constexpr size_t kStaticAxisBytes = 2 * 224 * sizeof(int) + kStaticMaxTaps * (sizeof(int) + sizeof(float));
+constexpr size_t kStaticScratchBytes = kStaticTmpBytes + 2 * kStaticAxisBytes;   // 3,018,240 bytes
+
+static __device__ __align__(256) unsigned char g_resize_scratch[kStaticScratchBytes];
+
+bool resize_crop_224_static(const uint8_t* d_image, int h, int w, uint8_t* d_out224, cudaStream_t st,
+                            std::string* err) {
+  // In host code `g_resize_scratch` is only a handle for the symbol, not an address a kernel can
+  // use; the device address is looked up once per GPU, with that GPU current.
+  static unsigned char* scratch_of_device[64] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) { *err = "no current CUDA device"; return false; }
+  unsigned char* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!scratch_of_device[dev]) {
+      unsigned char* ptr = nullptr;
+      e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_resize_scratch);
+      if (e != cudaSuccess || !ptr) {
+        *err = std::string("cudaGetSymbolAddress(resize scratch): ") + cudaGetErrorString(e);
+        return false;
+      }
+      scratch_of_device[dev] = ptr;
+    }
+    scratch = scratch_of_device[dev];
+  }
+  if (h < 1 || w < 1) { *err = "empty image"; return false; }
+  if (h > kStaticMaxH) {
+    *err = "image height " + std::to_string(h) + " exceeds the static scratch limit of " +
+           std::to_string(kStaticMaxH) + " rows; use b2i_resize_crop_u8";
+    return false;
+  }
+  const ResizeGeom g = resize_target(h, w);
+  AxisPlan px, py;
+  plan_axis(w, g.rw, g.crop_x, &px);
+  plan_axis(h, g.rh, g.crop_y, &py);
+  if (static_cast<int>(px.idx.size()) > kStaticMaxTaps || static_cast<int>(py.idx.size()) > kStaticMaxTaps) {
+    *err = "resampling plan of " + std::to_string(std::max(px.idx.size(), py.idx.size())) +
+           " taps exceeds the static scratch limit of " + std::to_string(kStaticMaxTaps) +
+           " taps per axis (image " + std::to_string(h) + "x" + std::to_string(w) + "); use b2i_resize_crop_u8";
+    return false;
+  }
+  // carve the array: [tmp rows][x plan][y plan]; every byte a kernel reads below is written
+  // earlier in this same call, so nothing has to be cleared between calls
+  float* d_tmp = reinterpret_cast<float*>(scratch);
+  auto carve = [&](int axis, int** first, int** count, int** idx, float** coef) {
+    unsigned char* b = scratch + kStaticTmpBytes + axis * kStaticAxisBytes;
+    *first = reinterpret_cast<int*>(b);
+    *count = *first + 224;
+    *idx = *count + 224;
+    *coef = reinterpret_cast<float*>(*idx + kStaticMaxTaps);
+  };
+  int *xf, *xc, *xi, *yf, *yc, *yi;
+  float *xw, *yw;
+  carve(0, &xf, &xc, &xi, &xw);
+  carve(1, &yf, &yc, &yi, &yw);
+  auto put = [&](void* dst, const void* src, size_t bytes) {
+    if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+  };
+  e = cudaSuccess;
+  put(xf, px.first.data(), 224 * sizeof(int));
+  put(xc, px.count.data(), 224 * sizeof(int));
+  put(xi, px.idx.data(), px.idx.size() * sizeof(int));
+  put(xw, px.coef.data(), px.coef.size() * sizeof(float));
+  put(yf, py.first.data(), 224 * sizeof(int));
+  put(yc, py.count.data(), 224 * sizeof(int));
+  put(yi, py.idx.data(), py.idx.size() * sizeof(int));
+  put(yw, py.coef.data(), py.coef.size() * sizeof(float));
+  if (e != cudaSuccess) { *err = std::string("plan upload: ") + cudaGetErrorString(e); return false; }
+  long long blocks = (static_cast<long long>(h) * 224 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  resize_h_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(d_image, h, w, xf, xc, xi, xw, d_tmp);
+  resize_v_kernel<<<(224 * 224 * 3 + 255) / 256, 256, 0, st>>>(d_tmp, yf, yc, yi, yw, d_out224);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) { *err = std::string("resize kernels: ") + cudaGetErrorString(e); return false; }
+  return true;
+}
+
+int resize_static_max_rows() { return kStaticMaxH; }
 
 }  // namespace b2i

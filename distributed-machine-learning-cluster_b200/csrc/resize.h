@@ -31,4 +31,11 @@ void plan_axis(int in_size, int out_size, int crop, AxisPlan* plan);
 bool resize_crop_224_host(const uint8_t* image, int h, int w, uint8_t* out224, cudaStream_t st,
                           std::string* err);
 
+// Same two kernels, but no allocation of any kind on the GPU side: device in/out pointers from the
+// caller, scratch in a static device array (limits: resize_static_max_rows() input rows, 16384
+// resampling taps per axis).  Enqueues on `st` and returns without synchronising.
+bool resize_crop_224_static(const uint8_t* d_image, int h, int w, uint8_t* d_out224, cudaStream_t st,
+                            std::string* err);
+int resize_static_max_rows();
+
 }  // namespace b2i

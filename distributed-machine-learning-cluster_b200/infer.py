@@ -111,6 +111,13 @@ class Context:
         check(_lib.lib().b2i_resize_crop_u8(self._h, dev, _ptr(img), h, w, _ptr(out)))
         return out
 
+    def resize_crop_static(self, d_image, h, w, d_out224, stream=None, dev=0):
+        """Allocation-free resize + crop for callers that may not allocate GPU memory: `d_image`
+        (u8 [h,w,3]) and `d_out224` (u8 [224,224,3]) are device addresses (ints) owned by the
+        caller, the scratch is a fixed array inside the library (h <= 1024). Enqueues on `stream`
+        and returns; calls on one GPU must not overlap."""
+        check(_lib.lib().b2i_resize_crop_u8_static(self._h, dev, d_image, h, w, d_out224, stream))
+
 
 def resize_target(h, w):
     rw, rh, cx, cy = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()

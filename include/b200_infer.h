@@ -125,6 +125,23 @@ int b2i_model_profile(b2i_model* m, int dev, const void* d_images_u8, int n, int
  * u8 [h][w][3] -> u8 [224][224][3] on the GPU `dev` of ctx. */
 int b2i_resize_crop_u8(b2i_ctx* ctx, int dev, const uint8_t* image, int h, int w, uint8_t* out224);
 
+/* No counterpart in the reference: the same resize + centre crop as b2i_resize_crop_u8 for callers
+ * that are not allowed to allocate GPU memory while they run -- a server that hands out one
+ * pre-sized memory pool at start-up, or a process pinned to a fixed memory budget. Nothing is
+ * allocated here (no cudaMalloc/cudaFree, no pinned memory): d_image (u8 [h][w][3]) and d_out224
+ * (u8 [224][224][3]) are DEVICE buffers the caller owns, and the intermediate rows plus the two
+ * resampling plans live in a 3,018,240-byte array compiled into the library, which every GPU that
+ * loads the library holds until the process exits. Limits: h <= 1024 rows and <= 16384 resampling
+ * taps per axis (with h <= 1024 the tap limit is not reached for any width); larger images are refused with B2I_EINVAL and a
+ * message naming the limit. The first call on each GPU looks the array's device address up, so make
+ * that first call before starting any stream capture. Work is enqueued on `cuda_stream` and the
+ * call returns without synchronising. All calls on one GPU share the array and it keeps whatever
+ * the previous call left in it; each call overwrites every byte it later reads, so nothing needs
+ * clearing, but two calls that overlap on the GPU (different streams, or different threads) would
+ * corrupt each other's rows: keep calls on one GPU in one stream, or order them with events. */
+int b2i_resize_crop_u8_static(b2i_ctx* ctx, int dev, const void* d_image, int h, int w, void* d_out224,
+                              void* cuda_stream);
+
 /* CPU-only: the resampling plan b2i_resize_crop_u8 uses for one axis (in_size -> out_size, keeping
  * the 224 outputs from `crop` on). first/count: int[224]; idx/coef: up to cap taps. Returns the
  * number of taps or a negative code. Lets the host logic be checked without a GPU. */
