@@ -55,6 +55,8 @@ SIGNATURES = {
     "b2i_model_activation_bytes": (_ll, [_vp]),
     "b2i_predict_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2i_predict_u8_on": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp]),
+    "b2i_submit_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _c.POINTER(_ll)]),
+    "b2i_wait": (_i, [_vp, _ll]),
     "b2i_forward_device": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "b2i_model_profile": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _c.c_char_p, _sz]),
     "b2i_resize_crop_u8": (_i, [_vp, _i, _vp, _i, _i, _vp]),

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "engine.h"
+#include "predict.h"
 #include "resize.h"
 
 using namespace b2i;
@@ -72,124 +73,6 @@ cudaError_t download(const void* dsrc, float* dst, size_t n, int prec) {
   if (e != cudaSuccess) return e;
   for (size_t i = 0; i < n; ++i) dst[i] = bf2f(t[i]);
   return cudaSuccess;
-}
-
-bool is_pinned(const void* p) {
-  cudaPointerAttributes a;
-  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return a.type == cudaMemoryTypeHost;
-}
-
-}  // namespace
-
-struct b2i_ctx {
-  std::vector<int> devices;
-};
-
-// Per-GPU staging state of one model.
-struct DevSlot {
-  std::unique_ptr<DeviceModel> dm;
-  cudaStream_t copy_st = nullptr, comp_st = nullptr;
-  cudaEvent_t copied[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr};
-  uint8_t* h_stage[2] = {nullptr, nullptr};  // pinned
-  uint8_t* d_in[2] = {nullptr, nullptr};
-  int32_t* d_idx = nullptr;
-  float* d_prob = nullptr;
-  float* d_logits = nullptr;
-  int32_t* h_idx = nullptr;  // pinned results
-  float* h_prob = nullptr;
-  float* h_logits = nullptr;  // pinned, allocated on first use
-  int chunk = 0;
-};
-
-struct b2i_model {
-  b2i_ctx* ctx = nullptr;
-  std::string name;
-  double flops = 0;
-  std::vector<DevSlot> slots;
-  std::mutex mu;
-  int max_batch = 0;
-};
-
-namespace {
-
-void free_slot(DevSlot& s) {
-  if (!s.dm) return;
-  cudaSetDevice(s.dm->device());
-  for (int i = 0; i < 2; ++i) {
-    if (s.h_stage[i]) cudaFreeHost(s.h_stage[i]);
-    if (s.d_in[i]) cudaFree(s.d_in[i]);
-    if (s.copied[i]) cudaEventDestroy(s.copied[i]);
-    if (s.done[i]) cudaEventDestroy(s.done[i]);
-  }
-  if (s.d_idx) cudaFree(s.d_idx);
-  if (s.d_prob) cudaFree(s.d_prob);
-  if (s.d_logits) cudaFree(s.d_logits);
-  if (s.h_idx) cudaFreeHost(s.h_idx);
-  if (s.h_prob) cudaFreeHost(s.h_prob);
-  if (s.h_logits) cudaFreeHost(s.h_logits);
-  if (s.copy_st) cudaStreamDestroy(s.copy_st);
-  if (s.comp_st) cudaStreamDestroy(s.comp_st);
-  s.dm.reset();
-}
-
-// One GPU's share of a predict call. Returns 0 or a B2I_E* code with `err` filled.
-int run_slot(DevSlot& s, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
-             float* logits, std::string* err) {
-  if (n == 0) return B2I_OK;
-  auto cu = [&](cudaError_t e, const char* what) {
-    if (e == cudaSuccess) return false;
-    *err = std::string(what) + ": " + cudaGetErrorString(e);
-    return true;
-  };
-  if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return B2I_ECUDA;
-  const bool pinned = is_pinned(images);
-  const int classes = s.dm->classes();
-  if (logits && !s.h_logits) {
-    if (cu(cudaMallocHost(reinterpret_cast<void**>(&s.h_logits),
-                          static_cast<size_t>(s.dm->max_batch()) * classes * 4), "cudaMallocHost(logits)"))
-      return B2I_ENOMEM;
-  }
-  int c = 0;
-  for (int off = 0; off < n; off += s.chunk, ++c) {
-    const int nb = std::min(s.chunk, n - off);
-    const int b = c & 1;
-    const size_t bytes = static_cast<size_t>(nb) * B2I_IMAGE_BYTES;
-    const uint8_t* src = images + static_cast<size_t>(off) * B2I_IMAGE_BYTES;
-    if (c >= 2) {
-      // slot b is free once the forward that read d_in[b] two chunks ago has finished
-      if (cu(cudaEventSynchronize(s.done[b]), "cudaEventSynchronize")) return B2I_ECUDA;
-    }
-    if (!pinned) {
-      std::memcpy(s.h_stage[b], src, bytes);
-      src = s.h_stage[b];
-    }
-    if (cu(cudaMemcpyAsync(s.d_in[b], src, bytes, cudaMemcpyHostToDevice, s.copy_st), "H2D copy")) return B2I_ECUDA;
-    if (cu(cudaEventRecord(s.copied[b], s.copy_st), "cudaEventRecord")) return B2I_ECUDA;
-    if (cu(cudaStreamWaitEvent(s.comp_st, s.copied[b], 0), "cudaStreamWaitEvent")) return B2I_ECUDA;
-    if (!s.dm->forward(s.d_in[b], nb, k, s.d_idx + static_cast<size_t>(off) * k,
-                       s.d_prob + static_cast<size_t>(off) * k,
-                       logits ? s.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, err))
-      return B2I_ECUDA;
-    if (cu(cudaEventRecord(s.done[b], s.comp_st), "cudaEventRecord")) return B2I_ECUDA;
-    // the next H2D into the other slot may start at once; the one after waits on `done`
-    if (cu(cudaStreamWaitEvent(s.copy_st, s.done[b], 0), "cudaStreamWaitEvent")) return B2I_ECUDA;
-  }
-  const size_t nk = static_cast<size_t>(n) * k;
-  if (cu(cudaMemcpyAsync(s.h_idx, s.d_idx, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H idx")) return B2I_ECUDA;
-  if (cu(cudaMemcpyAsync(s.h_prob, s.d_prob, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H prob")) return B2I_ECUDA;
-  if (logits &&
-      cu(cudaMemcpyAsync(s.h_logits, s.d_logits, static_cast<size_t>(n) * classes * 4,
-                         cudaMemcpyDeviceToHost, s.comp_st), "D2H logits"))
-    return B2I_ECUDA;
-  if (cu(cudaStreamSynchronize(s.comp_st), "cudaStreamSynchronize")) return B2I_ECUDA;
-  std::memcpy(idx, s.h_idx, nk * 4);
-  std::memcpy(prob, s.h_prob, nk * 4);
-  if (logits) std::memcpy(logits, s.h_logits, static_cast<size_t>(n) * classes * 4);
-  return B2I_OK;
 }
 
 }  // namespace
@@ -322,30 +205,12 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
     DevSlot& s = m->slots[i];
     s.dm = std::make_unique<DeviceModel>();
     if (!s.dm->init(ctx->devices[i], net, ec, &err)) {
-      for (auto& t : m->slots) free_slot(t);
+      for (auto& t : m->slots) slot_free(&t);
       return fail(B2I_ECUDA, err);
     }
-    s.chunk = s.dm->micro_batch();
-    const size_t in_bytes = static_cast<size_t>(s.chunk) * B2I_IMAGE_BYTES;
-    const size_t nk = static_cast<size_t>(cfg.max_batch) * 8;
-    cudaError_t e = cudaSuccess;
-    auto chk = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
-    chk(cudaStreamCreateWithFlags(&s.copy_st, cudaStreamNonBlocking));
-    chk(cudaStreamCreateWithFlags(&s.comp_st, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; ++b) {
-      chk(cudaEventCreateWithFlags(&s.copied[b], cudaEventDisableTiming));
-      chk(cudaEventCreateWithFlags(&s.done[b], cudaEventDisableTiming));
-      chk(cudaMallocHost(reinterpret_cast<void**>(&s.h_stage[b]), in_bytes));
-      chk(cudaMalloc(reinterpret_cast<void**>(&s.d_in[b]), in_bytes));
-    }
-    chk(cudaMalloc(reinterpret_cast<void**>(&s.d_idx), nk * 4));
-    chk(cudaMalloc(reinterpret_cast<void**>(&s.d_prob), nk * 4));
-    chk(cudaMalloc(reinterpret_cast<void**>(&s.d_logits), static_cast<size_t>(cfg.max_batch) * B2I_CLASSES * 4));
-    chk(cudaMallocHost(reinterpret_cast<void**>(&s.h_idx), nk * 4));
-    chk(cudaMallocHost(reinterpret_cast<void**>(&s.h_prob), nk * 4));
-    if (e != cudaSuccess) {
-      for (auto& t : m->slots) free_slot(t);
-      return cuda_fail(e, "staging allocation");
+    if (!slot_setup(&s, cfg.max_batch, &err)) {
+      for (auto& t : m->slots) slot_free(&t);
+      return fail(B2I_ECUDA, err);
     }
   }
   *out = m.release();
@@ -354,7 +219,7 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
 
 void b2i_model_free(b2i_model* m) {
   if (!m) return;
-  for (auto& s : m->slots) free_slot(s);
+  for (auto& s : m->slots) slot_free(&s);
   delete m;
 }
 
@@ -373,34 +238,17 @@ long long b2i_model_activation_bytes(const b2i_model* m) {
 int b2i_predict_u8_on(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
                       int32_t* idx, float* prob, float* logits) {
   if (!m) return fail(B2I_EINVAL, "null model");
-  if (n < 0 || (n > 0 && (!images || !idx || !prob))) return fail(B2I_EINVAL, "b2i_predict_u8: null buffer");
-  if (k < 1 || k > 8) return fail(B2I_EINVAL, "k must be in 1..8");
-  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size()))
-    return fail(B2I_EINVAL, "device range outside the model's context");
-  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch)
-    return fail(B2I_EINVAL, "batch " + std::to_string(n) + " exceeds " + std::to_string(n_dev) + " GPU(s) x max_batch " +
-                                std::to_string(m->max_batch));
   if (n == 0) return B2I_OK;
-  std::lock_guard<std::mutex> lock(m->mu);
-  // contiguous shards: GPU g takes images [g*per, min(n, (g+1)*per))
-  const int per = (n + n_dev - 1) / n_dev;
-  std::vector<int> rc(n_dev, B2I_OK);
-  std::vector<std::string> errs(n_dev);
-  auto work = [&](int g) {
-    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
-    rc[g] = run_slot(m->slots[first_dev + g], images + static_cast<size_t>(lo) * B2I_IMAGE_BYTES, hi - lo, k,
-                     idx + static_cast<size_t>(lo) * k, prob + static_cast<size_t>(lo) * k,
-                     logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, &errs[g]);
-  };
-  if (n_dev == 1) {
-    work(0);
-  } else {
-    std::vector<std::thread> th;
-    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
-    for (auto& t : th) t.join();
-  }
-  for (int g = 0; g < n_dev; ++g)
-    if (rc[g] != B2I_OK) return fail(rc[g], "GPU " + std::to_string(first_dev + g) + ": " + errs[g]);
+  std::lock_guard<std::mutex> lock(m->mu);   // calls on one model are serialised (reference: Mutex<Box<dyn ModuleT>>)
+  std::string err;
+  // a blocking call drains whatever an asynchronous user left in flight on its lane first
+  const int lane = static_cast<int>(m->next_ticket & 1);
+  if (m->pending[lane].active) return fail(B2I_EINVAL, "an asynchronous request is still in flight; b2i_wait for it first");
+  long long t = -1;
+  int rc = predict_submit(m, first_dev, n_dev, images, n, k, idx, prob, logits, &t, &err);
+  if (rc != B2I_OK) return fail(rc, err);
+  rc = predict_wait(m, t, &err);
+  if (rc != B2I_OK) return fail(rc, err);
   return B2I_OK;
 }
 
@@ -408,6 +256,25 @@ int b2i_predict_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* i
                    float* logits) {
   if (!m) return fail(B2I_EINVAL, "null model");
   return b2i_predict_u8_on(m, 0, static_cast<int>(m->slots.size()), images, n, k, idx, prob, logits);
+}
+
+int b2i_submit_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
+                  float* logits, long long* ticket) {
+  if (!m || !ticket) return fail(B2I_EINVAL, "null model/ticket");
+  std::lock_guard<std::mutex> lock(m->mu);
+  std::string err;
+  const int rc = predict_submit(m, 0, static_cast<int>(m->slots.size()), images, n, k, idx, prob, logits, ticket, &err);
+  if (rc != B2I_OK) return fail(rc, err);
+  return B2I_OK;
+}
+
+int b2i_wait(b2i_model* m, long long ticket) {
+  if (!m) return fail(B2I_EINVAL, "null model");
+  std::lock_guard<std::mutex> lock(m->mu);
+  std::string err;
+  const int rc = predict_wait(m, ticket, &err);
+  if (rc != B2I_OK) return fail(rc, err);
+  return B2I_OK;
 }
 
 int b2i_forward_device(b2i_model* m, int dev, const void* d_images, int n, int k, void* d_idx,

@@ -1,0 +1,215 @@
+// See predict.h.
+#include "predict.h"
+
+#include <algorithm>
+#include <cstring>
+#include <thread>
+
+#include "../../include/b200_infer.h"
+
+namespace b2i {
+
+namespace {
+
+bool is_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+struct Shard {
+  int rc = B2I_OK;
+  std::string err;
+};
+
+// H2D (chunked, own stream) + forward per chunk + D2H of the results, all asynchronous.
+void enqueue_shard(DevSlot& s, int lane_id, const uint8_t* images, int n, int k, int32_t* idx,
+                   float* prob, float* logits, Shard* out) {
+  Lane& L = s.lane[lane_id];
+  L.n = n; L.k = k; L.out_idx = idx; L.out_prob = prob; L.out_logits = logits;
+  if (n == 0) return;
+  auto cu = [&](cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return false;
+    out->rc = B2I_ECUDA;
+    out->err = std::string(what) + ": " + cudaGetErrorString(e);
+    return true;
+  };
+  if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
+  const int classes = s.dm->classes();
+  const size_t cap = static_cast<size_t>(s.dm->max_batch());
+  if (logits && !L.d_logits) {
+    if (cu(cudaMalloc(reinterpret_cast<void**>(&L.d_logits), cap * classes * 4), "cudaMalloc(logits)")) return;
+    if (cu(cudaMallocHost(reinterpret_cast<void**>(&L.h_logits), cap * classes * 4), "cudaMallocHost(logits)")) return;
+  }
+  const uint8_t* src = images;
+  if (!is_pinned(images)) {
+    // pageable source: stage through pinned memory so the copy is a real asynchronous DMA
+    if (!L.h_stage && cu(cudaMallocHost(reinterpret_cast<void**>(&L.h_stage), cap * B2I_IMAGE_BYTES), "cudaMallocHost(stage)")) return;
+    std::memcpy(L.h_stage, images, static_cast<size_t>(n) * B2I_IMAGE_BYTES);
+    src = L.h_stage;
+  }
+  int c = 0;
+  for (int off = 0; off < n; off += s.chunk, ++c) {
+    const int nb = std::min(s.chunk, n - off);
+    const size_t byte_off = static_cast<size_t>(off) * B2I_IMAGE_BYTES;
+    if (cu(cudaMemcpyAsync(L.d_in + byte_off, src + byte_off, static_cast<size_t>(nb) * B2I_IMAGE_BYTES,
+                           cudaMemcpyHostToDevice, s.copy_st), "H2D copy")) return;
+    if (cu(cudaEventRecord(L.copied[c], s.copy_st), "cudaEventRecord")) return;
+    if (cu(cudaStreamWaitEvent(s.comp_st, L.copied[c], 0), "cudaStreamWaitEvent")) return;
+    if (!s.dm->forward(L.d_in + byte_off, nb, k, L.d_idx + static_cast<size_t>(off) * k,
+                       L.d_prob + static_cast<size_t>(off) * k,
+                       logits ? L.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, &out->err)) {
+      out->rc = B2I_ECUDA;
+      return;
+    }
+  }
+  const size_t nk = static_cast<size_t>(n) * k;
+  if (cu(cudaMemcpyAsync(L.h_idx, L.d_idx, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H idx")) return;
+  if (cu(cudaMemcpyAsync(L.h_prob, L.d_prob, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H prob")) return;
+  if (logits && cu(cudaMemcpyAsync(L.h_logits, L.d_logits, static_cast<size_t>(n) * classes * 4,
+                                   cudaMemcpyDeviceToHost, s.comp_st), "D2H logits"))
+    return;
+  cu(cudaEventRecord(L.done, s.comp_st), "cudaEventRecord(done)");
+}
+
+void collect_shard(DevSlot& s, int lane_id, Shard* out) {
+  Lane& L = s.lane[lane_id];
+  if (L.n == 0) return;
+  cudaError_t e = cudaSetDevice(s.dm->device());
+  if (e == cudaSuccess) e = cudaEventSynchronize(L.done);
+  if (e != cudaSuccess) {
+    out->rc = B2I_ECUDA;
+    out->err = std::string("waiting for the forward: ") + cudaGetErrorString(e);
+    return;
+  }
+  const size_t nk = static_cast<size_t>(L.n) * L.k;
+  std::memcpy(L.out_idx, L.h_idx, nk * 4);
+  std::memcpy(L.out_prob, L.h_prob, nk * 4);
+  if (L.out_logits) std::memcpy(L.out_logits, L.h_logits, static_cast<size_t>(L.n) * s.dm->classes() * 4);
+}
+
+}  // namespace
+
+bool slot_setup(DevSlot* s, int max_batch, std::string* err) {
+  cudaError_t e = cudaSetDevice(s->dm->device());
+  auto chk = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+  s->chunk = s->dm->micro_batch();
+  const int chunks = (max_batch + s->chunk - 1) / s->chunk;
+  const size_t in_bytes = static_cast<size_t>(max_batch) * B2I_IMAGE_BYTES;
+  const size_t nk = static_cast<size_t>(max_batch) * 8;
+  chk(cudaStreamCreateWithFlags(&s->copy_st, cudaStreamNonBlocking));
+  chk(cudaStreamCreateWithFlags(&s->comp_st, cudaStreamNonBlocking));
+  for (Lane& L : s->lane) {
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_in), in_bytes));
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_idx), nk * 4));
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_prob), nk * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_idx), nk * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_prob), nk * 4));
+    chk(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+    L.copied.assign(chunks, nullptr);
+    for (auto& ev : L.copied) chk(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  }
+  if (e != cudaSuccess) {
+    *err = std::string("staging allocation: ") + cudaGetErrorString(e);
+    return false;
+  }
+  return true;
+}
+
+void slot_free(DevSlot* s) {
+  if (!s->dm) return;
+  cudaSetDevice(s->dm->device());
+  cudaDeviceSynchronize();
+  for (Lane& L : s->lane) {
+    if (L.d_in) cudaFree(L.d_in);
+    if (L.h_stage) cudaFreeHost(L.h_stage);
+    if (L.d_idx) cudaFree(L.d_idx);
+    if (L.d_prob) cudaFree(L.d_prob);
+    if (L.d_logits) cudaFree(L.d_logits);
+    if (L.h_idx) cudaFreeHost(L.h_idx);
+    if (L.h_prob) cudaFreeHost(L.h_prob);
+    if (L.h_logits) cudaFreeHost(L.h_logits);
+    if (L.done) cudaEventDestroy(L.done);
+    for (auto ev : L.copied) if (ev) cudaEventDestroy(ev);
+    L = Lane();
+  }
+  if (s->copy_st) cudaStreamDestroy(s->copy_st);
+  if (s->comp_st) cudaStreamDestroy(s->comp_st);
+  s->dm.reset();
+}
+
+int predict_submit(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
+                   int32_t* idx, float* prob, float* logits, long long* ticket, std::string* err) {
+  if (n < 0 || (n > 0 && (!images || !idx || !prob))) { *err = "null buffer"; return B2I_EINVAL; }
+  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
+  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size())) {
+    *err = "device range outside the model's context";
+    return B2I_EINVAL;
+  }
+  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch) {
+    *err = "batch " + std::to_string(n) + " exceeds " + std::to_string(n_dev) + " GPU(s) x max_batch " +
+           std::to_string(m->max_batch);
+    return B2I_EINVAL;
+  }
+  const long long t = m->next_ticket;
+  const int lane = static_cast<int>(t & 1);
+  if (m->pending[lane].active) {
+    *err = "two requests are already in flight on this model; collect ticket " +
+           std::to_string(m->pending[lane].ticket) + " with b2i_wait first";
+    return B2I_EINVAL;
+  }
+  // contiguous shards: GPU g takes images [g*per, min(n, (g+1)*per))
+  const int per = (n + n_dev - 1) / n_dev;
+  std::vector<Shard> sh(n_dev);
+  auto work = [&](int g) {
+    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
+    enqueue_shard(m->slots[first_dev + g], lane, images + static_cast<size_t>(lo) * B2I_IMAGE_BYTES, hi - lo, k,
+                  idx + static_cast<size_t>(lo) * k, prob + static_cast<size_t>(lo) * k,
+                  logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, &sh[g]);
+  };
+  if (n_dev == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;   // one enqueuing thread per GPU: launches are CPU-bound at small batch
+    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
+    for (auto& x : th) x.join();
+  }
+  m->pending[lane].active = true;
+  m->pending[lane].ticket = t;
+  m->pending[lane].first_dev = first_dev;
+  m->pending[lane].n_dev = n_dev;
+  m->next_ticket = t + 1;
+  *ticket = t;
+  for (int g = 0; g < n_dev; ++g)
+    if (sh[g].rc != B2I_OK) {
+      // leave the lane collectable so the caller's b2i_wait (or the blocking wrapper) clears it
+      *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].err;
+      for (int q = 0; q < n_dev; ++q) m->slots[first_dev + q].lane[lane].n = 0;
+      m->pending[lane].active = false;
+      return sh[g].rc;
+    }
+  return B2I_OK;
+}
+
+int predict_wait(b2i_model* m, long long ticket, std::string* err) {
+  const int lane = static_cast<int>(ticket & 1);
+  Pending& p = m->pending[lane];
+  if (ticket < 0 || !p.active || p.ticket != ticket) {
+    *err = "ticket " + std::to_string(ticket) + " is not in flight";
+    return B2I_EINVAL;
+  }
+  std::vector<Shard> sh(p.n_dev);
+  for (int g = 0; g < p.n_dev; ++g) collect_shard(m->slots[p.first_dev + g], lane, &sh[g]);
+  p.active = false;
+  for (int g = 0; g < p.n_dev; ++g)
+    if (sh[g].rc != B2I_OK) {
+      *err = "GPU " + std::to_string(p.first_dev + g) + ": " + sh[g].err;
+      return sh[g].rc;
+    }
+  return B2I_OK;
+}
+
+}  // namespace b2i

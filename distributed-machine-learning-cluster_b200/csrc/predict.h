@@ -1,0 +1,79 @@
+// Batched predict over the GPUs of a context: per-GPU lanes (two requests may be in flight so the
+// host->device copy of request t+1 overlaps the forward of request t), contiguous batch sharding,
+// pinned staging, results written back into the caller's arrays.  Replaces the reference's
+// one-image-per-RPC scattering (reference src/services.rs:415-421) on one multi-GPU member.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "engine.h"
+
+struct b2i_ctx {
+  std::vector<int> devices;
+};
+
+namespace b2i {
+
+// One in-flight request's share on one GPU.
+struct Lane {
+  uint8_t* d_in = nullptr;       // device, max_batch images
+  uint8_t* h_stage = nullptr;    // pinned, max_batch images; allocated the first time a pageable source shows up
+  int32_t* d_idx = nullptr;
+  float* d_prob = nullptr;
+  float* d_logits = nullptr;     // device, allocated on first use
+  int32_t* h_idx = nullptr;      // pinned
+  float* h_prob = nullptr;
+  float* h_logits = nullptr;     // pinned, allocated on first use
+  std::vector<cudaEvent_t> copied;  // one per micro-batch chunk
+  cudaEvent_t done = nullptr;
+  // the request currently using this lane
+  int n = 0, k = 0;
+  int32_t* out_idx = nullptr;
+  float* out_prob = nullptr;
+  float* out_logits = nullptr;
+};
+
+struct DevSlot {
+  std::unique_ptr<DeviceModel> dm;
+  cudaStream_t copy_st = nullptr, comp_st = nullptr;
+  Lane lane[2];
+  int chunk = 0;
+};
+
+struct Pending {
+  bool active = false;
+  long long ticket = -1;
+  int first_dev = 0, n_dev = 0;
+};
+
+}  // namespace b2i
+
+struct b2i_model {
+  b2i_ctx* ctx = nullptr;
+  std::string name;
+  double flops = 0;
+  std::vector<b2i::DevSlot> slots;
+  std::mutex mu;
+  int max_batch = 0;
+  long long next_ticket = 0;
+  b2i::Pending pending[2];
+};
+
+namespace b2i {
+
+bool slot_setup(DevSlot* s, int max_batch, std::string* err);   // streams, lanes, events (after dm is initialised)
+void slot_free(DevSlot* s);
+
+// Enqueue one request (H2D + forward + D2H of the results into pinned staging) on the GPUs
+// [first_dev, first_dev + n_dev) and return its ticket without waiting.  Returns 0 or a B2I_E* code.
+int predict_submit(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
+                   int32_t* idx, float* prob, float* logits, long long* ticket, std::string* err);
+// Block until the request is complete and its results are in the arrays given at submit time.
+int predict_wait(b2i_model* m, long long ticket, std::string* err);
+
+}  // namespace b2i

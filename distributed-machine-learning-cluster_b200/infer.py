@@ -221,6 +221,17 @@ class Model:
                                                _ptr(logits)))
         return (idx, prob, logits) if want_logits else (idx, prob)
 
+    def submit_u8(self, images_u8, idx, prob, logits=None):
+        """Asynchronous predict: enqueue and return a ticket. `images_u8` (ideally a PinnedBuffer
+        view), `idx` int32 [n,k] and `prob` f32 [n,k] must stay alive until wait(ticket) returns."""
+        n, k = idx.shape
+        t = ctypes.c_longlong(-1)
+        check(_lib.lib().b2i_submit_u8(self._h, _ptr(images_u8), n, k, _ptr(idx), _ptr(prob), _ptr(logits), ctypes.byref(t)))
+        return t.value
+
+    def wait(self, ticket):
+        check(_lib.lib().b2i_wait(self._h, ticket))
+
     def forward_device(self, d_images, n, k, d_idx, d_prob, d_logits=None, stream=None, dev=0):
         """Raw device pointers (ints) on GPU `dev`; enqueues on `stream` (cudaStream_t as int)."""
         check(_lib.lib().b2i_forward_device(self._h, dev, d_images, n, k, d_idx, d_prob, d_logits, stream))

@@ -105,6 +105,18 @@ int b2i_predict_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* i
 int b2i_predict_u8_on(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
                       int32_t* idx, float* prob, float* logits);
 
+/* Asynchronous pair for throughput: b2i_submit_u8 enqueues the whole request (host->device copy,
+ * forward, device->host copy of the results) on all GPUs of the model and returns a ticket at once;
+ * b2i_wait blocks until that request is complete and idx/prob(/logits) given at submit time are
+ * filled. Up to TWO requests may be in flight, so the copy of request t+1 overlaps the forward of
+ * request t; submitting a third before waiting for the first fails with B2I_EINVAL. `images` should
+ * be pinned (b2i_host_alloc) and must stay valid, with the output arrays, until b2i_wait returns.
+ * This is what a member serving several concurrent `predict` RPCs (reference src/main.rs:74-79:
+ * up to 10 channels) uses instead of serialising them. */
+int b2i_submit_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
+                  float* logits, long long* ticket);
+int b2i_wait(b2i_model* m, long long ticket);
+
 /* Device-resident form for one GPU of the model (dev = index inside the context): all pointers are
  * device pointers on that GPU, work is enqueued on `cuda_stream` (a cudaStream_t, may be NULL for
  * the default stream) and the call returns without synchronising. Used by the benchmark to time

@@ -184,6 +184,34 @@ def test_batch_shapes_ragged_empty_single(pkg, ctx, resnet18_ot):
     assert np.abs(lg_all[:4] - ref).max() <= bf16_budget(ref)
 
 
+def test_submit_wait_overlaps_and_matches_blocking_predict(pkg, ctx, resnet18_ot):
+    """b2i_submit_u8 / b2i_wait: two requests in flight give the same answers as blocking calls, a
+    third is refused, tickets are checked."""
+    from oracle import synth
+    a, b = synth.synthetic_images(6, seed=21), synth.synthetic_images(3, seed=22)
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=8, micro_batch=4) as m:
+        ia, pa = m.predict_u8(a, k=5)
+        ib, pb = m.predict_u8(b, k=5)
+        oa = (np.empty((6, 5), np.int32), np.empty((6, 5), np.float32))
+        ob = (np.empty((3, 5), np.int32), np.empty((3, 5), np.float32))
+        ta = m.submit_u8(a, *oa)
+        tb = m.submit_u8(b, *ob)
+        with pytest.raises(pkg.B2IError):
+            m.submit_u8(a, np.empty((6, 5), np.int32), np.empty((6, 5), np.float32))   # third in flight
+        with pytest.raises(pkg.B2IError):
+            m.predict_u8(a, k=5)                                                        # blocking call while tickets are open
+        m.wait(ta)
+        with pytest.raises(pkg.B2IError):
+            m.wait(ta)                                                                  # already collected
+        m.wait(tb)
+        assert np.array_equal(oa[0], ia) and np.array_equal(oa[1], pa)
+        assert np.array_equal(ob[0], ib) and np.array_equal(ob[1], pb)
+        for r in range(4):                                                              # steady-state pipeline
+            t = m.submit_u8(a, *oa)
+            m.wait(t)
+        assert np.array_equal(oa[0], ia)
+
+
 def test_model_load_errors(pkg, ctx, tmp_path, resnet18_ot):
     with pytest.raises(pkg.B2IError) as e:
         pkg.Model(ctx, "vgg16", resnet18_ot)
