@@ -24,6 +24,7 @@ class ModelConfig(ctypes.Structure):
         ("tile_n_max", ctypes.c_int),
         ("keep_tensors", ctypes.c_int),
         ("fused_stem", ctypes.c_int),
+        ("patch_conv", ctypes.c_int),
     ]
 
 

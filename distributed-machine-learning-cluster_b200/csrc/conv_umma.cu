@@ -456,6 +456,183 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// 3x3 / stride 1 / pad 1 convolution with 64 input and 64 output channels (ResNet layer1), reading
+// the nine filter taps as SHIFTED VIEWS of one halo patch instead of nine im2col loads.
+//
+// A CTA owns 16 rows x 8 columns of output pixels.  One TMA tiled load brings the 18 x 10 pixel
+// halo patch (128 bytes = 64 channels per pixel, 128-byte swizzle, zero fill outside the image =
+// the conv's padding).  For tap (r, s) the A operand of the MMA is the patch starting at pixel
+// (r, s): 8-row core-matrix groups are the 8 pixels of one output row (8 x 128 B contiguous), the
+// next group is the next patch row (SBO = 10 x 128 B).  The nine 64x64 weight tiles stay resident in
+// shared memory for the life of the CTA.  Per tile this moves 23 KB through L2 instead of 216 KB.
+constexpr int PT_W = 10, PT_H = 18;
+constexpr uint32_t PT_BYTES = ((PT_W * PT_H * 128 + 1023) / 1024) * 1024;   // 23552
+constexpr uint32_t PT_WBYTES = 9 * 64 * 128;                                // resident weights, 73728
+
+struct PatchP {
+  int N, H, W, tiles_w, tiles_h, total_tiles, relu;
+  const float* bias;
+  const __nv_bfloat16* residual;
+  __nv_bfloat16* out;
+};
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0,
+                                            int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(PTHREADS, 1)
+conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+                         const PatchP p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t w_smem = base;
+  const uint32_t patch0 = base + PT_WBYTES;
+  const uint32_t bar0 = smem_u32(bars);
+  auto patch_full = [&](int b) { return bar0 + 8u * b; };
+  auto patch_empty = [&](int b) { return bar0 + 8u * (2 + b); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (4 + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (6 + b); };
+  const uint32_t w_full = bar0 + 8u * 8;
+
+  if (threadIdx.x == 0) {
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(patch_full(b), 1);
+      mbar_init(patch_empty(b), 1);
+      mbar_init(acc_full(b), 1);
+      mbar_init(acc_empty(b), 4);
+    }
+    mbar_init(w_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmW);
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_slot), 128);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(w_full, PT_WBYTES);
+      for (int tap = 0; tap < 9; ++tap) tma_load_2d(w_smem + tap * 8192u, &tmW, w_full, tap * 64, 0);
+      int i = 0;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+        const int b = i & 1;
+        const int n = t / tiles_per_img;
+        const int rem = t - n * tiles_per_img;
+        const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
+        mbar_wait(patch_empty(b), ((i >> 1) & 1) ^ 1);
+        mbar_expect_tx(patch_full(b), PT_W * PT_H * 128);
+        tma_load_4d(patch0 + b * PT_BYTES, &tmX, patch_full(b), 0, tx * 8 - 1, ty * 16 - 1, n);
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = umma_idesc_bf16(128, 64);
+    if (lane == 0) mbar_wait(w_full, 0);
+    __syncwarp();
+    int i = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+      const int b = i & 1;
+      mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
+      mbar_wait(patch_full(b), (i >> 1) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t pb = patch0 + b * PT_BYTES;
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 64);
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          const uint32_t a_addr = pb + static_cast<uint32_t>(((tap / 3) * PT_W + (tap % 3)) * 128);
+          uint64_t adesc = umma_smem_desc_sw128(a_addr);
+          adesc = (adesc & ~(static_cast<uint64_t>(0x3FFF) << 32)) | (static_cast<uint64_t>((PT_W * 128) >> 4) << 32);
+          // base-offset field stays 0: measured on B200, the unit applies the 128B swizzle to absolute
+          // shared-memory address bits, exactly as TMA wrote the patch, so any 128-byte-aligned start works
+          const uint64_t bdesc = umma_smem_desc_sw128(w_smem + tap * 8192u);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (tap | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(patch_empty(b));
+        umma_commit(acc_full(b));
+      }
+      __syncwarp();
+    }
+  } else {
+    const int q = warp & 3;
+    int i = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+      const int b = i & 1;
+      const int n = t / tiles_per_img;
+      const int rem = t - n * tiles_per_img;
+      const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
+      mbar_wait(acc_full(b), (i >> 1) & 1);
+      tc_fence_after();
+      const int mrow = q * 32 + lane;              // row of the 128-row tile: (output row, column) = (mrow / 8, mrow % 8)
+      const int oh = ty * 16 + (mrow >> 3), ow = tx * 8 + (mrow & 7);
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 64);
+      uint32_t v0[32], v1[32];
+      tmem_ld32(t_row, v0);
+      tmem_ld32(t_row + 32u, v1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty(b));
+      if (oh < p.H && ow < p.W) {
+        const size_t off = ((static_cast<size_t>(n) * p.H + oh) * p.W + ow) * 64;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(c == 0 ? v0[j] : v1[j]) + __ldg(p.bias + c * 32 + j);
+          if (p.residual) {
+            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off + c * 32);
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const uint4 rv = __ldg(rp + g);
+              const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                f[g * 8 + e * 2] += bf16_lo(rr[e]);
+                f[g * 8 + e * 2 + 1] += bf16_hi(rr[e]);
+              }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          uint4* op = reinterpret_cast<uint4*>(p.out + off + c * 32);
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            op[g] = make_uint4(pack_bf16x2(f[g * 8 + 0], f[g * 8 + 1]), pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3]),
+                               pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5]), pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
 int persistent_stages(int BN) {
   int s = (210 * 1024) / (A_TILE_BYTES + BN * 128);
   if (s > MAX_STAGES) s = MAX_STAGES;
@@ -508,6 +685,37 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   return cudaGetLastError();
 }
 
+cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmW,
+                         cudaStream_t st) {
+  static bool attr_set[16] = {};
+  static int sm_count[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 16) return cudaErrorInvalidDevice;
+  const size_t smem = PT_WBYTES + 2 * PT_BYTES + 1024;
+  if (!attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  const ConvGeom& g = a.g;
+  PatchP p;
+  p.N = g.N; p.H = g.H; p.W = g.W;
+  p.tiles_w = (g.W + 7) / 8;
+  p.tiles_h = (g.H + 15) / 16;
+  p.total_tiles = g.N * p.tiles_w * p.tiles_h;
+  p.relu = a.relu;
+  p.bias = a.bias;
+  p.residual = static_cast<const __nv_bfloat16*>(a.residual);
+  p.out = static_cast<__nv_bfloat16*>(a.out);
+  const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
+  conv3x3_c64_patch_kernel<<<grid, PTHREADS, smem, st>>>(*tmX, *tmW, p);
+  return cudaGetLastError();
+}
+
 template <int AMODE, bool B_TMA>
 cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
                      cudaStream_t st) {
@@ -557,6 +765,10 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
       a.stages > MAX_STAGES || g.M <= 0)
     return cudaErrorInvalidValue;
   if (!a.out_fp32 && ((a.ldo & 7) || (g.Cout & 31))) return cudaErrorInvalidValue;
+  if (a.patch) {
+    if (!conv_patch_applicable(g) || a.out_fp32 || a.ldo != 64 || !tmA || !tmB) return cudaErrorInvalidValue;
+    return launch_patch(a, tmA, tmB, st);
+  }
   switch (a.amode) {
     case A_GATHER:
       if (g.C % 64 || g.K != g.R * g.S * g.C) return cudaErrorInvalidValue;
@@ -618,6 +830,27 @@ int make_tmap_rows(CUtensorMap* tm, const void* a, int rows, int K, int box_rows
 int make_tmap_weights(CUtensorMap* tm, const void* w, int Cout_pad, int K, int BN,
                       const char** err) {
   return make_tmap_rows(tm, w, Cout_pad, K, BN, err);
+}
+
+bool conv_patch_applicable(const ConvGeom& g) {
+  return g.C == 64 && g.Cout == 64 && g.Cout_pad == 64 && g.R == 3 && g.S == 3 && g.stride == 1 &&
+         g.pad == 1 && g.K == 576 && g.OH == g.H && g.OW == g.W;
+}
+
+// Tiled 4-D map over NHWC [N][H][W][64] with an 18 x 10 pixel box: the halo patch of one 16 x 8
+// output tile; out-of-image coordinates (the conv padding) are zero-filled by the TMA unit.
+int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err) {
+  static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
+  if (!fn) { *err = "cuTensorMapEncodeTiled entry point not found"; return -1; }
+  cuuint64_t dims[4] = {64, static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(N)};
+  cuuint64_t strides[3] = {128, static_cast<cuuint64_t>(W) * 128, static_cast<cuuint64_t>(H) * W * 128};
+  cuuint32_t box[4] = {64, PT_W, PT_H, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { *err = "cuTensorMapEncodeTiled (patch) failed"; return static_cast<int>(r); }
+  return 0;
 }
 
 int make_tmap_im2col(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax,

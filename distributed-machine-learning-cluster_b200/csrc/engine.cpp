@@ -390,6 +390,9 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       else if (c.smallc) d.amode = A_SMALLC;
       else d.amode = (cfg_.conv_amode == A_GATHER) ? A_GATHER : A_IM2COL;
       if (d.amode == A_IM2COL || d.amode == A_TILED) d.b_tma = 1;
+      d.patch = (cfg_.patch_conv && cfg_.precision == PREC_BF16 && !o.fc && d.amode == A_IM2COL && conv_patch_applicable(g))
+                    ? 1 : 0;
+      if (d.patch) d.BN = 64;
 
       const size_t wn = c.w.size();
       if (cfg_.precision == PREC_FP32) {
@@ -417,7 +420,10 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           d.has_tmB = true;
         }
         void* xin = bufs_[tensor_buf_[o.in]];
-        if (d.amode == A_IM2COL) {
+        if (d.patch) {
+          if (make_tmap_patch(&d.tmA, xin, mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
+          d.has_tmA = true;
+        } else if (d.amode == A_IM2COL) {
           if (make_tmap_im2col(&d.tmA, xin, g, mb_, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_TILED) {
@@ -487,6 +493,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.amode = d.amode;
         a.b_tma = d.b_tma;
         a.persistent = cfg_.persistent;
+        a.patch = d.patch;
         if (cfg_.precision == PREC_FP32) {
           B2I_CUDA(launch_conv_fp32(a, st));
         } else {

@@ -45,11 +45,13 @@ typedef struct b2i_model_config {
   int micro_batch;      /* images per kernel sequence, 0 = max_batch */
   int alexnet_geometry; /* B2I_ALEXNET_* */
   int conv_mode;        /* bf16 path, C % 64 == 0 layers: -1 auto (= 1); 0 cp.async gather, one tile per CTA;
-                           1 TMA im2col, persistent kernel; 2 TMA im2col, one tile per CTA */
+                           1 TMA im2col, persistent kernel; 2 TMA im2col, one tile per CTA
+                           (b2i_op_conv2d only: 3 = halo-patch kernel, 3x3/s1/p1 64->64) */
   int weights_tma;      /* 1: weight tiles through TMA (default), 0: cp.async (gather modes only) */
   int tile_n_max;       /* largest output-channel tile, multiple of 32 in [32,256]; 0 = default */
   int keep_tensors;     /* 1: no activation-buffer reuse, so b2i_model_read_tensor sees every layer */
   int fused_stem;       /* ResNet-18 bf16: 1 (default) = normalise + conv1 + max-pool in one kernel, 0 = three */
+  int patch_conv;       /* 3x3/s1 64->64 layers (ResNet layer1): 1 (default) = halo-patch kernel, 0 = im2col TMA */
 } b2i_model_config;
 
 /* Thread-local description of the last failure on the calling thread. Never NULL. */

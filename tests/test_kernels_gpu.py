@@ -128,6 +128,13 @@ def test_conv_tile_n_sweep(ctx, name, mode, btma, tile_n):
     conv_case(ctx, 2, 14, 14, 128, 256, 3, 1, 1, precision=BF16, conv_mode=mode, weights_tma=btma, tile_n=tile_n, seed=60)
 
 
+def test_conv3x3_c64_halo_patch_kernel(ctx, variant=3):
+    """ResNet layer1 geometry through the halo-patch kernel: taps as shifted descriptor views."""
+    conv_case(ctx, 3, 56, 56, 64, 64, 3, 1, 1, precision=BF16, conv_mode=variant, bn=True, residual=True, relu=True, seed=200)
+    conv_case(ctx, 2, 24, 40, 64, 64, 3, 1, 1, precision=BF16, conv_mode=variant, bn=True, seed=201)      # H not a multiple of 16
+    conv_case(ctx, 5, 7, 8, 64, 64, 3, 1, 1, precision=BF16, conv_mode=variant, bias=True, relu=True, seed=202)
+
+
 @pytest.mark.parametrize("btma", [0, 1], ids=["smallc_cpasyncB", "smallc_tmaB"])
 def test_conv_first_layers_rgb(ctx, btma):
     """C = 3 layers: ResNet conv1 (7x7 s2 p3) and AlexNet features.0 (11x11 s4 p2)."""
