@@ -311,8 +311,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // output tiles.  The TMA warp streams k-blocks of successive tiles through one shared-memory ring
 // without draining between tiles, the MMA thread alternates between two TMEM accumulators, and the
 // four epilogue warps drain accumulator (i & 1) while the tensor core fills the other one.
-//   warp 0: TMA producer   warp 1: TMEM alloc + MMA issue   warps 2-5: epilogue
-constexpr int PTHREADS = 192;
+//   warp 0: TMA producer   warp 1: TMEM alloc + MMA issue   warps 2-9: epilogue
+constexpr int PTHREADS = 64 + 256;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
 
 template <int AMODE>
 __global__ void __launch_bounds__(PTHREADS, 1)
@@ -341,7 +341,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(acc_full_bar(b), 1);
-      mbar_init(acc_empty_bar(b), 4);  // one arrival per epilogue warp
+      mbar_init(acc_empty_bar(b), 8);  // one arrival per epilogue warp
     }
     mbar_fence_init();
   }
@@ -433,11 +433,17 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       const int m = m0 + q * 32 + lane;
       const bool row_ok = m < p.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
-      for (int c = 0; c < n_chunks; ++c) {
+      const int half = (warp - 2) >> 2;          // the two warps of a lane quarter alternate 32-column chunks
+      const int last_c = ((n_chunks - 1 - half) & ~1) + half;
+      if (last_c < 0) {                          // BN = 32: the second warp of the quarter has nothing to drain
+        if (lane == 0) mbar_arrive(acc_empty_bar(buf));
+        continue;
+      }
+      for (int c = half; c < n_chunks; c += 2) {
         uint32_t v[32];
         tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
         tmem_ld_wait();
-        if (c == n_chunks - 1) {
+        if (c == last_c) {
           // every lane's TMEM reads are complete: hand the accumulator back before the stores
           tc_fence_before();
           __syncwarp();
@@ -486,7 +492,9 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm,
       : "memory");
 }
 
-__global__ void __launch_bounds__(PTHREADS, 1)
+constexpr int PATCH_THREADS = 64 + 256;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
+
+__global__ void __launch_bounds__(PATCH_THREADS, 1)
 conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                          const PatchP p) {
   extern __shared__ uint8_t smem_raw[];
@@ -510,7 +518,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       mbar_init(patch_full(b), 1);
       mbar_init(patch_empty(b), 1);
       mbar_init(acc_full(b), 1);
-      mbar_init(acc_empty(b), 4);
+      mbar_init(acc_empty(b), 8);
     }
     mbar_init(w_full, 1);
     mbar_fence_init();
@@ -583,44 +591,43 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       tc_fence_after();
       const int mrow = q * 32 + lane;              // row of the 128-row tile: (output row, column) = (mrow / 8, mrow % 8)
       const int oh = ty * 16 + (mrow >> 3), ow = tx * 8 + (mrow & 7);
-      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 64);
-      uint32_t v0[32], v1[32];
-      tmem_ld32(t_row, v0);
-      tmem_ld32(t_row + 32u, v1);
+      const int c = (warp - 2) >> 2;               // which 32-channel half of the 64 outputs this warp drains
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 64 + c * 32);
+      uint32_t v[32];
+      tmem_ld32(t_row, v);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(b));
       if (oh < p.H && ow < p.W) {
-        const size_t off = ((static_cast<size_t>(n) * p.H + oh) * p.W + ow) * 64;
+        const size_t off = ((static_cast<size_t>(n) * p.H + oh) * p.W + ow) * 64 + c * 32;
+        float f[32];
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          float f[32];
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + c * 32 + j);
+        if (p.residual) {
+          const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
+          uint4 rv[4];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(c == 0 ? v0[j] : v1[j]) + __ldg(p.bias + c * 32 + j);
-          if (p.residual) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off + c * 32);
+          for (int g = 0; g < 4; ++g) rv[g] = __ldg(rp + g);
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              const uint4 rv = __ldg(rp + g);
-              const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+          for (int g = 0; g < 4; ++g) {
+            const uint32_t rr[4] = {rv[g].x, rv[g].y, rv[g].z, rv[g].w};
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                f[g * 8 + e * 2] += bf16_lo(rr[e]);
-                f[g * 8 + e * 2 + 1] += bf16_hi(rr[e]);
-              }
+            for (int e = 0; e < 4; ++e) {
+              f[g * 8 + e * 2] += bf16_lo(rr[e]);
+              f[g * 8 + e * 2 + 1] += bf16_hi(rr[e]);
             }
           }
-          if (p.relu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-          }
-          uint4* op = reinterpret_cast<uint4*>(p.out + off + c * 32);
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            op[g] = make_uint4(pack_bf16x2(f[g * 8 + 0], f[g * 8 + 1]), pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3]),
-                               pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5]), pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]));
         }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        uint4* op = reinterpret_cast<uint4*>(p.out + off);
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          op[g] = make_uint4(pack_bf16x2(f[g * 8 + 0], f[g * 8 + 1]), pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3]),
+                             pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5]), pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]));
       }
     }
   }
@@ -712,7 +719,7 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   p.residual = static_cast<const __nv_bfloat16*>(a.residual);
   p.out = static_cast<__nv_bfloat16*>(a.out);
   const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
-  conv3x3_c64_patch_kernel<<<grid, PTHREADS, smem, st>>>(*tmX, *tmW, p);
+  conv3x3_c64_patch_kernel<<<grid, PATCH_THREADS, smem, st>>>(*tmX, *tmW, p);
   return cudaGetLastError();
 }
 
