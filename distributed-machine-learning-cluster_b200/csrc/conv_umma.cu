@@ -475,6 +475,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
 constexpr int PT_W = 10, PT_H = 18;
 constexpr uint32_t PT_BYTES = ((PT_W * PT_H * 128 + 1023) / 1024) * 1024;   // 23552
 constexpr uint32_t PT_WBYTES = 9 * 64 * 128;                                // resident weights, 73728
+constexpr int PT_BUFS = 4;   // patches in flight: TMA latency (~1.5 us) spans more than one tile of MMA work
 
 struct PatchP {
   int N, H, W, tiles_w, tiles_h, total_tiles, relu;
@@ -498,7 +499,7 @@ __global__ void __launch_bounds__(PATCH_THREADS, 1)
 conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                          const PatchP p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
+  __shared__ __align__(8) uint64_t bars[2 * PT_BUFS + 5];  // patch_full[], patch_empty[], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5;
@@ -508,15 +509,17 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   const uint32_t patch0 = base + PT_WBYTES;
   const uint32_t bar0 = smem_u32(bars);
   auto patch_full = [&](int b) { return bar0 + 8u * b; };
-  auto patch_empty = [&](int b) { return bar0 + 8u * (2 + b); };
-  auto acc_full = [&](int b) { return bar0 + 8u * (4 + b); };
-  auto acc_empty = [&](int b) { return bar0 + 8u * (6 + b); };
-  const uint32_t w_full = bar0 + 8u * 8;
+  auto patch_empty = [&](int b) { return bar0 + 8u * (PT_BUFS + b); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (2 * PT_BUFS + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (2 * PT_BUFS + 2 + b); };
+  const uint32_t w_full = bar0 + 8u * (2 * PT_BUFS + 4);
 
   if (threadIdx.x == 0) {
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < PT_BUFS; ++b) {
       mbar_init(patch_full(b), 1);
       mbar_init(patch_empty(b), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
       mbar_init(acc_full(b), 1);
       mbar_init(acc_empty(b), 8);
     }
@@ -540,13 +543,13 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       for (int tap = 0; tap < 9; ++tap) tma_load_2d(w_smem + tap * 8192u, &tmW, w_full, tap * 64, 0);
       int i = 0;
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
-        const int b = i & 1;
+        const int pb = i % PT_BUFS;
         const int n = t / tiles_per_img;
         const int rem = t - n * tiles_per_img;
         const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
-        mbar_wait(patch_empty(b), ((i >> 1) & 1) ^ 1);
-        mbar_expect_tx(patch_full(b), PT_W * PT_H * 128);
-        tma_load_4d(patch0 + b * PT_BYTES, &tmX, patch_full(b), 0, tx * 8 - 1, ty * 16 - 1, n);
+        mbar_wait(patch_empty(pb), ((i / PT_BUFS) & 1) ^ 1);
+        mbar_expect_tx(patch_full(pb), PT_W * PT_H * 128);
+        tma_load_4d(patch0 + pb * PT_BYTES, &tmX, patch_full(pb), 0, tx * 8 - 1, ty * 16 - 1, n);
       }
     }
   } else if (warp == 1) {
@@ -556,11 +559,12 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
+      const int pbuf = i % PT_BUFS;
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
-      mbar_wait(patch_full(b), (i >> 1) & 1);
+      mbar_wait(patch_full(pbuf), (i / PT_BUFS) & 1);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t pb = patch0 + b * PT_BYTES;
+        const uint32_t pb = patch0 + pbuf * PT_BYTES;
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 64);
 #pragma unroll
         for (int tap = 0; tap < 9; ++tap) {
@@ -574,7 +578,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
           for (int k = 0; k < 4; ++k)
             umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (tap | k) != 0 ? 1u : 0u);
         }
-        umma_commit(patch_empty(b));
+        umma_commit(patch_empty(pbuf));
         umma_commit(acc_full(b));
       }
       __syncwarp();
@@ -699,7 +703,7 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
-  const size_t smem = PT_WBYTES + 2 * PT_BYTES + 1024;
+  const size_t smem = PT_WBYTES + PT_BUFS * PT_BYTES + 1024;
   if (!attr_set[dev]) {
     cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
