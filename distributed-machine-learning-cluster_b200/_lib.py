@@ -25,6 +25,7 @@ class ModelConfig(ctypes.Structure):
         ("keep_tensors", ctypes.c_int),
         ("fused_stem", ctypes.c_int),
         ("patch_conv", ctypes.c_int),
+        ("pair_mma", ctypes.c_int),
     ]
 
 

@@ -127,6 +127,7 @@ void b2i_default_config(b2i_model_config* cfg) {
   cfg->keep_tensors = 0;
   cfg->fused_stem = 1;
   cfg->patch_conv = 1;
+  cfg->pair_mma = 0;
 }
 
 int b2i_ot_inspect(const char* path, char* names_out, size_t cap) {
@@ -192,6 +193,7 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   ec.conv_amode = cfg.conv_mode == 2 ? 1 : cfg.conv_mode;
   ec.persistent = cfg.conv_mode == 2 ? 0 : 1;
   ec.patch_conv = cfg.patch_conv;
+  ec.pair_mma = cfg.pair_mma;
   ec.b_tma = cfg.weights_tma;
   if (cfg.tile_n_max > 0) ec.bn_max = cfg.tile_n_max;
   ec.keep_tensors = cfg.keep_tensors;
@@ -433,6 +435,7 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   a.amode = cs.smallc ? A_SMALLC : (conv_mode >= 1 ? A_IM2COL : A_GATHER);
   a.persistent = conv_mode == 2 ? 0 : 1;
   a.b_tma = (a.amode == A_IM2COL) ? 1 : weights_tma;
+  if (conv_mode == 5) a.pair = 1;
   if (conv_mode == 3) {
     if (!bf16 || !conv_patch_applicable(g)) return fail(B2I_EINVAL, "conv_mode 3 (halo patch) needs bf16, 3x3 s1 p1, 64 -> 64 channels");
     a.patch = 1;
@@ -443,7 +446,7 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   } else {
     CUtensorMap tmA, tmB;
     const char* terr = "";
-    if (a.b_tma && make_tmap_weights(&tmB, dw.p, cs.Cout_pad, cs.K, a.BN, &terr)) return fail(B2I_ECUDA, terr);
+    if (a.b_tma && make_tmap_weights(&tmB, dw.p, cs.Cout_pad, cs.K, (a.pair && a.BN >= 64) ? a.BN / 2 : a.BN, &terr)) return fail(B2I_ECUDA, terr);
     if (a.patch) {
       if (make_tmap_patch(&tmA, dx.p, N, H, W, &terr)) return fail(B2I_ECUDA, terr);
     } else if (a.amode == A_IM2COL && make_tmap_im2col(&tmA, dx.p, g, N, &terr)) {

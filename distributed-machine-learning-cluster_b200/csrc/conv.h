@@ -43,6 +43,7 @@ struct ConvArgs {
   int amode = A_GATHER;
   int b_tma = 1;                  // 1: weights through TMA, 0: cp.async gather (A_GATHER / A_SMALLC only)
   int persistent = 1;             // TMA modes: persistent CTA-per-SM kernel with double-buffered TMEM
+  int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)
 };
 

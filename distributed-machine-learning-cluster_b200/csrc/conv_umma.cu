@@ -13,6 +13,8 @@
 // Operand tiles are K-major rows of 64 bf16 (128 bytes) with the 128-byte swizzle, which is what
 // both TMA (CU_TENSOR_MAP_SWIZZLE_128B) and the hand gather produce and what the UMMA shared-memory
 // descriptors in ptx.cuh declare.
+#include <algorithm>
+
 #include "conv.h"
 #include "ptx.cuh"
 
@@ -463,6 +465,219 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
 }
 
 // ------------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): two CTAs on the two SMs of a TPC compute one 256 x BN tile.
+// Each CTA loads its own 128 rows of A and HALF of the weight tile; one thread of the leader CTA
+// issues M=256 MMAs that read both halves, so per SM the operand fetch per K step drops from
+// 4 KB + 32*BN B to 4 KB + 16*BN B.  Barriers: the leader's `full` barrier collects the TMA bytes of
+// both CTAs (peer bit cleared in the barrier address), tcgen05.commit is multicast to both CTAs'
+// `empty` / `acc_full` barriers, and both CTAs' epilogue warps arrive on the leader's `acc_empty`.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // shared::cluster address of the same offset in the even CTA
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4}], [%2];" ::"r"(dst), "l"(tm), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_4d_2sm(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c,
+                                                       int w, int h, int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst), "l"(tm), "r"(bar & kPeerBitMask), "r"(c), "r"(w),
+      "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar),
+      "r"(cta)
+      : "memory");
+}
+
+template <int AMODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
+conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const KP p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int half_n = p.BN >> 1;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_tile_bytes = static_cast<uint32_t>(half_n) * 128u;
+  const uint32_t stage_bytes = A_TILE_BYTES + b_tile_bytes;
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
+  auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + b); };
+  auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
+  const int total_tiles = p.tiles_m * p.tiles_n;   // tiles_m counts 256-row tiles here
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full_bar(s), 2);    // leader's expect_tx arrive + the peer's arrive
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full_bar(b), 1);
+      mbar_init(acc_empty_bar(b), 16);  // 8 epilogue warps in each of the two CTAs
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
+      const int ohw = p.OH * p.OW;
+      int s = 0, ph = 0;
+      for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+        const int m0 = (t / p.tiles_n) * 256 + static_cast<int>(rank) * BM;
+        const int n0 = (t % p.tiles_n) * p.BN + static_cast<int>(rank) * half_n;
+        int iw_base = 0, ih_base = 0, n_base = 0;
+        if (AMODE == A_IM2COL) {
+          n_base = m0 / ohw;
+          const int rem = m0 - n_base * ohw;
+          const int oh = rem / p.OW;
+          const int ow = rem - oh * p.OW;
+          ih_base = oh * p.stride - p.pad;
+          iw_base = ow * p.stride - p.pad;
+        }
+        int cblk = 0, r = 0, sx = 0;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(empty_bar(s), ph ^ 1);
+          const uint32_t a_s = smem_base + s * stage_bytes;
+          if (leader) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
+          else mbar_arrive_cluster(full_bar(s), 0);
+          if (AMODE == A_IM2COL) {
+            tma_load_im2col_4d_2sm(a_s, &tmA, full_bar(s), cblk << 6, iw_base, ih_base, n_base,
+                                   static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
+            if (++cblk == cpb) {
+              cblk = 0;
+              if (++sx == p.S) { sx = 0; ++r; }
+            }
+          } else {
+            tma_load_2d_2sm(a_s, &tmA, full_bar(s), kb * BK, m0);
+          }
+          tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader) {
+      const uint32_t idesc = umma_idesc_bf16(256, p.BN);
+      int s = 0, ph = 0, i = 0;
+      for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
+        const int buf = i & 1;
+        mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(full_bar(s), ph);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t a_s = smem_base + s * stage_bytes;
+            const uint64_t adesc = umma_smem_desc_sw128(a_s);
+            const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_2sm(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit_2sm(empty_bar(s));
+            if (kb == p.num_kb - 1) umma_commit_2sm(acc_full_bar(buf));
+          }
+          __syncwarp();
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int n_chunks = p.BN >> 5;
+    const int last_c = ((n_chunks - 1 - half) & ~1) + half;
+    int i = 0;
+    for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
+      const int buf = i & 1;
+      const int m0 = (t / p.tiles_n) * 256 + static_cast<int>(rank) * BM;
+      const int n0 = (t % p.tiles_n) * p.BN;
+      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
+      tc_fence_after();
+      const int m = m0 + q * 32 + lane;
+      const bool row_ok = m < p.M;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
+      for (int c = half; c < n_chunks; c += 2) {
+        uint32_t v[32];
+        tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+        tmem_ld_wait();
+        if (c == last_c) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (leader) mbar_arrive(acc_empty_bar(buf));
+            else mbar_arrive_cluster(acc_empty_bar(buf), 0);
+          }
+        }
+        if (row_ok) epilogue_chunk(p, m, n0 + c * 32, v);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // the peer may still be arriving on / reading this CTA's barriers and smem
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // 3x3 / stride 1 / pad 1 convolution with 64 input and 64 output channels (ResNet layer1), reading
 // the nine filter taps as SHIFTED VIEWS of one halo patch instead of nine im2col loads.
 //
@@ -696,6 +911,36 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   return cudaGetLastError();
 }
 
+template <int AMODE>
+cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB, cudaStream_t st) {
+  static bool attr_set[16] = {};
+  static int sm_count[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 16) return cudaErrorInvalidDevice;
+  auto kern = conv_umma_pair_kernel<AMODE>;
+  if (!attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  KP p;
+  fill_kp(&p, a);
+  p.tiles_m = (a.g.M + 255) / 256;
+  const int stage = A_TILE_BYTES + (a.BN / 2) * 128;
+  p.stages = std::min(MAX_STAGES, (210 * 1024) / stage);
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
+  p.tmem_cols = cols;
+  const int total = p.tiles_m * p.tiles_n;
+  int grid = std::min(2 * total, sm_count[dev] & ~1);
+  const size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
+  kern<<<dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, p);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmW,
                          cudaStream_t st) {
   static bool attr_set[16] = {};
@@ -791,10 +1036,12 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
                      : launch_t<A_SMALLC, false>(a, nullptr, nullptr, st);
     case A_IM2COL:
       if (g.C % 64 || g.K != g.R * g.S * g.C || !tmA || !tmB) return cudaErrorInvalidValue;
+      if (a.pair && a.BN >= 64) return launch_pair<A_IM2COL>(a, tmA, tmB, st);
       return a.persistent ? launch_persistent<A_IM2COL>(a, tmA, tmB, st)
                           : launch_t<A_IM2COL, true>(a, tmA, tmB, st);
     case A_TILED:
       if (!tmA || !tmB) return cudaErrorInvalidValue;
+      if (a.pair && a.BN >= 64) return launch_pair<A_TILED>(a, tmA, tmB, st);
       return a.persistent ? launch_persistent<A_TILED>(a, tmA, tmB, st)
                           : launch_t<A_TILED, true>(a, tmA, tmB, st);
   }

@@ -393,6 +393,8 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       d.patch = (cfg_.patch_conv && cfg_.precision == PREC_BF16 && !o.fc && d.amode == A_IM2COL && conv_patch_applicable(g))
                     ? 1 : 0;
       if (d.patch) d.BN = 64;
+      d.pair = (cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && d.BN >= cfg_.pair_mma &&
+                (d.amode == A_IM2COL || d.amode == A_TILED)) ? 1 : 0;
 
       const size_t wn = c.w.size();
       if (cfg_.precision == PREC_FP32) {
@@ -416,7 +418,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       if (cfg_.precision == PREC_BF16) {
         const char* terr = "";
         if (d.b_tma) {
-          if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
+          if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.pair ? d.BN / 2 : d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmB = true;
         }
         void* xin = bufs_[tensor_buf_[o.in]];
@@ -494,6 +496,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.b_tma = d.b_tma;
         a.persistent = cfg_.persistent;
         a.patch = d.patch;
+        a.pair = d.pair;
         if (cfg_.precision == PREC_FP32) {
           B2I_CUDA(launch_conv_fp32(a, st));
         } else {

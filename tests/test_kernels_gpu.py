@@ -85,7 +85,7 @@ def conv_case(ctx, N, H, W, C, Cout, k, stride, pad, *, precision, conv_mode, we
 # ---- tcgen05 path: every A-operand mode on the same geometries ------------------------------
 IM2COL_ONE_TILE = 2
 MODES = [("gather_cpasyncB", GATHER, 0), ("gather_tmaB", GATHER, 1), ("im2col", IM2COL, 1),
-         ("im2col_onetile", IM2COL_ONE_TILE, 1)]
+         ("im2col_onetile", IM2COL_ONE_TILE, 1), ("pair_im2col", 5, 1)]
 
 
 @pytest.mark.parametrize("name,mode,btma", MODES, ids=[m[0] for m in MODES])
