@@ -283,19 +283,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int kb = 0; kb < p.num_kb; ++kb) {
       mbar_wait(full_bar(s), ph);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t a_s = smem_base + s * stage_bytes;
         const uint64_t adesc = umma_smem_desc_sw128(a_s);
         const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k) {
           // advancing 16 bf16 (32 bytes) along K inside the swizzle atom: +2 in 16-byte units
-          umma_bf16(tmem_base, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_bf16_elect(tmem_base, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
         }
-        umma_commit(empty_bar(s));  // smem slot reusable once these MMAs have read it
-        if (kb == p.num_kb - 1) umma_commit(tmem_full_bar);
+        umma_commit_elect(empty_bar(s));  // smem slot reusable once these MMAs have read it
+        if (kb == p.num_kb - 1) umma_commit_elect(tmem_full_bar);
       }
-      __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1; }
     }
   }
@@ -408,17 +407,16 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       for (int kb = 0; kb < p.num_kb; ++kb) {
         mbar_wait(full_bar(s), ph);
         tc_fence_after();
-        if (lane == 0) {
+        {
           const uint32_t a_s = smem_base + s * stage_bytes;
           const uint64_t adesc = umma_smem_desc_sw128(a_s);
           const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(empty_bar(s));
-          if (kb == p.num_kb - 1) umma_commit(acc_full_bar(buf));
+            umma_bf16_elect(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit_elect(empty_bar(s));
+          if (kb == p.num_kb - 1) umma_commit_elect(acc_full_bar(buf));
         }
-        __syncwarp();
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
     }
@@ -498,15 +496,18 @@ __device__ __forceinline__ void tma_load_im2col_4d_2sm(uint32_t dst, const CUten
 __device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                               uint32_t accumulate) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
+      "{\n\t.reg .pred pe, p;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "@pe tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
   asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "{\n\t.reg .pred pe;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "@pe tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(bar),
       "h"(static_cast<uint16_t>(3))
       : "memory");
 }
@@ -621,7 +622,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(full_bar(s), ph);
           tc_fence_after();
-          if (lane == 0) {
+          {
             const uint32_t a_s = smem_base + s * stage_bytes;
             const uint64_t adesc = umma_smem_desc_sw128(a_s);
             const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
@@ -631,7 +632,6 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             umma_commit_2sm(empty_bar(s));
             if (kb == p.num_kb - 1) umma_commit_2sm(acc_full_bar(buf));
           }
-          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -769,8 +769,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     }
   } else if (warp == 1) {
     const uint32_t idesc = umma_idesc_bf16(128, 64);
-    if (lane == 0) mbar_wait(w_full, 0);
-    __syncwarp();
+    mbar_wait(w_full, 0);
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
@@ -778,7 +777,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
       mbar_wait(patch_full(pbuf), (i / PT_BUFS) & 1);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t pb = patch0 + pbuf * PT_BYTES;
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 64);
 #pragma unroll
@@ -791,12 +790,11 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
           const uint64_t bdesc = umma_smem_desc_sw128(w_smem + tap * 8192u);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (tap | k) != 0 ? 1u : 0u);
+            umma_bf16_elect(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (tap | k) != 0 ? 1u : 0u);
         }
-        umma_commit(patch_empty(pbuf));
-        umma_commit(acc_full(b));
+        umma_commit_elect(patch_empty(pbuf));
+        umma_commit_elect(acc_full(b));
       }
-      __syncwarp();
     }
   } else {
     const int q = warp & 3;

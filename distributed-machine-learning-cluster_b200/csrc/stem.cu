@@ -113,7 +113,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
       mbar_wait(patch_full(b), (i >> 1) & 1);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t pbase = patch0 + b * PATCH_BYTES;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {          // conv columns 0-7 / 8-15 of the 16x16 patch
@@ -122,12 +122,11 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
           for (int j = 0; j < 14; ++j) {        // K step j: filter row j/2, taps 4*(j&1) .. +3
             const uint32_t a_addr = pbase + static_cast<uint32_t>(h * 128 + (j >> 1) * PATCH_ROW_BYTES + (j & 1) * 32);
             const uint64_t bdesc = umma_smem_desc_sw128(b_smem + (j >> 2) * 8192u) + 2u * (j & 3);
-            umma_bf16(d_tmem, patch_desc(a_addr), bdesc, idesc, j != 0 ? 1u : 0u);
+            umma_bf16_elect(d_tmem, patch_desc(a_addr), bdesc, idesc, j != 0 ? 1u : 0u);
           }
         }
-        umma_commit(acc_full(b));
+        umma_commit_elect(acc_full(b));
       }
-      __syncwarp();
     }
   } else {
     // ------------------------------------------------------------------ patch loaders / epilogue
