@@ -7,17 +7,19 @@
 // per image through HBM and were 43 % of the step; fused, the kernel reads the 150 KB u8 image and
 // writes the 401 KB pooled map.
 //
-// One CTA (two co-resident per SM) produces a 7x7 pooled tile = a 15x15 patch of conv outputs
-// (1 halo row/column, recomputed), computed as two M=128 MMAs (16 conv rows x 8 conv columns each):
-//   load   256 threads stage the 37x40-pixel input patch in shared memory as normalised bf16x4
-//          pixels (8 bytes), double buffered: the patch of tile i+1 is fetched while tile i computes
-//   MMA    warp 8 issues 2 x 14 tcgen05.mma (K = 16 = four taps each) whose A descriptors point
-//          STRAIGHT INTO THE PATCH: with 8-byte pixels and stride 2, the tap window of the next conv
-//          pixel starts 16 bytes further, which is exactly the canonical no-swizzle K-major core
-//          matrix (8 rows x 16 B); the next conv row is 640 B further (SBO), the next two taps 16 B
-//          (LBO), the next filter row 320 B (new descriptor).  No im2col matrix is ever materialised.
-//   drain  TMEM -> registers -> +bias, ReLU, bf16 -> shared staging tile (TMEM double buffered)
-//   pool   3x3/s2 max over the staging tile -> 16-byte stores of the pooled tile
+// One CTA (two co-resident per SM) produces 7x7 pooled tiles = 15x15 patches of conv outputs
+// (1 halo row/column, recomputed), each computed as two M=128 MMAs (16 conv rows x 8 conv columns).
+// Three groups of warps run concurrently, connected by mbarriers, each on its own tile:
+//   loaders (4 warps)  stage the 37x40-pixel input patch of tile i+1 in shared memory as normalised
+//                      bf16x4 pixels (8 bytes), double buffered
+//   MMA (1 warp)       issues 2 x 14 tcgen05.mma (K = 16 = four taps each) whose A descriptors point
+//                      STRAIGHT INTO THE PATCH: with 8-byte pixels and stride 2, the tap window of the
+//                      next conv pixel starts 16 bytes further, which is exactly the canonical
+//                      no-swizzle K-major core matrix (8 rows x 16 B); the next conv row is 640 B
+//                      further (SBO), the next two taps 16 B (LBO), the next filter row 320 B (new
+//                      descriptor).  No im2col matrix is ever materialised.  TMEM double buffered.
+//   drain (8 warps)    TMEM -> registers -> +bias, ReLU, bf16 -> shared staging tile, then the
+//                      3x3/s2 max over the staging tile -> 16-byte stores of the pooled tile
 // Weights ([64][256] bf16, K order (r, s<8, c<4), rows r = 7 / taps s = 7 / channel 3 are zero) are
 // loaded once per CTA by TMA into the 128B-swizzled layout.
 #include "conv.h"
@@ -27,8 +29,9 @@
 namespace b2i {
 namespace {
 
-constexpr int ST_BUILDERS = 256;
-constexpr int ST_THREADS = ST_BUILDERS + 32;
+constexpr int ST_DRAIN = 256;                      // warps 0-7
+constexpr int ST_LOADERS = 128;                    // warps 9-12
+constexpr int ST_THREADS = ST_DRAIN + 32 + ST_LOADERS;
 constexpr int PATCH_H = 37, PATCH_W = 40;          // pixels of 8 bytes (bf16 r, g, b, 0)
 constexpr uint32_t PATCH_ROW_BYTES = PATCH_W * 8;  // 320
 constexpr uint32_t PATCH_BYTES = ((PATCH_H * PATCH_W * 8 + 127) / 128) * 128;
@@ -59,7 +62,7 @@ __device__ __forceinline__ uint64_t patch_desc(uint32_t saddr) {
 __global__ void __launch_bounds__(ST_THREADS, 2)
 stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[7];  // patch_full[2], acc_full[2], acc_empty[2], w_full
+  __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
   __shared__ float lut[3][256];               // (u/255 - mean)/std per channel, exact fp32 ops
 
@@ -72,13 +75,15 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   const uint32_t patch0 = stage + STAGE_BYTES;
   const uint32_t bar0 = smem_u32(bars);
   auto patch_full = [&](int b) { return bar0 + 8u * b; };
-  auto acc_full = [&](int b) { return bar0 + 8u * (2 + b); };
-  auto acc_empty = [&](int b) { return bar0 + 8u * (4 + b); };
-  const uint32_t w_full = bar0 + 8u * 6;
+  auto patch_empty = [&](int b) { return bar0 + 8u * (2 + b); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (4 + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (6 + b); };
+  const uint32_t w_full = bar0 + 8u * 8;
 
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
-      mbar_init(patch_full(b), ST_BUILDERS);
+      mbar_init(patch_full(b), ST_LOADERS);
+      mbar_init(patch_empty(b), 1);
       mbar_init(acc_full(b), 1);
       mbar_init(acc_empty(b), 8);
     }
@@ -103,9 +108,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       tma_prefetch_desc(&tmW);
       mbar_expect_tx(w_full, B_BYTES);
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(b_smem + kb * 8192u, &tmW, w_full, kb * 64, 0);
-      mbar_wait(w_full, 0);
     }
-    __syncwarp();
+    mbar_wait(w_full, 0);
     const uint32_t idesc = umma_idesc_bf16(128, 64);
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
@@ -113,74 +117,77 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
       mbar_wait(patch_full(b), (i >> 1) & 1);
       tc_fence_after();
-      {
-        const uint32_t pbase = patch0 + b * PATCH_BYTES;
+      const uint32_t pbase = patch0 + b * PATCH_BYTES;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {          // conv columns 0-7 / 8-15 of the 16x16 patch
-          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + h * 64);
+      for (int h = 0; h < 2; ++h) {          // conv columns 0-7 / 8-15 of the 16x16 patch
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + h * 64);
 #pragma unroll
-          for (int j = 0; j < 14; ++j) {        // K step j: filter row j/2, taps 4*(j&1) .. +3
-            const uint32_t a_addr = pbase + static_cast<uint32_t>(h * 128 + (j >> 1) * PATCH_ROW_BYTES + (j & 1) * 32);
-            const uint64_t bdesc = umma_smem_desc_sw128(b_smem + (j >> 2) * 8192u) + 2u * (j & 3);
-            umma_bf16_elect(d_tmem, patch_desc(a_addr), bdesc, idesc, j != 0 ? 1u : 0u);
-          }
+        for (int j = 0; j < 14; ++j) {        // K step j: filter row j/2, taps 4*(j&1) .. +3
+          const uint32_t a_addr = pbase + static_cast<uint32_t>(h * 128 + (j >> 1) * PATCH_ROW_BYTES + (j & 1) * 32);
+          const uint64_t bdesc = umma_smem_desc_sw128(b_smem + (j >> 2) * 8192u) + 2u * (j & 3);
+          umma_bf16_elect(d_tmem, patch_desc(a_addr), bdesc, idesc, j != 0 ? 1u : 0u);
         }
-        umma_commit_elect(acc_full(b));
       }
+      umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
+      umma_commit_elect(acc_full(b));
     }
-  } else {
-    // ------------------------------------------------------------------ patch loaders / epilogue
-    const int h = warp >> 2, q = warp & 3;
+  } else if (warp > 8) {
+    // ------------------------------------------------------------------ patch loaders
+    const int lt = tid - (ST_DRAIN + 32);
     uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));  // generic pointer to `base`
-
-    auto load_patch = [&](int t, int b) {
+    constexpr int ROUNDS = (PATCH_H * PATCH_W + ST_LOADERS - 1) / ST_LOADERS;   // 12
+    constexpr int HALF = ROUNDS / 2;
+    int i = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+      const int b = i & 1;
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
       const int ih0 = 28 * pty - 5, iw0 = 28 * ptx - 5;   // input row / col of patch pixel (0, 0)
       const uint8_t* img = p.in + static_cast<size_t>(n) * (224 * 224 * 3);
-      constexpr int ROUNDS = (PATCH_H * PATCH_W + ST_BUILDERS - 1) / ST_BUILDERS;
-      uint32_t r0[ROUNDS], r1[ROUNDS], r2[ROUNDS];
-#pragma unroll
-      for (int k = 0; k < ROUNDS; ++k) {       // all global loads first: one exposed latency
-        const int e = tid + k * ST_BUILDERS;
-        const int py = e / PATCH_W, px = e - py * PATCH_W;
-        const int ih = ih0 + py, iw = iw0 + px;
-        r0[k] = 0xFFFFFFFFu;
-        r1[k] = r2[k] = 0;
-        if (e < PATCH_H * PATCH_W && ih >= 0 && ih < 224 && iw >= 0 && iw < 224) {
-          const uint8_t* s3 = img + (ih * 224 + iw) * 3;
-          r0[k] = __ldg(s3);
-          r1[k] = __ldg(s3 + 1);
-          r2[k] = __ldg(s3 + 2);
-        }
-      }
       uint8_t* dst = gen_base + B_BYTES + STAGE_BYTES + b * PATCH_BYTES;
+      mbar_wait(patch_empty(b), ((i >> 1) & 1) ^ 1);
 #pragma unroll
-      for (int k = 0; k < ROUNDS; ++k) {
-        const int e = tid + k * ST_BUILDERS;
-        if (e < PATCH_H * PATCH_W) {
-          uint2 v = make_uint2(0u, 0u);        // outside the image: the conv's zero padding
-          if (r0[k] != 0xFFFFFFFFu) {
-            v.x = pack_bf16x2(lut[0][r0[k]], lut[1][r1[k]]);
-            v.y = pack_bf16x2(lut[2][r2[k]], 0.f);
+      for (int part = 0; part < 2; ++part) {   // two batches of 6 rounds: 18 byte loads in flight per thread
+        uint32_t r0[HALF], r1[HALF], r2[HALF];
+#pragma unroll
+        for (int k = 0; k < HALF; ++k) {
+          const int e = lt + (part * HALF + k) * ST_LOADERS;
+          const int py = e / PATCH_W, px = e - py * PATCH_W;
+          const int ih = ih0 + py, iw = iw0 + px;
+          r0[k] = 0xFFFFFFFFu;
+          r1[k] = r2[k] = 0;
+          if (e < PATCH_H * PATCH_W && ih >= 0 && ih < 224 && iw >= 0 && iw < 224) {
+            const uint8_t* s3 = img + (ih * 224 + iw) * 3;
+            r0[k] = __ldg(s3);
+            r1[k] = __ldg(s3 + 1);
+            r2[k] = __ldg(s3 + 2);
           }
-          *reinterpret_cast<uint2*>(dst + e * 8) = v;
+        }
+#pragma unroll
+        for (int k = 0; k < HALF; ++k) {
+          const int e = lt + (part * HALF + k) * ST_LOADERS;
+          if (e < PATCH_H * PATCH_W) {
+            uint2 v = make_uint2(0u, 0u);        // outside the image: the conv's zero padding
+            if (r0[k] != 0xFFFFFFFFu) {
+              v.x = pack_bf16x2(lut[0][r0[k]], lut[1][r1[k]]);
+              v.y = pack_bf16x2(lut[2][r2[k]], 0.f);
+            }
+            *reinterpret_cast<uint2*>(dst + e * 8) = v;
+          }
         }
       }
       fence_proxy_async_smem();                // generic-proxy stores -> visible to the tensor core
       mbar_arrive(patch_full(b));
-    };
-
+    }
+  } else {
+    // ------------------------------------------------------------------ drain + pool (warps 0-7)
+    const int h = warp >> 2, q = warp & 3;
     int i = 0;
-    if (static_cast<int>(blockIdx.x) < p.total_tiles) load_patch(blockIdx.x, 0);
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
       const int oh0 = 14 * pty - 1, ow0 = 14 * ptx - 1;   // conv row / col of patch slot (0, 0)
-      // the MMAs of tile i-1 (which read the other patch buffer) finished before its acc_full,
-      // which these threads waited on last iteration: that buffer may be overwritten now
-      if (t + static_cast<int>(gridDim.x) < p.total_tiles) load_patch(t + gridDim.x, b ^ 1);
 
       // accumulators -> +bias, ReLU, bf16 -> staging tile [ly*16 + lx][64], 16-byte chunks XOR-swizzled
       mbar_wait(acc_full(b), (i >> 1) & 1);
@@ -191,21 +198,22 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
         const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 128 + h * 64);
         const uint32_t st_row = stage + static_cast<uint32_t>(srow) * 128u;
         const uint32_t sw = static_cast<uint32_t>(srow & 7);
-        uint32_t v0[32], v1[32];
-        tmem_ld32(t_row, v0);
-        tmem_ld32(t_row + 32u, v1);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(acc_empty(b));          // TMEM buffer free for tile i+2
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
+          uint32_t v[32];
+          tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+          tmem_ld_wait();
+          if (c == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty(b));      // TMEM buffer free for tile i+2
+          }
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float f[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e)
-              f[e] = fmaxf(__uint_as_float(c == 0 ? v0[g * 8 + e] : v1[g * 8 + e]) + __ldg(p.bias + c * 32 + g * 8 + e), 0.f);
+              f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + __ldg(p.bias + c * 32 + g * 8 + e), 0.f);
             const uint32_t chunk = static_cast<uint32_t>(c * 4 + g);
             asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_row + ((chunk ^ sw) << 4)),
                          "r"(pack_bf16x2(f[0], f[1])), "r"(pack_bf16x2(f[2], f[3])),
@@ -213,7 +221,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
           }
         }
       }
-      asm volatile("bar.sync 1, %0;" ::"n"(ST_BUILDERS) : "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(ST_DRAIN) : "memory");
       // 3x3 stride-2 max over the staging tile -> pooled 7x7x64, two 16-byte chunks per thread
       if (tid < 49 * 4) {
         const int pp = tid >> 2, c8 = (tid & 3) * 2;
@@ -253,7 +261,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
           o[cc] = make_uint4(pack_bf16x2(mx[cc * 8 + 0], mx[cc * 8 + 1]), pack_bf16x2(mx[cc * 8 + 2], mx[cc * 8 + 3]),
                              pack_bf16x2(mx[cc * 8 + 4], mx[cc * 8 + 5]), pack_bf16x2(mx[cc * 8 + 6], mx[cc * 8 + 7]));
       }
-      asm volatile("bar.sync 1, %0;" ::"n"(ST_BUILDERS) : "memory");  // staging tile is rewritten next iteration
+      asm volatile("bar.sync 1, %0;" ::"n"(ST_DRAIN) : "memory");  // staging tile is rewritten next iteration
     }
   }
 
