@@ -44,8 +44,15 @@ struct KP {
 // One output row x 32 consecutive channels: acc + bias (+ residual) -> ReLU -> store.
 __device__ __forceinline__ void epilogue_chunk(const KP& p, int m, int nb, const uint32_t (&v)[32]) {
   float f[32];
+  const float4* b4 = reinterpret_cast<const float4*>(p.bias + nb);   // bias is padded to Cout_pad: always in range
 #pragma unroll
-  for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + nb + j);
+  for (int j = 0; j < 8; ++j) {
+    const float4 b = __ldg(b4 + j);
+    f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+    f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+    f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+    f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+  }
   if (p.out_fp32) {
     float* o = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
     if (p.relu) {
@@ -819,8 +826,15 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       if (oh < p.H && ow < p.W) {
         const size_t off = ((static_cast<size_t>(n) * p.H + oh) * p.W + ow) * 64 + c * 32;
         float f[32];
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias + c * 32);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + c * 32 + j);
+        for (int j = 0; j < 8; ++j) {
+          const float4 b = __ldg(b4 + j);
+          f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+          f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+          f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+          f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+        }
         if (p.residual) {
           const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
           uint4 rv[4];

@@ -65,6 +65,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
   __shared__ float lut[3][256];               // (u/255 - mean)/std per channel, exact fp32 ops
+  __shared__ __align__(16) float sbias[64];
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -96,6 +97,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     const float sd = c == 0 ? 0.229f : (c == 1 ? 0.224f : 0.225f);
     lut[c][u] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(u), 255.0f), mean), sd);
   }
+  if (tid < 64) sbias[tid] = __ldg(p.bias + tid);
   if (warp == 8) tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
   tc_fence_before();
   __syncthreads();
@@ -211,9 +213,11 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float f[8];
+            const float4 b0 = *reinterpret_cast<const float4*>(&sbias[c * 32 + g * 8]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&sbias[c * 32 + g * 8 + 4]);
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-            for (int e = 0; e < 8; ++e)
-              f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + __ldg(p.bias + c * 32 + g * 8 + e), 0.f);
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + bb[e], 0.f);
             const uint32_t chunk = static_cast<uint32_t>(c * 4 + g);
             asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_row + ((chunk ^ sw) << 4)),
                          "r"(pack_bf16x2(f[0], f[1])), "r"(pack_bf16x2(f[2], f[3])),
@@ -226,9 +230,10 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       if (tid < 49 * 4) {
         const int pp = tid >> 2, c8 = (tid & 3) * 2;
         const int py = pp / 7, px = pp - py * 7;
-        float mx[16];
+        // packed bf16x2 max: values are post-ReLU (>= 0) and the centre tap is always valid, so 0 is a safe start
+        __nv_bfloat162 mx[8];
 #pragma unroll
-        for (int e = 0; e < 16; ++e) mx[e] = 0.f;  // post-ReLU values are >= 0 and the centre tap is always valid
+        for (int e = 0; e < 8; ++e) mx[e] = __floats2bfloat162_rn(0.f, 0.f);
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy) {
           const int cy = 2 * py + dy;
@@ -243,23 +248,19 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
 #pragma unroll
             for (int cc = 0; cc < 2; ++cc) {
               const uint32_t a = stage + static_cast<uint32_t>(row) * 128u + ((static_cast<uint32_t>(c8 + cc) ^ (row & 7)) << 4);
-              uint32_t x0, x1, x2, x3;
-              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(a));
-              const uint32_t xs[4] = {x0, x1, x2, x3};
+              uint32_t xs[4];
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(xs[0]), "=r"(xs[1]), "=r"(xs[2]), "=r"(xs[3]) : "r"(a));
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                mx[cc * 8 + 2 * e] = fmaxf(mx[cc * 8 + 2 * e], bf16_lo(xs[e]));
-                mx[cc * 8 + 2 * e + 1] = fmaxf(mx[cc * 8 + 2 * e + 1], bf16_hi(xs[e]));
-              }
+              for (int e = 0; e < 4; ++e)
+                mx[cc * 4 + e] = __hmax2(mx[cc * 4 + e], *reinterpret_cast<const __nv_bfloat162*>(&xs[e]));
             }
           }
         }
         const int ph = pty * 7 + py, pw = ptx * 7 + px;
         uint4* o = reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + c8 * 8);
+        const uint32_t* mw = reinterpret_cast<const uint32_t*>(mx);
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc)
-          o[cc] = make_uint4(pack_bf16x2(mx[cc * 8 + 0], mx[cc * 8 + 1]), pack_bf16x2(mx[cc * 8 + 2], mx[cc * 8 + 3]),
-                             pack_bf16x2(mx[cc * 8 + 4], mx[cc * 8 + 5]), pack_bf16x2(mx[cc * 8 + 6], mx[cc * 8 + 7]));
+        for (int cc = 0; cc < 2; ++cc) o[cc] = make_uint4(mw[cc * 4 + 0], mw[cc * 4 + 1], mw[cc * 4 + 2], mw[cc * 4 + 3]);
       }
       asm volatile("bar.sync 1, %0;" ::"n"(ST_DRAIN) : "memory");  // staging tile is rewritten next iteration
     }
