@@ -444,11 +444,15 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   if (!bf16) {
     CAPI_CUDA(launch_conv_fp32(a, nullptr));
   } else {
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmR, tmO;
     const char* terr = "";
     if (a.b_tma && make_tmap_weights(&tmB, dw.p, cs.Cout_pad, cs.K, (a.pair && a.BN >= 64) ? a.BN / 2 : a.BN, &terr)) return fail(B2I_ECUDA, terr);
     if (a.patch) {
       if (make_tmap_patch(&tmA, dx.p, N, H, W, &terr)) return fail(B2I_ECUDA, terr);
+      if (make_tmap_tile(&tmO, dout.p, N, H, W, &terr)) return fail(B2I_ECUDA, terr);
+      if (residual && make_tmap_tile(&tmR, dr.p, N, H, W, &terr)) return fail(B2I_ECUDA, terr);
+      a.tmO = &tmO;
+      a.tmR = residual ? &tmR : nullptr;
     } else if (a.amode == A_IM2COL && make_tmap_im2col(&tmA, dx.p, g, N, &terr)) {
       return fail(B2I_ECUDA, terr);
     }

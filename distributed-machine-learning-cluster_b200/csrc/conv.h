@@ -44,12 +44,16 @@ struct ConvArgs {
   int b_tma = 1;                  // 1: weights through TMA, 0: cp.async gather (A_GATHER / A_SMALLC only)
   int persistent = 1;             // TMA modes: persistent CTA-per-SM kernel with double-buffered TMEM
   int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
+  const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
+  const CUtensorMap* tmO = nullptr;
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)
 };
 
 // True when the halo-patch kernel handles this geometry (ResNet layer1 convolutions).
 bool conv_patch_applicable(const ConvGeom& g);
-int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);
+int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);   // 18 x 10 halo patch
+int make_tmap_tile(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);    // 16 x 8 tile (residual in / result out)
+int make_tmap_nhwc64(CUtensorMap* tm, const void* x, int N, int H, int W, int box_w, int box_h, const char** err);
 
 // bf16 tcgen05 path.  tmA / tmB may be null when the corresponding operand is gathered.
 cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,

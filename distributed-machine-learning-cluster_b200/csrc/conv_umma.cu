@@ -697,7 +697,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 constexpr int PT_W = 10, PT_H = 18;
 constexpr uint32_t PT_BYTES = ((PT_W * PT_H * 128 + 1023) / 1024) * 1024;   // 23552
 constexpr uint32_t PT_WBYTES = 9 * 64 * 128;                                // resident weights, 73728
-constexpr int PT_BUFS = 4;   // patches in flight: TMA latency (~1.5 us) spans more than one tile of MMA work
+constexpr int PT_BUFS = 3;   // patches (+ residual tiles) in flight
 
 struct PatchP {
   int N, H, W, tiles_w, tiles_h, total_tiles, relu;
@@ -716,12 +716,23 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm,
 }
 
 constexpr int PATCH_THREADS = 64 + 256;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
+constexpr uint32_t PT_TILE_BYTES = 128 * 128;   // one 16x8-pixel x 64-channel bf16 tile (residual in / result out)
 
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(tm),
+               "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
+// Epilogue without per-thread global traffic: the residual tile arrives by TMA next to the patch,
+// the result leaves by one TMA store from a 128B-swizzled staging tile (rows past the image edge
+// are clipped by the TMA unit).
 __global__ void __launch_bounds__(PATCH_THREADS, 1)
 conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+                         const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
                          const PatchP p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * PT_BUFS + 5];  // patch_full[], patch_empty[], acc_full[2], acc_empty[2], w_full
+  __shared__ __align__(8) uint64_t bars[3 * PT_BUFS + 5];  // patch_full[], patch_empty[], res_empty[], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5;
@@ -729,17 +740,22 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_smem = base;
   const uint32_t patch0 = base + PT_WBYTES;
+  const uint32_t res0 = patch0 + PT_BUFS * PT_BYTES;
+  const uint32_t out0 = res0 + PT_BUFS * PT_TILE_BYTES;
   const uint32_t bar0 = smem_u32(bars);
   auto patch_full = [&](int b) { return bar0 + 8u * b; };
   auto patch_empty = [&](int b) { return bar0 + 8u * (PT_BUFS + b); };
-  auto acc_full = [&](int b) { return bar0 + 8u * (2 * PT_BUFS + b); };
-  auto acc_empty = [&](int b) { return bar0 + 8u * (2 * PT_BUFS + 2 + b); };
-  const uint32_t w_full = bar0 + 8u * (2 * PT_BUFS + 4);
+  auto res_empty = [&](int b) { return bar0 + 8u * (2 * PT_BUFS + b); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (3 * PT_BUFS + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (3 * PT_BUFS + 2 + b); };
+  const uint32_t w_full = bar0 + 8u * (3 * PT_BUFS + 4);
+  const bool has_res = p.residual != nullptr;
 
   if (threadIdx.x == 0) {
     for (int b = 0; b < PT_BUFS; ++b) {
       mbar_init(patch_full(b), 1);
       mbar_init(patch_empty(b), 1);
+      mbar_init(res_empty(b), 8);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(acc_full(b), 1);
@@ -751,6 +767,8 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX);
     tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmO);
+    if (has_res) tma_prefetch_desc(&tmR);
   }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_slot), 128);
   tc_fence_before();
@@ -766,12 +784,15 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       int i = 0;
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
         const int pb = i % PT_BUFS;
+        const uint32_t par = ((i / PT_BUFS) & 1) ^ 1;
         const int n = t / tiles_per_img;
         const int rem = t - n * tiles_per_img;
         const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
-        mbar_wait(patch_empty(pb), ((i / PT_BUFS) & 1) ^ 1);
-        mbar_expect_tx(patch_full(pb), PT_W * PT_H * 128);
+        mbar_wait(patch_empty(pb), par);
+        if (has_res) mbar_wait(res_empty(pb), par);
+        mbar_expect_tx(patch_full(pb), PT_W * PT_H * 128 + (has_res ? PT_TILE_BYTES : 0u));
         tma_load_4d(patch0 + pb * PT_BYTES, &tmX, patch_full(pb), 0, tx * 8 - 1, ty * 16 - 1, n);
+        if (has_res) tma_load_4d(res0 + pb * PT_TILE_BYTES, &tmR, patch_full(pb), 0, tx * 8, ty * 16, n);
       }
     }
   } else if (warp == 1) {
@@ -805,17 +826,25 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     }
   } else {
     const int q = warp & 3;
+    const int c = (warp - 2) >> 2;               // which 32-channel half of the 64 outputs this warp drains
+    const int mrow = q * 32 + lane;              // row of the 128-row tile: (output row, column) = (mrow / 8, mrow % 8)
+    const uint32_t sw = static_cast<uint32_t>(mrow & 7);
+    const bool storer = threadIdx.x == 64;       // first epilogue thread issues the TMA stores
+    float bias[32];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + c * 32) + j);
+      bias[4 * j] = bv.x; bias[4 * j + 1] = bv.y; bias[4 * j + 2] = bv.z; bias[4 * j + 3] = bv.w;
+    }
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
+      const int pbuf = i % PT_BUFS;
       const int n = t / tiles_per_img;
       const int rem = t - n * tiles_per_img;
       const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
       mbar_wait(acc_full(b), (i >> 1) & 1);
       tc_fence_after();
-      const int mrow = q * 32 + lane;              // row of the 128-row tile: (output row, column) = (mrow / 8, mrow % 8)
-      const int oh = ty * 16 + (mrow >> 3), ow = tx * 8 + (mrow & 7);
-      const int c = (warp - 2) >> 2;               // which 32-channel half of the 64 outputs this warp drains
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 64 + c * 32);
       uint32_t v[32];
       tmem_ld32(t_row, v);
@@ -823,44 +852,47 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(b));
-      if (oh < p.H && ow < p.W) {
-        const size_t off = ((static_cast<size_t>(n) * p.H + oh) * p.W + ow) * 64 + c * 32;
-        float f[32];
-        const float4* b4 = reinterpret_cast<const float4*>(p.bias + c * 32);
+      float f[32];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 b = __ldg(b4 + j);
-          f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
-          f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
-          f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
-          f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
-        }
-        if (p.residual) {
-          const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
-          uint4 rv[4];
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias[j];
+      if (has_res) {
+        const uint32_t r_row = res0 + pbuf * PT_TILE_BYTES + static_cast<uint32_t>(mrow) * 128u;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) rv[g] = __ldg(rp + g);
+        for (int g = 0; g < 4; ++g) {
+          uint32_t rr[4];
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(rr[0]), "=r"(rr[1]), "=r"(rr[2]), "=r"(rr[3])
+                       : "r"(r_row + ((static_cast<uint32_t>(c * 4 + g) ^ sw) << 4)));
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint32_t rr[4] = {rv[g].x, rv[g].y, rv[g].z, rv[g].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              f[g * 8 + e * 2] += bf16_lo(rr[e]);
-              f[g * 8 + e * 2 + 1] += bf16_hi(rr[e]);
-            }
+          for (int e = 0; e < 4; ++e) {
+            f[g * 8 + e * 2] += bf16_lo(rr[e]);
+            f[g * 8 + e * 2 + 1] += bf16_hi(rr[e]);
           }
         }
-        if (p.relu) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(res_empty(pbuf));
+      }
+      if (p.relu) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        uint4* op = reinterpret_cast<uint4*>(p.out + off);
+        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+      // staging tile b was handed to the TMA store two tiles ago: wait until that store has read it
+      if (storer) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const uint32_t o_row = out0 + b * PT_TILE_BYTES + static_cast<uint32_t>(mrow) * 128u;
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
-          op[g] = make_uint4(pack_bf16x2(f[g * 8 + 0], f[g * 8 + 1]), pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3]),
-                             pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5]), pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]));
+      for (int g = 0; g < 4; ++g)
+        asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(o_row + ((static_cast<uint32_t>(c * 4 + g) ^ sw) << 4)),
+                     "r"(pack_bf16x2(f[g * 8 + 0], f[g * 8 + 1])), "r"(pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3])),
+                     "r"(pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5])), "r"(pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]))
+                     : "memory");
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (storer) {
+        tma_store_4d(&tmO, out0 + b * PT_TILE_BYTES, 0, tx * 8, ty * 16, n);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
     }
+    if (storer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
 
   tc_fence_before();
@@ -955,12 +987,13 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
 
 cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmW,
                          cudaStream_t st) {
+  if (!a.tmO || (a.residual && !a.tmR)) return cudaErrorInvalidValue;
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
-  const size_t smem = PT_WBYTES + PT_BUFS * PT_BYTES + 1024;
+  const size_t smem = PT_WBYTES + PT_BUFS * (PT_BYTES + PT_TILE_BYTES) + 2 * PT_TILE_BYTES + 1024;
   if (!attr_set[dev]) {
     cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
@@ -980,7 +1013,7 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   p.residual = static_cast<const __nv_bfloat16*>(a.residual);
   p.out = static_cast<__nv_bfloat16*>(a.out);
   const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
-  conv3x3_c64_patch_kernel<<<grid, PATCH_THREADS, smem, st>>>(*tmX, *tmW, p);
+  conv3x3_c64_patch_kernel<<<grid, PATCH_THREADS, smem, st>>>(*tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
   return cudaGetLastError();
 }
 
@@ -1110,11 +1143,19 @@ bool conv_patch_applicable(const ConvGeom& g) {
 // Tiled 4-D map over NHWC [N][H][W][64] with an 18 x 10 pixel box: the halo patch of one 16 x 8
 // output tile; out-of-image coordinates (the conv padding) are zero-filled by the TMA unit.
 int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err) {
+  return make_tmap_nhwc64(tm, x, N, H, W, PT_W, PT_H, err);
+}
+
+int make_tmap_tile(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err) {
+  return make_tmap_nhwc64(tm, x, N, H, W, 8, 16, err);
+}
+
+int make_tmap_nhwc64(CUtensorMap* tm, const void* x, int N, int H, int W, int box_w, int box_h, const char** err) {
   static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
   if (!fn) { *err = "cuTensorMapEncodeTiled entry point not found"; return -1; }
   cuuint64_t dims[4] = {64, static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(N)};
   cuuint64_t strides[3] = {128, static_cast<cuuint64_t>(W) * 128, static_cast<cuuint64_t>(H) * W * 128};
-  cuuint32_t box[4] = {64, PT_W, PT_H, 1};
+  cuuint32_t box[4] = {64, static_cast<cuuint32_t>(box_w), static_cast<cuuint32_t>(box_h), 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,

@@ -424,6 +424,8 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         void* xin = bufs_[tensor_buf_[o.in]];
         if (d.patch) {
           if (make_tmap_patch(&d.tmA, xin, mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
+          if (make_tmap_tile(&d.tmO, bufs_[tensor_buf_[o.out]], mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
+          if (o.res >= 0 && make_tmap_tile(&d.tmR, bufs_[tensor_buf_[o.res]], mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_IM2COL) {
           if (make_tmap_im2col(&d.tmA, xin, g, mb_, &terr)) { *err = c.name + ": " + terr; return false; }
@@ -496,6 +498,8 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.b_tma = d.b_tma;
         a.persistent = cfg_.persistent;
         a.patch = d.patch;
+        a.tmO = &d.tmO;
+        a.tmR = o.res >= 0 ? &d.tmR : nullptr;
         a.pair = d.pair;
         if (cfg_.precision == PREC_FP32) {
           B2I_CUDA(launch_conv_fp32(a, st));

@@ -115,7 +115,7 @@ class DeviceModel {
     ConvGeom g{};
     void* w = nullptr;
     float* bias = nullptr;
-    CUtensorMap tmA{}, tmB{};
+    CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};
     bool has_tmA = false, has_tmB = false;
     int amode = 0, BN = 0, stages = 0, b_tma = 0, patch = 0, pair = 0;
   };
