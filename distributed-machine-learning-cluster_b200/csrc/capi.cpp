@@ -127,7 +127,7 @@ void b2i_default_config(b2i_model_config* cfg) {
   cfg->keep_tensors = 0;
   cfg->fused_stem = 1;
   cfg->patch_conv = 1;
-  cfg->pair_mma = 0;
+  cfg->pair_mma = 256;
 }
 
 int b2i_ot_inspect(const char* path, char* names_out, size_t cap) {

@@ -30,7 +30,7 @@ struct EngineConfig {
   int b_tma = 1;                // weights through TMA
   int bn_max = 256;             // largest tile-N the planner may choose
   int fused_stem = 1;           // ResNet bf16: normalise + conv1 + max-pool as one kernel
-  int pair_mma = 0;             // layers with tile-N >= 128 through the CTA-pair (cta_group::2) kernel
+  int pair_mma = 256;             // layers with tile-N >= 128 through the CTA-pair (cta_group::2) kernel
   int patch_conv = 1;           // 64->64 3x3/s1 layers through the halo-patch kernel
   int persistent = 1;           // TMA-fed layers: persistent kernel (0 = one tile per CTA)
   int keep_tensors = 0;         // 1: every activation gets its own buffer (per-layer parity tests)

@@ -160,6 +160,56 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(const void* __res
   }
 }
 
+// Global average (OH = OW = 1), one CTA per image: thread (pixel group g, channel chunk c) sums
+// pixels g, g + G, ... with fully coalesced 16-byte loads across c, then the G partial sums meet in
+// shared memory.  The generic kernel above gives one thread all 49 pixels of a chunk (64 CTAs total).
+template <bool F32>
+__global__ void __launch_bounds__(256) global_avgpool_kernel(const void* __restrict__ in,
+                                                              void* __restrict__ out, int HW, int C) {
+  constexpr int vec = F32 ? 4 : 8;
+  __shared__ float part[256][8];
+  const int cv = C / vec;
+  const int groups = 256 / cv;
+  const int c = threadIdx.x % cv, g = threadIdx.x / cv;
+  const int n = blockIdx.x;
+  float a[8] = {};
+  if (g < groups) {
+    for (int px = g; px < HW; px += groups) {
+      const size_t off = (static_cast<size_t>(n) * HW + px) * C + c * vec;
+      if (F32) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(in) + off));
+        a[0] += v.x; a[1] += v.y; a[2] += v.z; a[3] += v.w;
+      } else {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(in) + off));
+        const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          a[2 * e] += __uint_as_float(u[e] << 16);
+          a[2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[threadIdx.x][j] = a[j];
+  __syncthreads();
+  if (g == 0) {
+    for (int k = 1; k < groups; ++k)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] += part[k * cv + c][j];
+    const float cnt = static_cast<float>(HW);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = __fdiv_rn(a[j], cnt);
+    const size_t ooff = static_cast<size_t>(n) * C + c * vec;
+    if (F32) {
+      *reinterpret_cast<float4*>(static_cast<float*>(out) + ooff) = make_float4(a[0], a[1], a[2], a[3]);
+    } else {
+      *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + ooff) =
+          make_uint4(pack2(a[0], a[1]), pack2(a[2], a[3]), pack2(a[4], a[5]), pack2(a[6], a[7]));
+    }
+  }
+}
+
 // ------------------------------------------------------------------ softmax + top-k
 // One warp per row; each lane keeps classes lane, lane+32, ... in registers (<= 32 per lane).
 constexpr int kMaxPerLane = 32;
@@ -258,6 +308,12 @@ cudaError_t launch_adaptive_avgpool(const void* in, void* out, int dtype, int N,
                                     int C, int OH, int OW, cudaStream_t st) {
   const int vec = dtype == DT_F32 ? 4 : 8;
   if (C % vec) return cudaErrorInvalidValue;
+  const int cv = C / vec;
+  if (OH == 1 && OW == 1 && cv <= 256 && 256 % cv == 0) {
+    if (dtype == DT_F32) global_avgpool_kernel<true><<<N, 256, 0, st>>>(in, out, H * W, C);
+    else global_avgpool_kernel<false><<<N, 256, 0, st>>>(in, out, H * W, C);
+    return cudaGetLastError();
+  }
   const long long total = static_cast<long long>(N) * OH * OW * (C / vec);
   if (dtype == DT_F32)
     adaptive_avgpool_kernel<true><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, OH, OW);
