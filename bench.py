@@ -264,6 +264,7 @@ def main():
     if rank != 0:
         if world > 1:
             dist.barrier()
+            dist.destroy_process_group()
         return
 
     pk = peaks()
@@ -309,6 +310,7 @@ def main():
     print(json.dumps(out))
     if world > 1:
         dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

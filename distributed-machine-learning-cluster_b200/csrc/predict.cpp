@@ -59,9 +59,41 @@ void enqueue_shard(DevSlot& s, int lane_id, const uint8_t* images, int n, int k,
                            cudaMemcpyHostToDevice, s.copy_st), "H2D copy")) return;
     if (cu(cudaEventRecord(L.copied[c], s.copy_st), "cudaEventRecord")) return;
     if (cu(cudaStreamWaitEvent(s.comp_st, L.copied[c], 0), "cudaStreamWaitEvent")) return;
-    if (!s.dm->forward(L.d_in + byte_off, nb, k, L.d_idx + static_cast<size_t>(off) * k,
-                       L.d_prob + static_cast<size_t>(off) * k,
-                       logits ? L.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, &out->err)) {
+    auto run_forward = [&]() {
+      return s.dm->forward(L.d_in + byte_off, nb, k, L.d_idx + static_cast<size_t>(off) * k,
+                           L.d_prob + static_cast<size_t>(off) * k,
+                           logits ? L.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, &out->err);
+    };
+    bool done = false;
+    if (nb <= s.graph_max_batch) {
+      // key: every pointer the launches embed is a function of (lane, chunk index, nb, k, logits?)
+      const uint64_t key = (static_cast<uint64_t>(lane_id) << 60) | (static_cast<uint64_t>(c) << 40) |
+                           (static_cast<uint64_t>(nb) << 8) | (static_cast<uint64_t>(k) << 1) | (logits ? 1u : 0u);
+      GraphEntry& ge = s.graphs[key];
+      ++ge.uses;
+      if (ge.uses == 2 && !ge.exec && s.graphs.size() <= 256) {
+        // second use: capture (the first, eager use has run every one-time attribute / handle set-up)
+        cudaGraph_t graph = nullptr;
+        if (cudaStreamBeginCapture(s.comp_st, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+          const bool ok = run_forward();
+          cudaError_t ce = cudaStreamEndCapture(s.comp_st, &graph);
+          if (ok && ce == cudaSuccess && graph) {
+            if (cudaGraphInstantiate(&ge.exec, graph, 0) != cudaSuccess) ge.exec = nullptr;
+          }
+          if (graph) cudaGraphDestroy(graph);
+          if (!ok || ce != cudaSuccess) {
+            cudaGetLastError();
+            ge.exec = nullptr;
+            ge.uses = 1 << 20;   // do not try again for this shape
+          }
+        }
+      }
+      if (ge.exec) {
+        if (cu(cudaGraphLaunch(ge.exec, s.comp_st), "cudaGraphLaunch")) return;
+        done = true;
+      }
+    }
+    if (!done && !run_forward()) {
       out->rc = B2I_ECUDA;
       return;
     }
@@ -136,6 +168,8 @@ void slot_free(DevSlot* s) {
     for (auto ev : L.copied) if (ev) cudaEventDestroy(ev);
     L = Lane();
   }
+  for (auto& kv : s->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  s->graphs.clear();
   if (s->copy_st) cudaStreamDestroy(s->copy_st);
   if (s->comp_st) cudaStreamDestroy(s->comp_st);
   s->dm.reset();

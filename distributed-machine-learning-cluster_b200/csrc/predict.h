@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -38,11 +39,20 @@ struct Lane {
   float* out_logits = nullptr;
 };
 
+// A captured forward: the kernel sequence of one (lane, chunk, batch, k, logits?) combination,
+// replayed with a single cudaGraphLaunch.  Worth it where the sequence is launch-bound (small batch).
+struct GraphEntry {
+  int uses = 0;
+  cudaGraphExec_t exec = nullptr;
+};
+
 struct DevSlot {
   std::unique_ptr<DeviceModel> dm;
   cudaStream_t copy_st = nullptr, comp_st = nullptr;
   Lane lane[2];
   int chunk = 0;
+  int graph_max_batch = 64;                    // forwards of at most this many images are graph-replayed
+  std::map<uint64_t, GraphEntry> graphs;
 };
 
 struct Pending {

@@ -4,6 +4,7 @@ Same names, argument meaning and error behaviour as the Rust it stands in for (t
 is absent here, see INTEGRATION.md for the cgo-style binding a maintainer would add):
 
   load_labels          reference src/services.rs:170-184   (synset_words.txt -> [(wnid, label)])
+  sample_predict       reference src/model_utils.rs:7-22
   load_model           reference src/model_utils.rs:24-36  (fails loudly instead of swallowing errors)
   predict_image        reference src/model_utils.rs:38-49
   MemberState.predict  reference src/services.rs:475-497   (Member::predict RPC handler body)
@@ -46,6 +47,18 @@ def decode_image(path):
             return np.asarray(im.convert("RGB"))
     except Exception:
         return None
+
+
+def sample_predict(labels, ctx=None, weight_dir=WEIGHT_DIR,
+                   image_path=os.path.join(IMAGE_ROOT, "n01491361", "ILSVRC2012_00034413.JPEG")):
+    """The reference's demo (model_utils.rs:7-22): AlexNet top-1 label of one fixed image."""
+    ctx = ctx or Context((0,))
+    img = decode_image(image_path)
+    if img is None:
+        raise IOError("cannot decode %s" % image_path)           # `?` on the TchError in the reference
+    with Model(ctx, "alexnet", os.path.join(weight_dir, "alexnet.ot"), max_batch=1) as model:
+        idx, _ = model.predict_u8(ctx.resize_crop(img)[None], k=1)
+    return labels[int(idx[0, 0])][1]
 
 
 def load_model(model_name, ctx=None, weight_dir=WEIGHT_DIR, **kw):

@@ -212,6 +212,27 @@ def test_submit_wait_overlaps_and_matches_blocking_predict(pkg, ctx, resnet18_ot
         assert np.array_equal(oa[0], ia)
 
 
+def test_graph_replay_of_small_batches_is_transparent(pkg, ctx, resnet18_ot, alexnet_ot):
+    """Small forwards are captured into a CUDA graph on their second use and replayed afterwards:
+    the first (eager), second (captured) and later (replayed) calls must return identical results,
+    also when other batch sizes are interleaved."""
+    from oracle import synth
+    imgs = synth.synthetic_images(9, seed=41)
+    for name, ot in (("resnet18", resnet18_ot), ("alexnet", alexnet_ot)):
+        with pkg.Model(ctx, name, ot, precision=BF16, max_batch=16) as m:
+            first = {n: m.predict_u8(imgs[:n], k=5, want_logits=True) for n in (1, 3, 9)}
+            for rep in range(4):
+                for n in (3, 1, 9):
+                    i, p, lg = m.predict_u8(imgs[:n], k=5, want_logits=True)
+                    assert np.array_equal(lg, first[n][2]) and np.array_equal(i, first[n][0]), (name, n, rep)
+            # a different image through a captured shape must not see stale inputs
+            other = synth.synthetic_images(3, seed=42)
+            _, _, lo = m.predict_u8(other, k=5, want_logits=True)
+            assert not np.array_equal(lo, first[3][2])
+            _, _, lo2 = m.predict_u8(other, k=5, want_logits=True)
+            assert np.array_equal(lo, lo2)
+
+
 def test_model_load_errors(pkg, ctx, tmp_path, resnet18_ot):
     with pytest.raises(pkg.B2IError) as e:
         pkg.Model(ctx, "vgg16", resnet18_ot)
@@ -245,6 +266,8 @@ def test_member_predict_mirrors_reference_semantics(pkg, ctx, resnet18_ot, alexn
         for i, (p, lbl) in enumerate(res):
             if srt[i, -1] - srt[i, -2] > 2 * bf16_budget(GV["resnet18_logits"]):
                 assert lbl == labels[top1[i]][1]
+        demo = pkg.sample_predict(labels, ctx=ctx, weight_dir=str(wd), image_path=os.path.join(root, "n01491361", sorted(os.listdir(os.path.join(root, "n01491361")))[0]))
+        assert isinstance(demo, str) and demo in dict((l, 1) for _, l in labels)
         res5 = member.predict("alexnet", ids[:2], k=5)
         assert len(res5) == 2 and len(res5[0]) == 5
         with pytest.raises(FileNotFoundError):
