@@ -140,6 +140,7 @@ def main():
     ap.add_argument("--profile-out", default="")
     ap.add_argument("--patch-conv", type=int, default=None)
     ap.add_argument("--pair-mma", type=int, default=None)
+    ap.add_argument("--fuse-downsample", type=int, default=None)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -166,7 +167,8 @@ def main():
 
     ctx = b2.Context((local,))
     model = b2.Model(ctx, MODEL, ot, precision=b2.PREC_BF16, max_batch=BATCH, micro_batch=args.micro_batch,
-                     tile_n_max=args.tile_n_max, conv_mode=args.conv_mode, patch_conv=args.patch_conv, pair_mma=args.pair_mma)
+                     tile_n_max=args.tile_n_max, conv_mode=args.conv_mode, patch_conv=args.patch_conv, pair_mma=args.pair_mma,
+                     fuse_downsample=args.fuse_downsample)
     n_micro = (BATCH + (args.micro_batch or BATCH) - 1) // (args.micro_batch or BATCH)
 
     host = synth.synthetic_images(BATCH, seed=rank)

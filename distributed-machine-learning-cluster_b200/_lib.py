@@ -26,6 +26,7 @@ class ModelConfig(ctypes.Structure):
         ("fused_stem", ctypes.c_int),
         ("patch_conv", ctypes.c_int),
         ("pair_mma", ctypes.c_int),
+        ("fuse_downsample", ctypes.c_int),
     ]
 
 

@@ -128,6 +128,7 @@ void b2i_default_config(b2i_model_config* cfg) {
   cfg->fused_stem = 1;
   cfg->patch_conv = 1;
   cfg->pair_mma = 256;
+  cfg->fuse_downsample = 1;
 }
 
 int b2i_ot_inspect(const char* path, char* names_out, size_t cap) {
@@ -194,6 +195,7 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   ec.persistent = cfg.conv_mode == 2 ? 0 : 1;
   ec.patch_conv = cfg.patch_conv;
   ec.pair_mma = cfg.pair_mma;
+  ec.fuse_downsample = cfg.fuse_downsample;
   ec.b_tma = cfg.weights_tma;
   if (cfg.tile_n_max > 0) ec.bn_max = cfg.tile_n_max;
   ec.keep_tensors = cfg.keep_tensors;

@@ -43,6 +43,13 @@ struct ConvArgs {
   int amode = A_GATHER;
   int b_tma = 1;                  // 1: weights through TMA, 0: cp.async gather (A_GATHER / A_SMALLC only)
   int persistent = 1;             // TMA modes: persistent CTA-per-SM kernel with double-buffered TMEM
+  // optional second problem on the same A operand (see conv_umma.cu): a 1x1 conv whose input pixel is
+  // one tap of this conv; same Cout / BN; weights tmB2 [Cout_pad][num_kb2*64], k-blocks
+  // [kb_first2, kb_first2 + num_kb2) of this conv's im2col stream
+  const CUtensorMap* tmB2 = nullptr;
+  const float* bias2 = nullptr;
+  void* out2 = nullptr;
+  int ldo2 = 0, relu2 = 0, kb_first2 = 0, num_kb2 = 0;
   int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
   const CUtensorMap* tmO = nullptr;

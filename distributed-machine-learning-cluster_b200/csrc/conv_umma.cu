@@ -38,11 +38,36 @@ struct KP {
   const float* bias;
   const __nv_bfloat16* residual;
   void* out;
+  // optional second problem sharing the A operand (a 1x1/s2 downsample riding on its sibling 3x3/s2
+  // conv): `tiles_n2` extra N-tiles that run over k-blocks [kb_first2, kb_first2 + num_kb2) of the
+  // same im2col stream with their own weights (tmB2), bias and output; no residual, bf16 out.
+  int tiles_n2, kb_first2, num_kb2, ldo2, relu2, Cout2;
+  const float* bias2;
+  void* out2;
 };
+
+// Where one tile's results go.
+struct Epi {
+  const float* bias;
+  const __nv_bfloat16* residual;
+  void* out;
+  int ldo, relu, out_fp32, Cout;
+};
+__device__ __forceinline__ Epi epi_of(const KP& p, bool second) {
+  Epi e;
+  e.bias = second ? p.bias2 : p.bias;
+  e.residual = second ? nullptr : p.residual;
+  e.out = second ? p.out2 : p.out;
+  e.ldo = second ? p.ldo2 : p.ldo;
+  e.relu = second ? p.relu2 : p.relu;
+  e.out_fp32 = second ? 0 : p.out_fp32;
+  e.Cout = second ? p.Cout2 : p.Cout;
+  return e;
+}
 
 
 // One output row x 32 consecutive channels: acc + bias (+ residual) -> ReLU -> store.
-__device__ __forceinline__ void epilogue_chunk(const KP& p, int m, int nb, const uint32_t (&v)[32]) {
+__device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, const uint32_t (&v)[32]) {
   float f[32];
   const float4* b4 = reinterpret_cast<const float4*>(p.bias + nb);   // bias is padded to Cout_pad: always in range
 #pragma unroll
@@ -247,7 +272,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t v[32];
       tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
       tmem_ld_wait();
-      if (row_ok) epilogue_chunk(p, m, n0 + c * 32, v);
+      if (row_ok) epilogue_chunk(epi_of(p, false), m, n0 + c * 32, v);
     }
   } else if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
@@ -325,7 +350,8 @@ constexpr int PTHREADS = 64 + 256;   // TMA warp, MMA warp, 8 epilogue warps (tw
 template <int AMODE>
 __global__ void __launch_bounds__(PTHREADS, 1)
 conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
-                            const __grid_constant__ CUtensorMap tmB, const KP p) {
+                            const __grid_constant__ CUtensorMap tmB,
+                            const __grid_constant__ CUtensorMap tmB2, const KP p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
   __shared__ uint32_t tmem_slot;
@@ -340,7 +366,8 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
   auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + b); };
   auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
-  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int tn_all = p.tiles_n + p.tiles_n2;
+  const int total_tiles = p.tiles_m * tn_all;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -370,8 +397,13 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       const uint32_t tx = b_tile_bytes + A_TILE_BYTES;
       int s = 0, ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int m0 = (t / p.tiles_n) * BM;
-        const int n0 = (t % p.tiles_n) * p.BN;
+        const int tm = t / tn_all;
+        const int nn = t - tm * tn_all;
+        const bool second = nn >= p.tiles_n;
+        const int m0 = tm * BM;
+        const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
+        const int kb_begin = second ? p.kb_first2 : 0;
+        const int kb_count = second ? p.num_kb2 : p.num_kb;
         int iw_base = 0, ih_base = 0, n_base = 0;
         if (AMODE == A_IM2COL) {
           n_base = m0 / ohw;
@@ -381,8 +413,10 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
           ih_base = oh * p.stride - p.pad;
           iw_base = ow * p.stride - p.pad;
         }
-        int tap = 0, cblk = 0, r = 0, sx = 0;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int tap0 = kb_begin / cpb;
+        int cblk = kb_begin - tap0 * cpb, r = tap0 / p.S, sx = tap0 - (tap0 / p.S) * p.S;
+        for (int j = 0; j < kb_count; ++j) {
+          const int kb = kb_begin + j;
           mbar_wait(empty_bar(s), ph ^ 1);
           const uint32_t a_s = smem_base + s * stage_bytes;
           mbar_expect_tx(full_bar(s), tx);
@@ -391,16 +425,15 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                                static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
             if (++cblk == cpb) {
               cblk = 0;
-              ++tap;
               if (++sx == p.S) { sx = 0; ++r; }
             }
           } else {
             tma_load_2d(a_s, &tmA, full_bar(s), kb * BK, m0);
           }
-          tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          if (second) tma_load_2d(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
+          else tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
-        (void)tap;
       }
     }
   } else if (warp == 1) {
@@ -411,7 +444,8 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
-      for (int kb = 0; kb < p.num_kb; ++kb) {
+      const int kb_count = (t % tn_all) >= p.tiles_n ? p.num_kb2 : p.num_kb;
+      for (int kb = 0; kb < kb_count; ++kb) {
         mbar_wait(full_bar(s), ph);
         tc_fence_after();
         {
@@ -422,7 +456,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
           for (int k = 0; k < BK / 16; ++k)
             umma_bf16_elect(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit_elect(empty_bar(s));
-          if (kb == p.num_kb - 1) umma_commit_elect(acc_full_bar(buf));
+          if (kb == kb_count - 1) umma_commit_elect(acc_full_bar(buf));
         }
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
@@ -433,8 +467,12 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
     int i = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
       const int buf = i & 1;
-      const int m0 = (t / p.tiles_n) * BM;
-      const int n0 = (t % p.tiles_n) * p.BN;
+      const int tm = t / tn_all;
+      const int nn = t - tm * tn_all;
+      const bool second = nn >= p.tiles_n;
+      const int m0 = tm * BM;
+      const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
+      const Epi epi = epi_of(p, second);
       mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
       tc_fence_after();
       const int m = m0 + q * 32 + lane;
@@ -456,7 +494,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
           __syncwarp();
           if (lane == 0) mbar_arrive(acc_empty_bar(buf));
         }
-        if (row_ok) epilogue_chunk(p, m, n0 + c * 32, v);
+        if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v);
       }
     }
   }
@@ -530,7 +568,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
 template <int AMODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
 conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const KP p) {
+                      const __grid_constant__ CUtensorMap tmB2, const KP p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
   __shared__ uint32_t tmem_slot;
@@ -550,7 +588,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
   auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + b); };
   auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
-  const int total_tiles = p.tiles_m * p.tiles_n;   // tiles_m counts 256-row tiles here
+  const int tn_all = p.tiles_n + p.tiles_n2;
+  const int total_tiles = p.tiles_m * tn_all;       // tiles_m counts 256-row tiles here
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -585,8 +624,13 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int ohw = p.OH * p.OW;
       int s = 0, ph = 0;
       for (int t = cluster_id; t < total_tiles; t += num_clusters) {
-        const int m0 = (t / p.tiles_n) * 256 + static_cast<int>(rank) * BM;
-        const int n0 = (t % p.tiles_n) * p.BN + static_cast<int>(rank) * half_n;
+        const int tm = t / tn_all;
+        const int nn = t - tm * tn_all;
+        const bool second = nn >= p.tiles_n;
+        const int m0 = tm * 256 + static_cast<int>(rank) * BM;
+        const int n0 = (second ? nn - p.tiles_n : nn) * p.BN + static_cast<int>(rank) * half_n;
+        const int kb_begin = second ? p.kb_first2 : 0;
+        const int kb_count = second ? p.num_kb2 : p.num_kb;
         int iw_base = 0, ih_base = 0, n_base = 0;
         if (AMODE == A_IM2COL) {
           n_base = m0 / ohw;
@@ -596,8 +640,10 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           ih_base = oh * p.stride - p.pad;
           iw_base = ow * p.stride - p.pad;
         }
-        int cblk = 0, r = 0, sx = 0;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int tap0 = kb_begin / cpb;
+        int cblk = kb_begin - tap0 * cpb, r = tap0 / p.S, sx = tap0 - (tap0 / p.S) * p.S;
+        for (int j = 0; j < kb_count; ++j) {
+          const int kb = kb_begin + j;
           mbar_wait(empty_bar(s), ph ^ 1);
           const uint32_t a_s = smem_base + s * stage_bytes;
           if (leader) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
@@ -612,7 +658,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           } else {
             tma_load_2d_2sm(a_s, &tmA, full_bar(s), kb * BK, m0);
           }
-          tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          if (second) tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
+          else tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -626,7 +673,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int kb_count = (t % tn_all) >= p.tiles_n ? p.num_kb2 : p.num_kb;
+        for (int kb = 0; kb < kb_count; ++kb) {
           mbar_wait(full_bar(s), ph);
           tc_fence_after();
           {
@@ -637,7 +685,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             for (int k = 0; k < BK / 16; ++k)
               umma_bf16_2sm(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
             umma_commit_2sm(empty_bar(s));
-            if (kb == p.num_kb - 1) umma_commit_2sm(acc_full_bar(buf));
+            if (kb == kb_count - 1) umma_commit_2sm(acc_full_bar(buf));
           }
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
@@ -651,8 +699,12 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     int i = 0;
     for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
       const int buf = i & 1;
-      const int m0 = (t / p.tiles_n) * 256 + static_cast<int>(rank) * BM;
-      const int n0 = (t % p.tiles_n) * p.BN;
+      const int tm = t / tn_all;
+      const int nn = t - tm * tn_all;
+      const bool second = nn >= p.tiles_n;
+      const int m0 = tm * 256 + static_cast<int>(rank) * BM;
+      const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
+      const Epi epi = epi_of(p, second);
       mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
       tc_fence_after();
       const int m = m0 + q * 32 + lane;
@@ -670,7 +722,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             else mbar_arrive_cluster(acc_empty_bar(buf), 0);
           }
         }
-        if (row_ok) epilogue_chunk(p, m, n0 + c * 32, v);
+        if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v);
       }
     }
   }
@@ -924,6 +976,14 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->bias = a.bias;
   p->residual = static_cast<const __nv_bfloat16*>(a.residual);
   p->out = a.out;
+  p->tiles_n2 = a.tmB2 ? g.Cout_pad / a.BN : 0;
+  p->kb_first2 = a.kb_first2;
+  p->num_kb2 = a.num_kb2;
+  p->ldo2 = a.ldo2;
+  p->relu2 = a.relu2;
+  p->Cout2 = g.Cout;
+  p->bias2 = a.bias2;
+  p->out2 = a.out2;
 }
 
 template <int AMODE>
@@ -951,7 +1011,10 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   const int total = p.tiles_m * p.tiles_n;
   const int grid = total < sm_count[dev] ? total : sm_count[dev];
   const size_t smem = conv_umma_smem_bytes(a.BN, p.stages);
-  kern<<<dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, p);
+  const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2);
+  const int grid2 = total2 < sm_count[dev] ? total2 : sm_count[dev];
+  (void)grid;
+  kern<<<dim3(static_cast<unsigned>(grid2)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
   return cudaGetLastError();
 }
 
@@ -978,10 +1041,10 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
   p.tmem_cols = cols;
-  const int total = p.tiles_m * p.tiles_n;
+  const int total = p.tiles_m * (p.tiles_n + p.tiles_n2);
   int grid = std::min(2 * total, sm_count[dev] & ~1);
   const size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
-  kern<<<dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, p);
+  kern<<<dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
   return cudaGetLastError();
 }
 
@@ -1066,6 +1129,7 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
       a.stages > MAX_STAGES || g.M <= 0)
     return cudaErrorInvalidValue;
   if (!a.out_fp32 && ((a.ldo & 7) || (g.Cout & 31))) return cudaErrorInvalidValue;
+  if (a.tmB2 && !((a.amode == A_IM2COL) && (a.persistent || a.pair))) return cudaErrorInvalidValue;
   if (a.patch) {
     if (!conv_patch_applicable(g) || a.out_fp32 || a.ldo != 64 || !tmA || !tmB) return cudaErrorInvalidValue;
     return launch_patch(a, tmA, tmB, st);

@@ -446,6 +446,24 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
     }
   }
   op_names_.push_back("softmax_topk");
+  // A 1x1 / stride-s / pad-0 conv followed by a 3x3 / stride-s / pad-1 conv on the same input (the
+  // ResNet downsample and the block's first conv) read the same pixels: the 1x1 conv's input is the
+  // centre tap of the 3x3 window.  Compute the former as extra N-tiles of the latter's kernel.
+  if (cfg_.fuse_downsample && cfg_.precision == PREC_BF16) {
+    for (size_t i = 0; i + 1 < ops_.size(); ++i) {
+      DevOp& a = ops_[i];
+      DevOp& b = ops_[i + 1];
+      if (a.spec.kind != OpSpec::CONV || b.spec.kind != OpSpec::CONV || a.spec.fc || b.spec.fc) continue;
+      if (a.spec.in != b.spec.in || a.spec.res >= 0 || a.spec.relu) continue;
+      if (a.g.R != 1 || a.g.S != 1 || a.g.pad != 0 || b.g.R != 3 || b.g.S != 3 || b.g.pad != 1) continue;
+      if (a.g.stride != b.g.stride || a.g.OH != b.g.OH || a.g.OW != b.g.OW || a.g.Cout != b.g.Cout) continue;
+      if (a.amode != A_IM2COL || b.amode != A_IM2COL || a.patch || b.patch || a.BN != b.BN || a.pair != b.pair) continue;
+      if (!a.has_tmB || (a.g.Cout & 31)) continue;
+      b.fused_second = static_cast<int>(i);
+      a.skip = true;
+      op_names_[i + 1] += "+downsample";
+    }
+  }
   return true;
 }
 
@@ -460,6 +478,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
   mark();
   for (DevOp& d : ops_) {
     const OpSpec& o = d.spec;
+    if (d.skip) { mark(); continue; }
     switch (o.kind) {
       case OpSpec::STEM:
         B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias, nb, st));
@@ -501,6 +520,17 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.tmO = &d.tmO;
         a.tmR = o.res >= 0 ? &d.tmR : nullptr;
         a.pair = d.pair;
+        if (d.fused_second >= 0) {
+          const DevOp& s2 = ops_[d.fused_second];
+          const int cpb = d.g.C >> 6;
+          a.tmB2 = &s2.tmB;
+          a.bias2 = s2.bias;
+          a.out2 = buf(s2.spec.out);
+          a.ldo2 = s2.g.Cout;
+          a.relu2 = 0;
+          a.kb_first2 = (1 * d.g.S + 1) * cpb;   // centre tap (r, s) = (1, 1)
+          a.num_kb2 = cpb;
+        }
         if (cfg_.precision == PREC_FP32) {
           B2I_CUDA(launch_conv_fp32(a, st));
         } else {

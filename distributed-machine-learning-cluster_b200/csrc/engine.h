@@ -30,6 +30,7 @@ struct EngineConfig {
   int b_tma = 1;                // weights through TMA
   int bn_max = 256;             // largest tile-N the planner may choose
   int fused_stem = 1;           // ResNet bf16: normalise + conv1 + max-pool as one kernel
+  int fuse_downsample = 1;      // 1x1/s2 downsample convs ride on their sibling 3x3/s2 conv's kernel
   int pair_mma = 256;             // layers with tile-N >= 128 through the CTA-pair (cta_group::2) kernel
   int patch_conv = 1;           // 64->64 3x3/s1 layers through the halo-patch kernel
   int persistent = 1;           // TMA-fed layers: persistent kernel (0 = one tile per CTA)
@@ -118,6 +119,8 @@ class DeviceModel {
     CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};
     bool has_tmA = false, has_tmB = false;
     int amode = 0, BN = 0, stages = 0, b_tma = 0, patch = 0, pair = 0;
+    int fused_second = -1;   // index of a 1x1 conv computed inside this op's kernel
+    bool skip = false;       // computed by another op's kernel
   };
   bool run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_idx, float* d_prob,
                       float* d_logits, cudaStream_t st, std::string* err);

@@ -158,7 +158,8 @@ class Model:
 
     def __init__(self, ctx, model_name, ot_path, precision=PREC_BF16, max_batch=256, micro_batch=0,
                  alexnet_geometry=ALEXNET_TCH, conv_mode=-1, weights_tma=1, tile_n_max=0, keep_tensors=False,
-                 fused_stem=True, patch_conv=None, pair_mma=None):
+                 fused_stem=True, patch_conv=None, pair_mma=None,
+                 fuse_downsample=None):
         cfg = ModelConfig()
         _lib.lib().b2i_default_config(ctypes.byref(cfg))
         cfg.precision, cfg.max_batch, cfg.micro_batch = precision, max_batch, micro_batch
@@ -168,6 +169,8 @@ class Model:
             cfg.patch_conv = int(patch_conv)
         if pair_mma is not None:
             cfg.pair_mma = int(pair_mma)
+        if fuse_downsample is not None:
+            cfg.fuse_downsample = int(fuse_downsample)
         h = ctypes.c_void_p()
         check(_lib.lib().b2i_model_load(ctx._h, model_name.encode(), str(ot_path).encode(), ctypes.byref(cfg),
                                         ctypes.byref(h)))

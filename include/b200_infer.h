@@ -53,6 +53,7 @@ typedef struct b2i_model_config {
   int fused_stem;       /* ResNet-18 bf16: 1 (default) = normalise + conv1 + max-pool in one kernel, 0 = three */
   int patch_conv;       /* 3x3/s1 64->64 layers (ResNet layer1): 1 (default) = halo-patch kernel, 0 = im2col TMA */
   int pair_mma;         /* 0 = off; n = layers whose tile-N is >= n use the CTA-pair (cta_group::2) kernel; default 256 */
+  int fuse_downsample;  /* 1 (default): a 1x1/s2 downsample conv is computed inside its sibling 3x3/s2 conv's kernel */
 } b2i_model_config;
 
 /* Thread-local description of the last failure on the calling thread. Never NULL. */

@@ -19,6 +19,7 @@ pub struct b2i_model_config {
     pub fused_stem: c_int,
     pub patch_conv: c_int,
     pub pair_mma: c_int,
+    pub fuse_downsample: c_int,
 }
 
 pub const B2I_OK: c_int = 0;

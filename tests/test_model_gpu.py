@@ -166,6 +166,33 @@ def test_fused_stem_matches_unfused_and_oracle(pkg, ctx, resnet18_ot):
     assert np.abs(lg_f - lg_u).max() <= tol_for(BF16, lg_u)
 
 
+def test_kernel_variants_agree(pkg, ctx, resnet18_ot):
+    """Every optional kernel path (fused stem, halo patch, CTA pairs, fused downsample) against the
+    plain persistent im2col configuration: same roundings, so logits agree to bf16 noise."""
+    from oracle import synth
+    img = synth.synthetic_images(6, seed=61)
+    def run(**kw):
+        with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=6, **kw) as m:
+            return m.predict_u8(img, k=5, want_logits=True)[2]
+    plain = run(fused_stem=False, patch_conv=0, pair_mma=0, fuse_downsample=0)
+    tol = 0.5 * tol_for(BF16, plain)
+    for kw in (dict(fuse_downsample=1, patch_conv=0, pair_mma=0, fused_stem=False), dict(pair_mma=128, fuse_downsample=1),
+               dict(pair_mma=64, fuse_downsample=0), dict(), dict(conv_mode=2, pair_mma=0, fuse_downsample=0)):
+        got = run(**kw)
+        gap = float(np.abs(got - plain).max())
+        print("variant %s: gap to plain path %.3e (bound %.3e)" % (kw, gap, tol))
+        assert gap <= tol, kw
+    # the fused downsample writes the same tensor the separate kernel would
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=6, keep_tensors=True, fused_stem=False, patch_conv=0,
+                   pair_mma=0, fuse_downsample=0) as m0, \
+            pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=6, keep_tensors=True, fused_stem=False, patch_conv=0,
+                      pair_mma=0, fuse_downsample=1) as m1:
+        m0.predict_u8(img, k=5)
+        m1.predict_u8(img, k=5)
+        for tid in (7, 12, 17):   # layer2/3/4 .0 downsample outputs (tensor order: see the per-layer test)
+            assert np.array_equal(m0.read_tensor(tid, 6), m1.read_tensor(tid, 6)), tid
+
+
 def test_batch_shapes_ragged_empty_single(pkg, ctx, resnet18_ot):
     from oracle import synth
     img = synth.synthetic_images(11, seed=0)
