@@ -58,6 +58,7 @@ SIGNATURES = {
     "b2i_model_activation_bytes": (_ll, [_vp]),
     "b2i_predict_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2i_predict_u8_on": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp]),
+    "b2i_predict_raw_u8": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2i_submit_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _c.POINTER(_ll)]),
     "b2i_wait": (_i, [_vp, _ll]),
     "b2i_forward_device": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),

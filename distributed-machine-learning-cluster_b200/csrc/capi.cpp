@@ -264,6 +264,18 @@ int b2i_predict_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* i
   return b2i_predict_u8_on(m, 0, static_cast<int>(m->slots.size()), images, n, k, idx, prob, logits);
 }
 
+int b2i_predict_raw_u8(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
+                       const int* widths, int n, int k, int32_t* idx, float* prob, float* logits) {
+  if (!m) return fail(B2I_EINVAL, "null model");
+  if (n == 0) return B2I_OK;
+  if (n_dev <= 0) { first_dev = 0; n_dev = static_cast<int>(m->slots.size()); }
+  std::lock_guard<std::mutex> lock(m->mu);
+  std::string err;
+  const int rc = predict_raw(m, first_dev, n_dev, images, heights, widths, n, k, idx, prob, logits, &err);
+  if (rc != B2I_OK) return fail(rc, err);
+  return B2I_OK;
+}
+
 int b2i_submit_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* idx, float* prob,
                   float* logits, long long* ticket) {
   if (!m || !ticket) return fail(B2I_EINVAL, "null model/ticket");

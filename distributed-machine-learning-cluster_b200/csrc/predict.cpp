@@ -6,6 +6,7 @@
 #include <thread>
 
 #include "../../include/b200_infer.h"
+#include "resize.h"
 
 namespace b2i {
 
@@ -168,6 +169,12 @@ void slot_free(DevSlot* s) {
     for (auto ev : L.copied) if (ev) cudaEventDestroy(ev);
     L = Lane();
   }
+  if (s->raw.d_img) cudaFree(s->raw.d_img);
+  if (s->raw.h_img) cudaFreeHost(s->raw.h_img);
+  if (s->raw.d_tab) cudaFree(s->raw.d_tab);
+  if (s->raw.h_tab) cudaFreeHost(s->raw.h_tab);
+  if (s->raw.d_tmp) cudaFree(s->raw.d_tmp);
+  s->raw = RawScratch();
   for (auto& kv : s->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   s->graphs.clear();
   if (s->copy_st) cudaStreamDestroy(s->copy_st);
@@ -225,6 +232,131 @@ int predict_submit(b2i_model* m, int first_dev, int n_dev, const uint8_t* images
       m->pending[lane].active = false;
       return sh[g].rc;
     }
+  return B2I_OK;
+}
+
+namespace {
+
+bool grow(void** dev, void** host, size_t* cap, size_t need, std::string* err) {
+  if (need <= *cap) return true;
+  const size_t ncap = need + need / 4 + 4096;
+  if (*dev) cudaFree(*dev);
+  if (host && *host) cudaFreeHost(*host);
+  *dev = nullptr;
+  if (host) *host = nullptr;
+  *cap = 0;
+  cudaError_t e = cudaMalloc(dev, ncap);
+  if (e == cudaSuccess && host) e = cudaMallocHost(host, ncap);
+  if (e != cudaSuccess) { *err = std::string("raw-image scratch: ") + cudaGetErrorString(e); return false; }
+  *cap = ncap;
+  return true;
+}
+
+// One GPU's share: plan every image on the host, ship images + tables in two copies, run the two
+// resize passes per image into lane 0's device batch, then the usual chunked forward.
+void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const int* ws, int n, int k,
+               int32_t* idx, float* prob, float* logits, Shard* out) {
+  if (n == 0) return;
+  auto cu = [&](cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return false;
+    out->rc = B2I_ECUDA;
+    out->err = std::string(what) + ": " + cudaGetErrorString(e);
+    return true;
+  };
+  if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
+  Lane& L = s.lane[0];
+  RawScratch& R = s.raw;
+  std::vector<AxisPlan> px(n), py(n);
+  std::vector<size_t> img_off(n), tab_off(n);
+  size_t img_bytes = 0, tab_bytes = 0, tmp_elems = 0;
+  for (int i = 0; i < n; ++i) {
+    if (!images[i] || hs[i] < 1 || ws[i] < 1) { out->rc = B2I_EINVAL; out->err = "image " + std::to_string(i) + " is empty"; return; }
+    plan_image(hs[i], ws[i], &px[i], &py[i]);
+    img_off[i] = img_bytes;
+    img_bytes += (static_cast<size_t>(hs[i]) * ws[i] * 3 + 255) & ~static_cast<size_t>(255);
+    tab_off[i] = tab_bytes;
+    tab_bytes += ((4 * 224 * 4 + (px[i].idx.size() + py[i].idx.size()) * 8) + 255) & ~static_cast<size_t>(255);
+    tmp_elems = std::max(tmp_elems, static_cast<size_t>(hs[i]) * 224 * 3);
+  }
+  if (!grow(reinterpret_cast<void**>(&R.d_img), reinterpret_cast<void**>(&R.h_img), &R.img_cap, img_bytes, &out->err) ||
+      !grow(reinterpret_cast<void**>(&R.d_tab), reinterpret_cast<void**>(&R.h_tab), &R.tab_cap, tab_bytes, &out->err) ||
+      !grow(reinterpret_cast<void**>(&R.d_tmp), nullptr, &R.tmp_cap, tmp_elems * 4, &out->err)) {
+    out->rc = B2I_ENOMEM;
+    return;
+  }
+  std::vector<ResizeJob> jobs(n);
+  for (int i = 0; i < n; ++i) {
+    std::memcpy(R.h_img + img_off[i], images[i], static_cast<size_t>(hs[i]) * ws[i] * 3);
+    uint8_t* ht = R.h_tab + tab_off[i];
+    uint8_t* dt = R.d_tab + tab_off[i];
+    size_t o = 0;
+    auto put = [&](const void* src, size_t bytes) { std::memcpy(ht + o, src, bytes); const size_t at = o; o += bytes; return at; };
+    ResizeJob& j = jobs[i];
+    j.d_img = R.d_img + img_off[i]; j.h = hs[i]; j.w = ws[i];
+    j.xf = reinterpret_cast<const int*>(dt + put(px[i].first.data(), 224 * 4));
+    j.xc = reinterpret_cast<const int*>(dt + put(px[i].count.data(), 224 * 4));
+    j.yf = reinterpret_cast<const int*>(dt + put(py[i].first.data(), 224 * 4));
+    j.yc = reinterpret_cast<const int*>(dt + put(py[i].count.data(), 224 * 4));
+    j.xi = reinterpret_cast<const int*>(dt + put(px[i].idx.data(), px[i].idx.size() * 4));
+    j.yi = reinterpret_cast<const int*>(dt + put(py[i].idx.data(), py[i].idx.size() * 4));
+    j.xw = reinterpret_cast<const float*>(dt + put(px[i].coef.data(), px[i].coef.size() * 4));
+    j.yw = reinterpret_cast<const float*>(dt + put(py[i].coef.data(), py[i].coef.size() * 4));
+    j.d_tmp = R.d_tmp;
+    j.d_out = L.d_in + static_cast<size_t>(i) * B2I_IMAGE_BYTES;
+  }
+  if (cu(cudaMemcpyAsync(R.d_img, R.h_img, img_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D raw images")) return;
+  if (cu(cudaMemcpyAsync(R.d_tab, R.h_tab, tab_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D resize tables")) return;
+  for (int i = 0; i < n; ++i)
+    if (cu(launch_resize_job(jobs[i], s.comp_st), "resize kernels")) return;
+  const int classes = s.dm->classes();
+  if (logits && !L.d_logits) {
+    const size_t cap = static_cast<size_t>(s.dm->max_batch());
+    if (cu(cudaMalloc(reinterpret_cast<void**>(&L.d_logits), cap * classes * 4), "cudaMalloc(logits)")) return;
+    if (cu(cudaMallocHost(reinterpret_cast<void**>(&L.h_logits), cap * classes * 4), "cudaMallocHost(logits)")) return;
+  }
+  for (int off = 0; off < n; off += s.chunk) {
+    const int nb = std::min(s.chunk, n - off);
+    if (!s.dm->forward(L.d_in + static_cast<size_t>(off) * B2I_IMAGE_BYTES, nb, k, L.d_idx + static_cast<size_t>(off) * k,
+                       L.d_prob + static_cast<size_t>(off) * k,
+                       logits ? L.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, &out->err)) {
+      out->rc = B2I_ECUDA;
+      return;
+    }
+  }
+  const size_t nk = static_cast<size_t>(n) * k;
+  if (cu(cudaMemcpyAsync(L.h_idx, L.d_idx, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H idx")) return;
+  if (cu(cudaMemcpyAsync(L.h_prob, L.d_prob, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H prob")) return;
+  if (logits && cu(cudaMemcpyAsync(L.h_logits, L.d_logits, static_cast<size_t>(n) * classes * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H logits")) return;
+  if (cu(cudaStreamSynchronize(s.comp_st), "cudaStreamSynchronize")) return;
+  std::memcpy(idx, L.h_idx, nk * 4);
+  std::memcpy(prob, L.h_prob, nk * 4);
+  if (logits) std::memcpy(logits, L.h_logits, static_cast<size_t>(n) * classes * 4);
+}
+
+}  // namespace
+
+int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
+                const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, std::string* err) {
+  if (n < 0 || (n > 0 && (!images || !heights || !widths || !idx || !prob))) { *err = "null buffer"; return B2I_EINVAL; }
+  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
+  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size())) { *err = "device range outside the model's context"; return B2I_EINVAL; }
+  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch) { *err = "batch exceeds GPUs x max_batch"; return B2I_EINVAL; }
+  if (m->pending[0].active || m->pending[1].active) { *err = "an asynchronous request is still in flight; b2i_wait for it first"; return B2I_EINVAL; }
+  const int per = (n + n_dev - 1) / n_dev;
+  std::vector<Shard> sh(n_dev);
+  auto work = [&](int g) {
+    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
+    raw_shard(m->slots[first_dev + g], images + lo, heights + lo, widths + lo, hi - lo, k, idx + static_cast<size_t>(lo) * k,
+              prob + static_cast<size_t>(lo) * k, logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, &sh[g]);
+  };
+  if (n_dev == 1) work(0);
+  else {
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
+    for (auto& x : th) x.join();
+  }
+  for (int g = 0; g < n_dev; ++g)
+    if (sh[g].rc != B2I_OK) { *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].err; return sh[g].rc; }
   return B2I_OK;
 }
 

@@ -46,8 +46,17 @@ struct GraphEntry {
   cudaGraphExec_t exec = nullptr;
 };
 
+// Grow-only buffers of the raw-image path (predict_raw): packed source images, resampling tables,
+// horizontally resampled rows.
+struct RawScratch {
+  uint8_t* h_img = nullptr; uint8_t* d_img = nullptr; size_t img_cap = 0;   // pinned / device
+  uint8_t* h_tab = nullptr; uint8_t* d_tab = nullptr; size_t tab_cap = 0;
+  float* d_tmp = nullptr; size_t tmp_cap = 0;
+};
+
 struct DevSlot {
   std::unique_ptr<DeviceModel> dm;
+  RawScratch raw;
   cudaStream_t copy_st = nullptr, comp_st = nullptr;
   Lane lane[2];
   int chunk = 0;
@@ -83,6 +92,10 @@ void slot_free(DevSlot* s);
 // [first_dev, first_dev + n_dev) and return its ticket without waiting.  Returns 0 or a B2I_E* code.
 int predict_submit(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
                    int32_t* idx, float* prob, float* logits, long long* ticket, std::string* err);
+// Blocking: decoded images of arbitrary size -> resize + centre crop on the GPU, straight into the
+// device batch -> forward -> results.  images[i] is u8 [heights[i]][widths[i]][3] in host memory.
+int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
+                const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, std::string* err);
 // Block until the request is complete and its results are in the arrays given at submit time.
 int predict_wait(b2i_model* m, long long ticket, std::string* err);
 

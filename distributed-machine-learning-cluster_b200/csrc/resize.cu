@@ -226,6 +226,20 @@ bool resize_crop_224_host(const uint8_t* image, int h, int w, uint8_t* out224, c
 }
 
 
+void plan_image(int h, int w, AxisPlan* px, AxisPlan* py) {
+  const ResizeGeom g = resize_target(h, w);
+  plan_axis(w, g.rw, g.crop_x, px);
+  plan_axis(h, g.rh, g.crop_y, py);
+}
+
+cudaError_t launch_resize_job(const ResizeJob& j, cudaStream_t st) {
+  long long blocks = (static_cast<long long>(j.h) * 224 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  resize_h_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(j.d_img, j.h, j.w, j.xf, j.xc, j.xi, j.xw, j.d_tmp);
+  resize_v_kernel<<<(224 * 224 * 3 + 255) / 256, 256, 0, st>>>(j.d_tmp, j.yf, j.yc, j.yi, j.yw, j.d_out);
+  return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------
 // Allocation-free variant.  Some hosts of this library may not allocate GPU memory at run time: a
 // serving process whose memory pool is carved up once at start-up, code running between stream

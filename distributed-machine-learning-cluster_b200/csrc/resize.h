@@ -31,6 +31,21 @@ void plan_axis(int in_size, int out_size, int crop, AxisPlan* plan);
 bool resize_crop_224_host(const uint8_t* image, int h, int w, uint8_t* out224, cudaStream_t st,
                           std::string* err);
 
+// One image of a batch whose buffers the caller manages (predict_raw): every pointer is a device
+// pointer; enqueues the two passes on `st`.
+struct ResizeJob {
+  const uint8_t* d_img = nullptr;
+  int h = 0, w = 0;
+  const int *xf = nullptr, *xc = nullptr, *xi = nullptr;
+  const float* xw = nullptr;
+  const int *yf = nullptr, *yc = nullptr, *yi = nullptr;
+  const float* yw = nullptr;
+  float* d_tmp = nullptr;     // float [h][224][3]
+  uint8_t* d_out = nullptr;   // u8 [224][224][3]
+};
+cudaError_t launch_resize_job(const ResizeJob& j, cudaStream_t st);
+void plan_image(int h, int w, AxisPlan* px, AxisPlan* py);
+
 // Same two kernels, but no allocation of any kind on the GPU side: device in/out pointers from the
 // caller, scratch in a static device array (limits: resize_static_max_rows() input rows, 16384
 // resampling taps per axis).  Enqueues on `st` and returns without synchronising.

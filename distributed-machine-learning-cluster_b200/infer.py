@@ -228,6 +228,21 @@ class Model:
                                                _ptr(logits)))
         return (idx, prob, logits) if want_logits else (idx, prob)
 
+    def predict_raw(self, images, k=5, want_logits=False, devices=None):
+        """Decoded images of any size (list of u8 [H,W,3] arrays) -> GPU resize + crop -> forward ->
+        (idx, prob[, logits]); the whole Member::predict body after the JPEG decode in one call."""
+        imgs = [np.ascontiguousarray(im, dtype=np.uint8) for im in images]
+        n = len(imgs)
+        ptrs = (ctypes.c_void_p * max(n, 1))(*[im.ctypes.data for im in imgs])
+        hs = (ctypes.c_int * max(n, 1))(*[im.shape[0] for im in imgs])
+        ws = (ctypes.c_int * max(n, 1))(*[im.shape[1] for im in imgs])
+        idx = np.empty((n, k), np.int32)
+        prob = np.empty((n, k), np.float32)
+        logits = np.empty((n, CLASSES), np.float32) if want_logits else None
+        first, count = devices if devices is not None else (0, 0)
+        check(_lib.lib().b2i_predict_raw_u8(self._h, first, count, ptrs, hs, ws, n, k, _ptr(idx), _ptr(prob), _ptr(logits)))
+        return (idx, prob, logits) if want_logits else (idx, prob)
+
     def submit_u8(self, images_u8, idx, prob, logits=None):
         """Asynchronous predict: enqueue and return a ticket. `images_u8` (ideally a PinnedBuffer
         view), `idx` int32 [n,k] and `prob` f32 [n,k] must stay alive until wait(ticket) returns."""

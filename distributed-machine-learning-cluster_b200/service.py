@@ -117,10 +117,10 @@ class MemberState:
             img = decode_image(os.path.join(self.image_root, input_id, entries[0]))
             if img is None:
                 return None
-            batch.append(self.ctx.resize_crop(img))
+            batch.append(img)
         if not batch:
             return []
-        idx, prob = model.predict_u8(np.stack(batch), k=k, devices=devices)
+        idx, prob = model.predict_raw(batch, k=k, devices=devices)   # resize + crop + forward + top-k on the GPU
         if k == 1:
             return [(float(p[0]), self.labels[int(i[0])][1]) for i, p in zip(idx, prob)]
         return [[(float(pp), self.labels[int(ii)][1]) for ii, pp in zip(i, p)] for i, p in zip(idx, prob)]

@@ -109,6 +109,15 @@ int b2i_predict_u8(b2i_model* m, const uint8_t* images, int n, int k, int32_t* i
 int b2i_predict_u8_on(b2i_model* m, int first_dev, int n_dev, const uint8_t* images, int n, int k,
                       int32_t* idx, float* prob, float* logits);
 
+/* The body of `Member::predict` after the JPEG decode in one call (services.rs:492-494): images[i] is
+ * a decoded u8 [heights[i]][widths[i]][3] image in host memory; each is resized + centre-cropped on
+ * the GPU exactly as b2i_resize_crop_u8 does, written straight into the device batch, normalised,
+ * run through the network and reduced to its top-k. Same sharding and outputs as b2i_predict_u8_on;
+ * n_dev <= 0 means all GPUs of the model. Blocking. */
+int b2i_predict_raw_u8(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images,
+                       const int* heights, const int* widths, int n, int k, int32_t* idx, float* prob,
+                       float* logits);
+
 /* Asynchronous pair for throughput: b2i_submit_u8 enqueues the whole request (host->device copy,
  * forward, device->host copy of the results) on all GPUs of the model and returns a ticket at once;
  * b2i_wait blocks until that request is complete and idx/prob(/logits) given at submit time are

@@ -43,6 +43,9 @@ extern "C" {
     pub fn b2i_predict_u8_on(m: *mut b2i_model, first_dev: c_int, n_dev: c_int, images: *const u8,
                              n: c_int, k: c_int, idx: *mut i32, prob: *mut c_float,
                              logits: *mut c_float) -> c_int;
+    pub fn b2i_predict_raw_u8(m: *mut b2i_model, first_dev: c_int, n_dev: c_int, images: *const *const u8,
+                              heights: *const c_int, widths: *const c_int, n: c_int, k: c_int,
+                              idx: *mut i32, prob: *mut c_float, logits: *mut c_float) -> c_int;
     pub fn b2i_submit_u8(m: *mut b2i_model, images: *const u8, n: c_int, k: c_int, idx: *mut i32,
                          prob: *mut c_float, logits: *mut c_float, ticket: *mut c_longlong) -> c_int;
     pub fn b2i_wait(m: *mut b2i_model, ticket: c_longlong) -> c_int;

@@ -260,6 +260,27 @@ def test_graph_replay_of_small_batches_is_transparent(pkg, ctx, resnet18_ot, ale
             assert np.array_equal(lo, lo2)
 
 
+def test_predict_raw_equals_resize_then_predict(pkg, ctx, resnet18_ot):
+    """b2i_predict_raw_u8 (decoded images of any size in, top-k out) is bit-identical to
+    b2i_resize_crop_u8 per image followed by b2i_predict_u8, on fixture JPEGs and synthetic sizes."""
+    from oracle import stb_resize
+    root = os.path.join(GOLDEN, "imagenet_1k", "train")
+    imgs = [stb_resize.decode_image(os.path.join(root, w, sorted(os.listdir(os.path.join(root, w)))[0])) for w in GV["wnids"]]
+    rng = np.random.default_rng(5)
+    imgs += [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in ((224, 224), (90, 301), (640, 480))]
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=16, micro_batch=4) as m:
+        crops = np.stack([ctx.resize_crop(im) for im in imgs])
+        want = m.predict_u8(crops, k=5, want_logits=True)
+        got = m.predict_raw(imgs, k=5, want_logits=True)
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
+        again = m.predict_raw(imgs[:3], k=1)           # scratch buffers are reused
+        assert np.array_equal(again[0][:, 0], want[0][:3, 0])
+        assert m.predict_raw([], k=5)[0].shape == (0, 5)
+    # and the crops themselves are the oracle's
+    assert np.array_equal(crops[0], stb_resize.resize_crop_224(imgs[0]))
+
+
 def test_model_load_errors(pkg, ctx, tmp_path, resnet18_ot):
     with pytest.raises(pkg.B2IError) as e:
         pkg.Model(ctx, "vgg16", resnet18_ot)
