@@ -44,28 +44,61 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock and throttle reasons polled every 20 ms through NVML while the timed regions run
+    (falls back to `nvidia-smi -lms 100` when the NVML binding is missing)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.rows, self.proc = [], None
+        self.sm, self.max_mhz, self.reasons, self.stop_flag = [], None, set(), False
+        self.proc = self.thread = None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except OSError:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            names = {"hw_slowdown": getattr(pynvml, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                     "hw_thermal_slowdown": getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                     "sw_thermal_slowdown": getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                     "sw_power_cap": getattr(pynvml, "nvmlClocksEventReasonSwPowerCap", 0x4)}
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            def poll():
+                while not self.stop_flag:
+                    try:
+                        self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                        get = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                            pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+                        mask = int(get(h))
+                        for k, bit in names.items():
+                            if mask & bit:
+                                self.reasons.add(k)
+                    except Exception:
+                        pass
+                    time.sleep(0.02)
+
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.thread = None
+            try:
+                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
+                                              "--format=csv,noheader,nounits", "-lms", "100"],
+                                             stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                self.rows = []
+                self.reader = threading.Thread(target=lambda: [self.rows.append([c.strip() for c in ln.split(",")])
+                                                               for ln in self.proc.stdout], daemon=True)
+                self.reader.start()
+            except OSError:
+                self.proc = None
 
     def stop(self):
+        if self.thread:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                    "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml, 20 ms"}
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML and no nvidia-smi"], "samples": 0}
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -76,7 +109,7 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvidia-smi, 100 ms"}
 
 
 def cpu_oracle_rate(budget_s, batch=64):
@@ -192,10 +225,10 @@ def main():
             torch.cuda.synchronize()
 
     # ---------------- device-resident timing (value)
+    sampler = ClockSampler(local) if rank == 0 else None   # polls through the device-timed AND the e2e regions
     for i in range(args.warmup):
         step_device(i)
     sync_all()
-    sampler = ClockSampler(local) if rank == 0 else None
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     evs[0].record(stream)
     for i in range(args.steps):
@@ -204,7 +237,6 @@ def main():
     sync_all()
     step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     total_ms = evs[0].elapsed_time(evs[-1])
-    clocks = sampler.stop() if sampler else None
     if world > 1:
         t = torch.tensor([total_ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -241,6 +273,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_total, blocking_total = float(t[0].item()), float(t[1].item())
     e2e_value = world * BATCH * args.steps / e2e_total
+    clocks = sampler.stop() if sampler else None
     e2e_blocking_value = world * BATCH * args.steps / blocking_total
 
     # ---------------- per-launch share (rank 0): CUDA events around every launch of one step

@@ -106,7 +106,11 @@ class DeviceModel {
   int classes() const { return classes_; }
   int num_tensors() const { return static_cast<int>(tshape_.size()); }
   TensorShape tensor_shape(int id) const { return tshape_[id]; }
-  long long launches_per_microbatch() const { return static_cast<long long>(ops_.size()) + 1; }
+  long long launches_per_microbatch() const {   // kernels actually launched: ops folded into a sibling's kernel do not count
+    long long n = 1;                              // softmax + top-k
+    for (const DevOp& d : ops_) n += d.skip ? 0 : 1;
+    return n;
+  }
   size_t weight_bytes() const { return weight_bytes_; }
   size_t activation_bytes() const { return act_bytes_; }
 
