@@ -51,6 +51,7 @@ SIGNATURES = {
     "b2i_ot_read_tensor": (_ll, [_c.c_char_p, _c.c_char_p, _vp, _ll]),
     "b2i_model_load": (_i, [_vp, _c.c_char_p, _c.c_char_p, _c.POINTER(ModelConfig), _c.POINTER(_vp)]),
     "b2i_model_free": (None, [_vp]),
+    "b2i_model_reload": (_i, [_vp, _c.c_char_p]),
     "b2i_model_flops_per_image": (_c.c_double, [_vp]),
     "b2i_model_launches_per_microbatch": (_i, [_vp]),
     "b2i_model_num_devices": (_i, [_vp]),

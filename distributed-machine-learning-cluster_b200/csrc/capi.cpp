@@ -202,6 +202,7 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   ec.fused_stem = fused ? 1 : 0;
 
   auto m = std::make_unique<b2i_model>();
+  m->engine_cfg = ec;
   m->ctx = ctx;
   m->name = name;
   m->flops = net.flops_per_image;
@@ -220,6 +221,36 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
     }
   }
   *out = m.release();
+  return B2I_OK;
+}
+
+int b2i_model_reload(b2i_model* m, const char* ot_path) {
+  if (!m || !ot_path) return fail(B2I_EINVAL, "b2i_model_reload: null argument");
+  std::map<std::string, HostTensor> tensors;
+  std::string err;
+  if (!read_ot_archive(ot_path, &tensors, &err)) return fail(B2I_EIO, err);
+  NetSpec net;
+  const bool ok = m->name == "resnet18" ? build_resnet18(tensors, m->engine_cfg.fused_stem != 0, &net, &err)
+                                        : build_alexnet(tensors, m->engine_cfg.alexnet_geometry, &net, &err);
+  if (!ok) return fail(B2I_EIO, err);
+  tensors.clear();
+  // build the new device copies first (the old ones keep serving), then swap them in under the lock
+  std::vector<std::unique_ptr<DeviceModel>> fresh(m->slots.size());
+  for (size_t i = 0; i < m->slots.size(); ++i) {
+    fresh[i] = std::make_unique<DeviceModel>();
+    if (!fresh[i]->init(m->slots[i].dm->device(), net, m->engine_cfg, &err)) return fail(B2I_ECUDA, err);
+  }
+  std::lock_guard<std::mutex> lock(m->mu);
+  if (m->pending[0].active || m->pending[1].active) return fail(B2I_EINVAL, "requests are in flight; b2i_wait for them before reloading");
+  for (size_t i = 0; i < m->slots.size(); ++i) {
+    DevSlot& s = m->slots[i];
+    cudaSetDevice(s.dm->device());
+    cudaDeviceSynchronize();
+    for (auto& kv : s.graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);   // captured pointers die with the old buffers
+    s.graphs.clear();
+    s.dm = std::move(fresh[i]);
+  }
+  m->flops = net.flops_per_image;
   return B2I_OK;
 }
 

@@ -81,6 +81,7 @@ struct b2i_model {
   int max_batch = 0;
   long long next_ticket = 0;
   b2i::Pending pending[2];
+  b2i::EngineConfig engine_cfg;   // kept for b2i_model_reload
 };
 
 namespace b2i {

@@ -180,6 +180,10 @@ class Model:
         self.max_batch = max_batch
         self.precision = precision
 
+    def reload(self, ot_path):
+        """Swap in the weights of another `.ot` archive of the same architecture (the `train` flow)."""
+        check(_lib.lib().b2i_model_reload(self._h, str(ot_path).encode()))
+
     def close(self):
         if self._h:
             _lib.lib().b2i_model_free(self._h)

@@ -8,6 +8,7 @@ is absent here, see INTEGRATION.md for the cgo-style binding a maintainer would 
   load_model           reference src/model_utils.rs:24-36  (fails loudly instead of swallowing errors)
   predict_image        reference src/model_utils.rs:38-49
   MemberState.predict  reference src/services.rs:475-497   (Member::predict RPC handler body)
+  MemberState.train    reference src/main.rs:231-256       (member side: reload the copied .ot)
   Job                  reference src/services.rs:54-81
   Leader.assign_members reference src/services.rs:199-211  (dual-job fair share; members = GPUs)
   Leader.run_job       reference src/services.rs:407-433   (batched: many ids per predict call)
@@ -90,6 +91,7 @@ class MemberState:
         self.ctx = ctx
         self.labels = labels
         self.image_root = image_root
+        self.weight_dir = weight_dir
         # services.rs:516,522 `.unwrap()`: a missing archive is fatal at start-up
         self.models = {
             name: Model(ctx, name, os.path.join(weight_dir, name + ".ot"), precision=precision,
@@ -100,6 +102,15 @@ class MemberState:
     def close(self):
         for m in self.models.values():
             m.close()
+
+    def train(self, model_name, weight_dir=None):
+        """Member side of the `train <sdfs_file> <model>` command (main.rs:231-256): the leader has
+        just copied a new `<model>.ot` to every member; re-read it and swap the weights in on every
+        GPU.  The reference stops at the copy (its models keep the weights they started with)."""
+        model = self.models.get(model_name)
+        if model is None:
+            raise ValueError("Model not found: %r" % (model_name,))
+        model.reload(os.path.join(weight_dir or self.weight_dir, model_name + ".ot"))
 
     def predict(self, model_name, input_ids, k=1, devices=None):
         """Option<Vec<(f64, String)>>: None for an unknown model (services.rs:480) or when any image

@@ -83,6 +83,14 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
                    const b2i_model_config* cfg, b2i_model** out);
 void b2i_model_free(b2i_model* m);
 
+/* Re-read the weights of a loaded model from `ot_path` (same architecture) and swap them in on every GPU:
+ * the new device copies are built while the old ones keep serving, then exchanged under the model's lock,
+ * so a concurrent predict sees either the old or the new weights, never a mixture. This is the operator
+ * side of the reference's `train <sdfs_file> <model>` command, which lands a new `<model>.ot` on every
+ * member (reference src/main.rs:231-256, src/services.rs:139-144) but never reloads it (load_model at
+ * src/model_utils.rs:24-36 is dead code). On failure the old weights stay active. */
+int b2i_model_reload(b2i_model* m, const char* ot_path);
+
 /* Static facts: algorithmic FLOPs per image, kernel launches per micro-batch, bytes resident. */
 double b2i_model_flops_per_image(const b2i_model* m);
 int b2i_model_launches_per_microbatch(const b2i_model* m);

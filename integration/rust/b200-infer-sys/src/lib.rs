@@ -37,6 +37,7 @@ extern "C" {
     pub fn b2i_model_load(ctx: *mut b2i_ctx, model_name: *const c_char, ot_path: *const c_char,
                           cfg: *const b2i_model_config, out: *mut *mut b2i_model) -> c_int;
     pub fn b2i_model_free(m: *mut b2i_model);
+    pub fn b2i_model_reload(m: *mut b2i_model, ot_path: *const c_char) -> c_int;
     pub fn b2i_model_flops_per_image(m: *const b2i_model) -> c_double;
     pub fn b2i_predict_u8(m: *mut b2i_model, images: *const u8, n: c_int, k: c_int,
                           idx: *mut i32, prob: *mut c_float, logits: *mut c_float) -> c_int;

@@ -68,5 +68,10 @@ impl Model {
         check(rc)?;
         Ok((0..n).map(|i| (0..k).map(|j| (prob[i * k + j] as f64, idx[i * k + j] as usize)).collect()).collect())
     }
+    /// After `train` has copied a new `<model>.ot` to this member (main.rs:231-256): swap the weights in.
+    pub fn reload(&self, ot_path: &str) -> Result<(), Error> {
+        let p = CString::new(ot_path).unwrap();
+        check(unsafe { sys::b2i_model_reload(self.0, p.as_ptr()) })
+    }
 }
 impl Drop for Model { fn drop(&mut self) { unsafe { sys::b2i_model_free(self.0) } } }

@@ -281,6 +281,28 @@ def test_predict_raw_equals_resize_then_predict(pkg, ctx, resnet18_ot):
     assert np.array_equal(crops[0], stb_resize.resize_crop_224(imgs[0]))
 
 
+def test_reload_swaps_weights(pkg, ctx, resnet18_ot, tmp_path):
+    """b2i_model_reload: after the `train` flow drops a new archive, the model answers with the new
+    weights (checked against the oracle on those weights); a bad archive leaves the old ones active."""
+    from oracle import ot_format, synth, tch_oracle
+    w2 = synth.resnet18_weights(seed=7)
+    path2 = str(tmp_path / "resnet18_v2.ot")
+    ot_format.write_ot(path2, w2, stem="resnet18")
+    img = synth.synthetic_images(3, seed=71)
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=FP32, max_batch=4) as m:
+        _, _, lg1 = m.predict_u8(img, k=5, want_logits=True)
+        m.predict_u8(img, k=5)                      # second use: small-batch graph captured on the old buffers
+        m.reload(path2)
+        _, _, lg2 = m.predict_u8(img, k=5, want_logits=True)
+        _, _, ref2 = tch_oracle.predict_u8("resnet18", w2, img, k=5)
+        assert np.abs(lg2 - ref2).max() <= tol_for(FP32, ref2)
+        assert np.abs(lg2 - lg1).max() > 100 * tol_for(FP32, ref2)
+        with pytest.raises(pkg.B2IError):
+            m.reload(str(tmp_path / "missing.ot"))
+        _, _, lg3 = m.predict_u8(img, k=5, want_logits=True)
+        assert np.array_equal(lg3, lg2)
+
+
 def test_model_load_errors(pkg, ctx, tmp_path, resnet18_ot):
     with pytest.raises(pkg.B2IError) as e:
         pkg.Model(ctx, "vgg16", resnet18_ot)
