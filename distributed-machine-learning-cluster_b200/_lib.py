@@ -4,7 +4,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200infer.so")
+# B2I_LIB: another build of the same library (A/B timing of two builds inside one GPU session)
+LIB_PATH = os.environ.get("B2I_LIB") or os.path.join(_HERE, "libb200infer.so")
 
 OK, EINVAL, EIO, ECUDA, ENODEV, ENOMEM = 0, -1, -2, -3, -4, -5
 PREC_BF16, PREC_FP32 = 0, 1

@@ -64,7 +64,6 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
-  __shared__ float lut[3][256];               // (u/255 - mean)/std per channel, exact fp32 ops
   __shared__ __align__(16) float sbias[64];
 
   const int tid = threadIdx.x;
@@ -90,12 +89,6 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     }
     mbar_init(w_full, 1);
     mbar_fence_init();
-  }
-  for (int i = tid; i < 768; i += ST_THREADS) {
-    const int c = i >> 8, u = i & 255;
-    const float mean = c == 0 ? 0.485f : (c == 1 ? 0.456f : 0.406f);
-    const float sd = c == 0 ? 0.229f : (c == 1 ? 0.224f : 0.225f);
-    lut[c][u] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(u), 255.0f), mean), sd);
   }
   if (tid < 64) sbias[tid] = __ldg(p.bias + tid);
   if (warp == 8) tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
@@ -137,8 +130,16 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     // ------------------------------------------------------------------ patch loaders
     const int lt = tid - (ST_DRAIN + 32);
     uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));  // generic pointer to `base`
-    constexpr int ROUNDS = (PATCH_H * PATCH_W + ST_LOADERS - 1) / ST_LOADERS;   // 12
-    constexpr int HALF = ROUNDS / 2;
+    // One task = four neighbouring pixels of one patch row = 12 image bytes, fetched as four aligned
+    // 32-bit words: the patch starts at image column 28*ptx - 5, i.e. at byte 84*ptx - 15 of the row,
+    // which is always 1 past a word boundary (rows are 672 bytes, images 150528).
+    constexpr int GROUPS = PATCH_W / 4;                                       // 10 per patch row
+    constexpr int TASKS = PATCH_H * GROUPS;                                   // 370
+    constexpr int ROUNDS = (TASKS + ST_LOADERS - 1) / ST_LOADERS;             // 3
+    // (u/255 - mean)/std as one FMA per byte: a = 1/(255*std), b = -mean/std.  After rounding to bf16
+    // all 3 x 256 values equal the exact divide-subtract-divide sequence (tests/test_oracle.py::test_stem_fma_normalise_is_exact_in_bf16).
+    const float na[3] = {0x1.18926cp-6f, 0x1.1ed5b2p-6f, 0x1.1d8f56p-6f};     // fp32(1 / (255 * std))
+    const float nb[3] = {-0x1.0f177ap+1f, -0x1.04924ap+1f, -0x1.cdf012p+0f};  // fp32(-mean / std)
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
@@ -147,36 +148,51 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       const int ih0 = 28 * pty - 5, iw0 = 28 * ptx - 5;   // input row / col of patch pixel (0, 0)
       const uint8_t* img = p.in + static_cast<size_t>(n) * (224 * 224 * 3);
       uint8_t* dst = gen_base + B_BYTES + STAGE_BYTES + b * PATCH_BYTES;
+      uint32_t w[ROUNDS][4];
+#pragma unroll
+      for (int k = 0; k < ROUNDS; ++k) {
+        const int e = lt + k * ST_LOADERS;
+        const int py = e / GROUPS, g = e - py * GROUPS;
+        const int ih = ih0 + py;
+        const int wo = 84 * ptx - 16 + 12 * g;             // byte offset of the first word in the image row
+        const bool row_ok = e < TASKS && ih >= 0 && ih < 224;
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(img + ih * 672 + wo);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int o = wo + 4 * j;
+          w[k][j] = (row_ok && o >= 0 && o < 672) ? __ldg(src + j) : 0u;
+        }
+      }
       mbar_wait(patch_empty(b), ((i >> 1) & 1) ^ 1);
 #pragma unroll
-      for (int part = 0; part < 2; ++part) {   // two batches of 6 rounds: 18 byte loads in flight per thread
-        uint32_t r0[HALF], r1[HALF], r2[HALF];
+      for (int k = 0; k < ROUNDS; ++k) {
+        const int e = lt + k * ST_LOADERS;
+        if (e >= TASKS) continue;
+        const int py = e / GROUPS, g = e - py * GROUPS;
+        const int ih = ih0 + py;
+        const bool row_ok = ih >= 0 && ih < 224;
+        // byte q of the 16 loaded ones as a float: 0x4B0000uu is 2^23 + u
+        auto byte_f = [&](int q) {
+          return __uint_as_float(__byte_perm(w[k][q >> 2], 0x4B000000u, 0x7440u | (q & 3))) - 8388608.0f;
+        };
+        uint32_t o[8];
 #pragma unroll
-        for (int k = 0; k < HALF; ++k) {
-          const int e = lt + (part * HALF + k) * ST_LOADERS;
-          const int py = e / PATCH_W, px = e - py * PATCH_W;
-          const int ih = ih0 + py, iw = iw0 + px;
-          r0[k] = 0xFFFFFFFFu;
-          r1[k] = r2[k] = 0;
-          if (e < PATCH_H * PATCH_W && ih >= 0 && ih < 224 && iw >= 0 && iw < 224) {
-            const uint8_t* s3 = img + (ih * 224 + iw) * 3;
-            r0[k] = __ldg(s3);
-            r1[k] = __ldg(s3 + 1);
-            r2[k] = __ldg(s3 + 2);
-          }
+        for (int j = 0; j < 4; ++j) {                      // pixel j = bytes 1+3j .. 3+3j
+          const int iw = iw0 + 4 * g + j;
+          const bool ok = row_ok && iw >= 0 && iw < 224;   // outside the image: the conv's zero padding
+          const float r = fmaf(byte_f(1 + 3 * j), na[0], nb[0]);
+          const float gg = fmaf(byte_f(2 + 3 * j), na[1], nb[1]);
+          const float bl = fmaf(byte_f(3 + 3 * j), na[2], nb[2]);
+          o[2 * j] = ok ? pack_bf16x2(r, gg) : 0u;
+          o[2 * j + 1] = ok ? pack_bf16x2(bl, 0.f) : 0u;
         }
-#pragma unroll
-        for (int k = 0; k < HALF; ++k) {
-          const int e = lt + (part * HALF + k) * ST_LOADERS;
-          if (e < PATCH_H * PATCH_W) {
-            uint2 v = make_uint2(0u, 0u);        // outside the image: the conv's zero padding
-            if (r0[k] != 0xFFFFFFFFu) {
-              v.x = pack_bf16x2(lut[0][r0[k]], lut[1][r1[k]]);
-              v.y = pack_bf16x2(lut[2][r2[k]], 0.f);
-            }
-            *reinterpret_cast<uint2*>(dst + e * 8) = v;
-          }
-        }
+        // two 16-byte stores; odd groups of four lanes write their halves in the other order so that
+        // each store instruction covers all 32 banks once per eight lanes
+        uint4* d4 = reinterpret_cast<uint4*>(dst + e * 32);
+        const int first = (lt >> 2) & 1;
+        const uint4 lo = make_uint4(o[0], o[1], o[2], o[3]), hi = make_uint4(o[4], o[5], o[6], o[7]);
+        d4[first] = first ? hi : lo;
+        d4[first ^ 1] = first ? lo : hi;
       }
       fence_proxy_async_smem();                // generic-proxy stores -> visible to the tensor core
       mbar_arrive(patch_full(b));
@@ -291,6 +307,7 @@ cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap*
     attr_set[dev] = true;
   }
   if (n_images < 1 || !tmW) return cudaErrorInvalidValue;
+  if (reinterpret_cast<uintptr_t>(in_u8) & 3) return cudaErrorMisalignedAddress;   // the loaders fetch aligned words
   StemParams p;
   p.in = in_u8;
   p.out = static_cast<__nv_bfloat16*>(out_bf16);

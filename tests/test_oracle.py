@@ -85,6 +85,22 @@ def test_normalize_matches_definition():
         assert np.allclose(x[c], want, rtol=0, atol=1e-6)
 
 
+def test_stem_fma_normalise_is_exact_in_bf16():
+    """csrc/stem.cu normalises with one fp32 FMA per byte (u * a + b, the constants below) instead of
+    the oracle's divide / subtract / divide.  For every one of the 3 x 256 possible inputs both give
+    the same bf16 value, so the fused stem sees bit-identical pixels."""
+    na = [float.fromhex("0x1.18926cp-6"), float.fromhex("0x1.1ed5b2p-6"), float.fromhex("0x1.1d8f56p-6")]
+    nb = [float.fromhex("-0x1.0f177ap+1"), float.fromhex("-0x1.04924ap+1"), float.fromhex("-0x1.cdf012p+0")]
+    u = np.arange(256, dtype=np.float32)
+    for c in range(3):
+        assert np.float32(na[c]) == np.float32(1.0 / (255.0 * tch_oracle.STD[c]))
+        assert np.float32(nb[c]) == np.float32(-tch_oracle.MEAN[c] / tch_oracle.STD[c])
+        exact = ((u / np.float32(255.0)) - np.float32(tch_oracle.MEAN[c])) / np.float32(tch_oracle.STD[c])
+        fma = (u.astype(np.float64) * na[c] + nb[c]).astype(np.float32)   # the product and sum are exact in f64
+        to_bf16 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(torch.bfloat16)
+        assert torch.equal(to_bf16(exact), to_bf16(fma))
+
+
 def test_softmax_topk_sorted_and_normalised():
     lg = torch.randn(7, 1000, generator=torch.Generator().manual_seed(0))
     idx, prob = tch_oracle.softmax_topk(lg, 5)
