@@ -358,6 +358,11 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       const char* terr = "";
       if (make_tmap_weights(&d.tmB, d.w, 64, 256, 64, &terr)) { *err = std::string("stem: ") + terr; return false; }
       d.has_tmB = true;
+      void* sp = nullptr;                      // the stem kernel's tile counter (two words, zero between launches)
+      B2I_CUDA(cudaMalloc(&sp, 256));
+      B2I_CUDA(cudaMemset(sp, 0, 256));
+      owned_.push_back(sp);
+      stem_sched_ = static_cast<unsigned int*>(sp);
     }
     if (o.kind == OpSpec::CONV) {
       const ConvSpec& c = net.convs[o.conv];
@@ -481,7 +486,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     if (d.skip) { mark(); continue; }
     switch (o.kind) {
       case OpSpec::STEM:
-        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias, nb, st));
+        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias, nb, stem_sched_, st));
         break;
       case OpSpec::NORMALIZE:
         B2I_CUDA(launch_normalize_u8(d_u8, buf(o.out), dt, static_cast<long long>(nb) * 224 * 224, st));

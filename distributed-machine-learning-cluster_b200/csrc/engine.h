@@ -141,6 +141,7 @@ class DeviceModel {
   std::vector<void*> bufs_;
   std::vector<size_t> buf_bytes_;
   std::vector<void*> owned_;         // weight allocations
+  unsigned int* stem_sched_ = nullptr;
   int logits_tensor_ = -1;
   size_t weight_bytes_ = 0, act_bytes_ = 0;
 };

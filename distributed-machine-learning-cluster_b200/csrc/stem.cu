@@ -40,11 +40,23 @@ constexpr uint32_t STAGE_BYTES = 256 * 128;        // conv outputs of one tile, 
 constexpr uint32_t STEM_SMEM = B_BYTES + STAGE_BYTES + 2 * PATCH_BYTES + 1024;
 constexpr uint32_t TMEM_COLS = 256;                // 2 tiles in flight x two 128x64 fp32 accumulators
 
+#ifdef B2I_STEM_TRACE
+// tools/microbench/stem_trace.cu: clock64 stamps of CTA 0's three roles for its first 64 tiles
+__device__ long long g_stem_trace[64][12];
+__device__ long long g_stem_cta[512][2];   // globaltimer at entry / exit of every CTA
+__device__ __forceinline__ long long stem_now_ns() { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); return (long long)ns; }
+#define STEM_STAMP(tile_i, slot, cond) do { if (blockIdx.x == 0 && (tile_i) < 64 && (cond)) { g_stem_trace[tile_i][slot] = clock64(); \
+    if ((slot) == 10) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); g_stem_trace[tile_i][11] = (long long)ns; } } } while (0)
+#else
+#define STEM_STAMP(tile_i, slot, cond) do { } while (0)
+#endif
+
 struct StemParams {
   const uint8_t* in;
   __nv_bfloat16* out;
   const float* bias;
   int total_tiles;  // N * 64
+  unsigned int* sched;  // [0] tiles handed out beyond the first gridDim.x, [1] CTAs done; both zero between launches
 };
 
 // A-operand descriptor over the RAW patch (no swizzle, K-major): row i of an 8-row core matrix is
@@ -65,8 +77,13 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
   __shared__ __align__(16) float sbias[64];
+  __shared__ int tile_ring[8];   // tile of iteration i (or -1 = no more), written by the loaders, read by the other roles
+  __shared__ int next_tile[2];
 
   const int tid = threadIdx.x;
+#ifdef B2I_STEM_TRACE
+  if (tid == 0 && blockIdx.x < 512) g_stem_cta[blockIdx.x][0] = stem_now_ns();
+#endif
   const int warp = tid >> 5;
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -106,12 +123,16 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     }
     mbar_wait(w_full, 0);
     const uint32_t idesc = umma_idesc_bf16(128, 64);
-    int i = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+    for (int i = 0;; ++i) {
       const int b = i & 1;
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
       mbar_wait(patch_full(b), (i >> 1) & 1);
+      if (*reinterpret_cast<volatile int*>(&tile_ring[i & 7]) < 0) {   // out of tiles: pass the news on to the drain warps
+        umma_commit_elect(acc_full(b));   // arrives once every earlier MMA has completed, i.e. after their own commits
+        break;
+      }
       tc_fence_after();
+      STEM_STAMP(i, 3, lane == 0);
       const uint32_t pbase = patch0 + b * PATCH_BYTES;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {          // conv columns 0-7 / 8-15 of the 16x16 patch
@@ -125,6 +146,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       }
       umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
       umma_commit_elect(acc_full(b));
+      STEM_STAMP(i, 4, lane == 0);
     }
   } else if (warp > 8) {
     // ------------------------------------------------------------------ patch loaders
@@ -140,14 +162,27 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     // all 3 x 256 values equal the exact divide-subtract-divide sequence (tests/test_oracle.py::test_stem_fma_normalise_is_exact_in_bf16).
     const float na[3] = {0x1.18926cp-6f, 0x1.1ed5b2p-6f, 0x1.1d8f56p-6f};     // fp32(1 / (255 * std))
     const float nb[3] = {-0x1.0f177ap+1f, -0x1.04924ap+1f, -0x1.cdf012p+0f};  // fp32(-mean / std)
-    int i = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+    // Tiles are handed out dynamically (the first one is blockIdx.x, the rest come from a global
+    // counter): the two CTAs of an SM do not run at the same speed, a static split leaves a 20 % tail.
+    int t = blockIdx.x;
+    for (int i = 0;; ++i) {
       const int b = i & 1;
+      if (lt == 0) tile_ring[i & 7] = t < p.total_tiles ? t : -1;
+      if (t >= p.total_tiles) {
+        // not before the MMA warp has consumed this barrier's previous phase (two completed phases
+        // look like none to a parity wait)
+        mbar_wait(patch_empty(b), ((i >> 1) & 1) ^ 1);
+        mbar_arrive(patch_full(b));
+        break;
+      }
+      unsigned int ticket = 0;
+      if (lt == 0) ticket = atomicAdd(p.sched, 1u);          // needed only at the end of this tile
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
       const int ih0 = 28 * pty - 5, iw0 = 28 * ptx - 5;   // input row / col of patch pixel (0, 0)
       const uint8_t* img = p.in + static_cast<size_t>(n) * (224 * 224 * 3);
       uint8_t* dst = gen_base + B_BYTES + STAGE_BYTES + b * PATCH_BYTES;
+      STEM_STAMP(i, 0, lt == 0);
       uint32_t w[ROUNDS][4];
 #pragma unroll
       for (int k = 0; k < ROUNDS; ++k) {
@@ -164,6 +199,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
         }
       }
       mbar_wait(patch_empty(b), ((i >> 1) & 1) ^ 1);
+      STEM_STAMP(i, 1, lt == 0);
 #pragma unroll
       for (int k = 0; k < ROUNDS; ++k) {
         const int e = lt + k * ST_LOADERS;
@@ -196,20 +232,26 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       }
       fence_proxy_async_smem();                // generic-proxy stores -> visible to the tensor core
       mbar_arrive(patch_full(b));
+      STEM_STAMP(i, 2, lt == 0);
+      if (lt == 0) next_tile[b] = static_cast<int>(gridDim.x + ticket);
+      asm volatile("bar.sync 2, %0;" ::"n"(ST_LOADERS) : "memory");
+      t = *reinterpret_cast<volatile int*>(&next_tile[b]);
     }
   } else {
     // ------------------------------------------------------------------ drain + pool (warps 0-7)
     const int h = warp >> 2, q = warp & 3;
-    int i = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
+    const uint8_t* const stage_gen = smem_raw + (stage - smem_u32(smem_raw));  // generic pointer to the staging tile
+    for (int i = 0;; ++i) {
       const int b = i & 1;
+      mbar_wait(acc_full(b), (i >> 1) & 1);
+      const int t = *reinterpret_cast<volatile int*>(&tile_ring[i & 7]);
+      if (t < 0) break;
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
-      const int oh0 = 14 * pty - 1, ow0 = 14 * ptx - 1;   // conv row / col of patch slot (0, 0)
 
       // accumulators -> +bias, ReLU, bf16 -> staging tile [ly*16 + lx][64], 16-byte chunks XOR-swizzled
-      mbar_wait(acc_full(b), (i >> 1) & 1);
       tc_fence_after();
+      STEM_STAMP(i, 5, tid == 0);
       {
         const int mrow = q * 32 + lane;                    // row inside this half's 128-row MMA
         const int srow = (mrow >> 3) * 16 + h * 8 + (mrow & 7);
@@ -225,6 +267,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty(b));      // TMEM buffer free for tile i+2
+            STEM_STAMP(i, 6, tid == 0);
           }
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -241,59 +284,78 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
           }
         }
       }
+      STEM_STAMP(i, 7, tid == 0);
       asm volatile("bar.sync 1, %0;" ::"n"(ST_DRAIN) : "memory");
-      // 3x3 stride-2 max over the staging tile -> pooled 7x7x64, two 16-byte chunks per thread
-      if (tid < 49 * 4) {
-        const int pp = tid >> 2, c8 = (tid & 3) * 2;
+      STEM_STAMP(i, 8, tid == 0);
+      // 3x3 stride-2 max over the staging tile -> pooled 7x7x64.  One task = one pooled pixel x one
+      // 16-byte chunk; eight neighbouring lanes read one whole 128-byte staging row per tap, which
+      // is bank-conflict free whatever the row's XOR swizzle.
+      const int cy_min = pty == 0 ? 1 : 0, cx_min = ptx == 0 ? 1 : 0;   // patch slot 0 is conv row / column -1 there
+      for (int task = tid; task < 49 * 8; task += ST_DRAIN) {
+        const int pp = task >> 3;
+        const uint32_t ch = static_cast<uint32_t>(task & 7);
         const int py = pp / 7, px = pp - py * 7;
-        // packed bf16x2 max: values are post-ReLU (>= 0) and the centre tap is always valid, so 0 is a safe start
-        __nv_bfloat162 mx[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) mx[e] = __floats2bfloat162_rn(0.f, 0.f);
+        // Window taps that fall outside the image (only possible at its top / left edge) are clamped
+        // onto the first valid row / column: a duplicate tap leaves the max unchanged, and the nine
+        // loads carry no branches, so they are all in flight together.
+        uint4 tap[9];
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy) {
-          const int cy = 2 * py + dy;
-          const int oh = oh0 + cy;
-          if (oh < 0 || oh >= 112) continue;
+          const int cy = max(2 * py + dy, cy_min);
 #pragma unroll
           for (int dx = 0; dx < 3; ++dx) {
-            const int cx = 2 * px + dx;
-            const int ow = ow0 + cx;
-            if (ow < 0 || ow >= 112) continue;
-            const int row = cy * 16 + cx;
-#pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-              const uint32_t a = stage + static_cast<uint32_t>(row) * 128u + ((static_cast<uint32_t>(c8 + cc) ^ (row & 7)) << 4);
-              uint32_t xs[4];
-              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(xs[0]), "=r"(xs[1]), "=r"(xs[2]), "=r"(xs[3]) : "r"(a));
-#pragma unroll
-              for (int e = 0; e < 4; ++e)
-                mx[cc * 4 + e] = __hmax2(mx[cc * 4 + e], *reinterpret_cast<const __nv_bfloat162*>(&xs[e]));
-            }
+            const int cx = max(2 * px + dx, cx_min);
+            const uint32_t row = static_cast<uint32_t>(cy * 16 + cx);
+            tap[dy * 3 + dx] = *reinterpret_cast<const uint4*>(stage_gen + row * 128u + ((ch ^ (row & 7u)) << 4));
           }
         }
-        const int ph = pty * 7 + py, pw = ptx * 7 + px;
-        uint4* o = reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + c8 * 8);
-        const uint32_t* mw = reinterpret_cast<const uint32_t*>(mx);
+        __nv_bfloat162 mx[4];
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) o[cc] = make_uint4(mw[cc * 4 + 0], mw[cc * 4 + 1], mw[cc * 4 + 2], mw[cc * 4 + 3]);
+        for (int e = 0; e < 4; ++e) {
+          mx[e] = *reinterpret_cast<const __nv_bfloat162*>(&reinterpret_cast<const uint32_t*>(&tap[0])[e]);
+#pragma unroll
+          for (int k = 1; k < 9; ++k)
+            mx[e] = __hmax2(mx[e], *reinterpret_cast<const __nv_bfloat162*>(&reinterpret_cast<const uint32_t*>(&tap[k])[e]));
+        }
+        const int ph = pty * 7 + py, pw = ptx * 7 + px;
+        const uint32_t* mw = reinterpret_cast<const uint32_t*>(mx);
+        *reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + ch * 8) =
+            make_uint4(mw[0], mw[1], mw[2], mw[3]);
       }
+      STEM_STAMP(i, 9, tid == 0);
       asm volatile("bar.sync 1, %0;" ::"n"(ST_DRAIN) : "memory");  // staging tile is rewritten next iteration
+      STEM_STAMP(i, 10, tid == 0);
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) {   // the last CTA out re-arms the tile counter for the next launch
+    __threadfence();
+    if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+      p.sched[0] = 0;
+      p.sched[1] = 0;
+      __threadfence();
+    }
+  }
   if (warp == 8) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+#ifdef B2I_STEM_TRACE
+    if (lane == 0 && blockIdx.x < 512) g_stem_cta[blockIdx.x][1] = stem_now_ns();
+#endif
   }
 }
 
 }  // namespace
 
+#ifdef B2I_STEM_TRACE
+cudaError_t stem_trace_read(long long* host) { return cudaMemcpyFromSymbol(host, g_stem_trace, sizeof(g_stem_trace)); }
+cudaError_t stem_cta_read(long long* host) { return cudaMemcpyFromSymbol(host, g_stem_cta, sizeof(g_stem_cta)); }
+#endif
+
 cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                        const float* bias, int n_images, cudaStream_t st) {
+                        const float* bias, int n_images, unsigned int* sched, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
@@ -306,13 +368,14 @@ cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap*
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  if (n_images < 1 || !tmW) return cudaErrorInvalidValue;
+  if (n_images < 1 || !tmW || !sched) return cudaErrorInvalidValue;
   if (reinterpret_cast<uintptr_t>(in_u8) & 3) return cudaErrorMisalignedAddress;   // the loaders fetch aligned words
   StemParams p;
   p.in = in_u8;
   p.out = static_cast<__nv_bfloat16*>(out_bf16);
   p.bias = bias;
   p.total_tiles = n_images * 64;
+  p.sched = sched;
   const int grid = p.total_tiles < 2 * sm_count[dev] ? p.total_tiles : 2 * sm_count[dev];
   stem_kernel<<<grid, ST_THREADS, STEM_SMEM, st>>>(*tmW, p);
   return cudaGetLastError();
