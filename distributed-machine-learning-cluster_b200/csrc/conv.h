@@ -71,9 +71,10 @@ int conv_umma_pick_stages(int BN);
 // Fused ResNet stem (bf16 path): u8 [n][224][224][3] -> normalise -> conv1 7x7/2 + folded BN + ReLU ->
 // max-pool 3x3/2 -> bf16 [n][56][56][64].  tmW: weight map over [64][256] (K order r, s<8, c<4).
 // sched: two zero-initialised device words (the kernel's tile counter; it leaves them zero again), not
-// shared by launches that may overlap.  in_u8 must be 4-byte aligned.
+// shared by launches that may overlap.  in_u8 must be 4-byte aligned.  bias_host: 64 floats in HOST memory
+// (they travel as kernel parameters).
 cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                        const float* bias, int n_images, unsigned int* sched, cudaStream_t st);
+                        const float* bias_host, int n_images, unsigned int* sched, cudaStream_t st);
 
 // fp32 FFMA path (the 1e-4 parity mode; also the on-device cross-check for the tcgen05 path).
 cudaError_t launch_conv_fp32(const ConvArgs& a, cudaStream_t st);

@@ -355,6 +355,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       B2I_CUDA(cudaMemcpy(bp, c.bias.data(), c.bias.size() * 4, cudaMemcpyHostToDevice));
       owned_.push_back(bp);
       d.bias = static_cast<float*>(bp);
+      d.bias_host.assign(c.bias.begin(), c.bias.begin() + 64);
       const char* terr = "";
       if (make_tmap_weights(&d.tmB, d.w, 64, 256, 64, &terr)) { *err = std::string("stem: ") + terr; return false; }
       d.has_tmB = true;
@@ -486,7 +487,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     if (d.skip) { mark(); continue; }
     switch (o.kind) {
       case OpSpec::STEM:
-        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias, nb, stem_sched_, st));
+        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, st));
         break;
       case OpSpec::NORMALIZE:
         B2I_CUDA(launch_normalize_u8(d_u8, buf(o.out), dt, static_cast<long long>(nb) * 224 * 224, st));

@@ -120,6 +120,7 @@ class DeviceModel {
     ConvGeom g{};
     void* w = nullptr;
     float* bias = nullptr;
+    std::vector<float> bias_host;   // fused stem only: its bias travels as kernel parameters
     CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};
     bool has_tmA = false, has_tmB = false;
     int amode = 0, BN = 0, stages = 0, b_tma = 0, patch = 0, pair = 0;

@@ -54,7 +54,7 @@ __device__ __forceinline__ long long stem_now_ns() { unsigned long long ns; asm 
 struct StemParams {
   const uint8_t* in;
   __nv_bfloat16* out;
-  const float* bias;
+  float bias[64];      // folded BN bias, by value: the drain warps read it as constant-bank operands
   int total_tiles;  // N * 64
   unsigned int* sched;  // [0] tiles handed out beyond the first gridDim.x, [1] CTAs done; both zero between launches
 };
@@ -76,7 +76,6 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
-  __shared__ __align__(16) float sbias[64];
   __shared__ int tile_ring[8];   // tile of iteration i (or -1 = no more), written by the loaders, read by the other roles
   __shared__ int next_tile[2];
 
@@ -107,7 +106,6 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     mbar_init(w_full, 1);
     mbar_fence_init();
   }
-  if (tid < 64) sbias[tid] = __ldg(p.bias + tid);
   if (warp == 8) tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
   tc_fence_before();
   __syncthreads();
@@ -272,11 +270,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float f[8];
-            const float4 b0 = *reinterpret_cast<const float4*>(&sbias[c * 32 + g * 8]);
-            const float4 b1 = *reinterpret_cast<const float4*>(&sbias[c * 32 + g * 8 + 4]);
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + bb[e], 0.f);
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + p.bias[c * 32 + g * 8 + e], 0.f);
             const uint32_t chunk = static_cast<uint32_t>(c * 4 + g);
             asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_row + ((chunk ^ sw) << 4)),
                          "r"(pack_bf16x2(f[0], f[1])), "r"(pack_bf16x2(f[2], f[3])),
@@ -355,7 +350,7 @@ cudaError_t stem_cta_read(long long* host) { return cudaMemcpyFromSymbol(host, g
 #endif
 
 cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                        const float* bias, int n_images, unsigned int* sched, cudaStream_t st) {
+                        const float* bias_host, int n_images, unsigned int* sched, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
@@ -368,12 +363,12 @@ cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap*
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  if (n_images < 1 || !tmW || !sched) return cudaErrorInvalidValue;
+  if (n_images < 1 || !tmW || !sched || !bias_host) return cudaErrorInvalidValue;
   if (reinterpret_cast<uintptr_t>(in_u8) & 3) return cudaErrorMisalignedAddress;   // the loaders fetch aligned words
   StemParams p;
   p.in = in_u8;
   p.out = static_cast<__nv_bfloat16*>(out_bf16);
-  p.bias = bias;
+  for (int c = 0; c < 64; ++c) p.bias[c] = bias_host[c];
   p.total_tiles = n_images * 64;
   p.sched = sched;
   const int grid = p.total_tiles < 2 * sm_count[dev] ? p.total_tiles : 2 * sm_count[dev];

@@ -20,17 +20,19 @@ int main() {
   for (auto& v : h) v = rand() & 255;
   cudaMemcpy(d_in, h.data(), h.size(), cudaMemcpyHostToDevice);
   cudaMemset(d_w, 0, 64 * 256 * 2); cudaMemset(d_bias, 0, 256);
+  static float h_bias[64];
   CUtensorMap tm; const char* err = nullptr;
   if (make_tmap_weights(&tm, d_w, 64, 256, 64, &err)) { printf("tmap: %s\n", err); return 1; }
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   for (int rep = 0; rep < 200; ++rep) {
     cudaEventRecord(e0);
-    cudaError_t e = launch_stem(d_in, d_out, &tm, d_bias, N, d_sched, 0);
+    cudaError_t e = launch_stem(d_in, d_out, &tm, h_bias, N, d_sched, 0);
     cudaEventRecord(e1);
     cudaError_t s = cudaDeviceSynchronize();
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     if (rep < 3 || rep >= 197) printf("rep %d: %.4f ms [%s / %s]\n", rep, ms, cudaGetErrorString(e), cudaGetErrorString(s));
   }
+#ifdef B2I_STEM_TRACE
   static long long t[64][12];
   stem_trace_read(&t[0][0]);
   const long long z = t[0][0];
@@ -55,5 +57,6 @@ int main() {
   printf("exit time per CTA (us):");
   for (int i = 0; i < 296; ++i) { if (i % 16 == 0) printf("\n%3d:", i); printf(" %5.1f", (c[i][1] - t_first) * 1e-3); }
   printf("\n");
+#endif
   return 0;
 }
