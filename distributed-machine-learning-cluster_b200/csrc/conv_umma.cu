@@ -101,7 +101,7 @@ __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, cons
     const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const uint4 rv = __ldg(rp + q);
+      const uint4 rv = __ldcg(rp + q);   // written by an earlier kernel that may have overlapped this one's start: no L1
       const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
@@ -133,6 +133,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr bool A_IS_TMA = (AMODE == A_IM2COL || AMODE == A_TILED);
   static_assert(!(A_IS_TMA && !B_TMA), "TMA A with gathered B is not a supported combination");
 
+  griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 1];
   __shared__ uint32_t tmem_slot;
@@ -170,6 +171,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
   if (warp < 4) {
     // ------------------------------------------------------------------ gather producer
@@ -352,6 +354,7 @@ __global__ void __launch_bounds__(PTHREADS, 1)
 conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                             const __grid_constant__ CUtensorMap tmB,
                             const __grid_constant__ CUtensorMap tmB2, const KP p) {
+  griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
   __shared__ uint32_t tmem_slot;
@@ -389,6 +392,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
   if (warp == 0) {
     if (lane == 0) {
@@ -569,6 +573,7 @@ template <int AMODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
 conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmB2, const KP p) {
+  griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
   __shared__ uint32_t tmem_slot;
@@ -617,6 +622,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
   if (warp == 0) {
     if (lane == 0) {
@@ -783,6 +789,7 @@ __global__ void __launch_bounds__(PATCH_THREADS, 1)
 conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                          const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
                          const PatchP p) {
+  griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[3 * PT_BUFS + 5];  // patch_full[], patch_empty[], res_empty[], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
@@ -827,6 +834,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
@@ -1014,8 +1022,7 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2);
   const int grid2 = total2 < sm_count[dev] ? total2 : sm_count[dev];
   (void)grid;
-  kern<<<dim3(static_cast<unsigned>(grid2)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
-  return cudaGetLastError();
+  return launch_pdl(kern, dim3(static_cast<unsigned>(grid2)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
 template <int AMODE>
@@ -1044,8 +1051,7 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   const int total = p.tiles_m * (p.tiles_n + p.tiles_n2);
   int grid = std::min(2 * total, sm_count[dev] & ~1);
   const size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
-  kern<<<dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st>>>(*tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
-  return cudaGetLastError();
+  return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
 cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmW,
@@ -1076,8 +1082,7 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   p.residual = static_cast<const __nv_bfloat16*>(a.residual);
   p.out = static_cast<__nv_bfloat16*>(a.out);
   const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
-  conv3x3_c64_patch_kernel<<<grid, PATCH_THREADS, smem, st>>>(*tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
-  return cudaGetLastError();
+  return launch_pdl(conv3x3_c64_patch_kernel, dim3(grid), dim3(PATCH_THREADS), smem, st, *tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
 }
 
 template <int AMODE, bool B_TMA>
@@ -1098,8 +1103,10 @@ cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMa
   const int tiles_m = p.tiles_m;
   const size_t smem = conv_umma_smem_bytes(a.BN, a.stages);
   static const CUtensorMap dummy = {};
-  kern<<<dim3(static_cast<unsigned>(tiles_m * p.tiles_n)), dim3(NTHREADS), smem, st>>>(
-      tmA ? *tmA : dummy, tmB ? *tmB : dummy, p);
+  const dim3 grid(static_cast<unsigned>(tiles_m * p.tiles_n));
+  if (AMODE == A_IM2COL || AMODE == A_TILED)   // activations arrive by TMA (L2): safe to start under the previous kernel's tail
+    return launch_pdl(kern, grid, dim3(NTHREADS), smem, st, tmA ? *tmA : dummy, tmB ? *tmB : dummy, p);
+  kern<<<grid, dim3(NTHREADS), smem, st>>>(tmA ? *tmA : dummy, tmB ? *tmB : dummy, p);   // gathered A goes through L1
   return cudaGetLastError();
 }
 

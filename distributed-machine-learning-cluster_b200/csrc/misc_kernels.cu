@@ -2,6 +2,7 @@
 // average pool, fused softmax + top-k.  All are HBM-bound: coalesced 16-byte accesses along the
 // NHWC channel axis, grids sized in multiples of the 148 SMs, warp shuffles for reductions.
 #include "ops.h"
+#include "ptx.cuh"
 
 #include <cuda_bf16.h>
 #include <float.h>
@@ -173,14 +174,16 @@ __global__ void __launch_bounds__(256) global_avgpool_kernel(const void* __restr
   const int c = threadIdx.x % cv, g = threadIdx.x / cv;
   const int n = blockIdx.x;
   float a[8] = {};
+  griddep_launch();
+  griddep_wait();   // launched under the tail of the last conv; its output is read below, past L1 (__ldcg)
   if (g < groups) {
     for (int px = g; px < HW; px += groups) {
       const size_t off = (static_cast<size_t>(n) * HW + px) * C + c * vec;
       if (F32) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(in) + off));
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(static_cast<const float*>(in) + off));
         a[0] += v.x; a[1] += v.y; a[2] += v.z; a[3] += v.w;
       } else {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(in) + off));
+        const uint4 v = __ldcg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(in) + off));
         const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -221,6 +224,8 @@ __global__ void __launch_bounds__(256) softmax_topk_kernel(const float* __restri
                                                             float* __restrict__ prob) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  griddep_launch();
+  griddep_wait();
   if (row >= rows) return;
   const float* x = logits + static_cast<size_t>(row) * ld;
   float v[kMaxPerLane];
@@ -228,7 +233,7 @@ __global__ void __launch_bounds__(256) softmax_topk_kernel(const float* __restri
 #pragma unroll
   for (int j = 0; j < kMaxPerLane; ++j) {
     const int c = lane + 32 * j;
-    v[j] = (c < classes) ? __ldg(x + c) : -FLT_MAX;
+    v[j] = (c < classes) ? __ldcg(x + c) : -FLT_MAX;
     mx = fmaxf(mx, v[j]);
   }
 #pragma unroll
@@ -310,9 +315,8 @@ cudaError_t launch_adaptive_avgpool(const void* in, void* out, int dtype, int N,
   if (C % vec) return cudaErrorInvalidValue;
   const int cv = C / vec;
   if (OH == 1 && OW == 1 && cv <= 256 && 256 % cv == 0) {
-    if (dtype == DT_F32) global_avgpool_kernel<true><<<N, 256, 0, st>>>(in, out, H * W, C);
-    else global_avgpool_kernel<false><<<N, 256, 0, st>>>(in, out, H * W, C);
-    return cudaGetLastError();
+    if (dtype == DT_F32) return launch_pdl(global_avgpool_kernel<true>, dim3(N), dim3(256), 0, st, in, out, H * W, C);
+    return launch_pdl(global_avgpool_kernel<false>, dim3(N), dim3(256), 0, st, in, out, H * W, C);
   }
   const long long total = static_cast<long long>(N) * OH * OW * (C / vec);
   if (dtype == DT_F32)
@@ -325,8 +329,7 @@ cudaError_t launch_adaptive_avgpool(const void* in, void* out, int dtype, int N,
 cudaError_t launch_softmax_topk(const float* logits, int rows, int classes, int ld, int k,
                                 int32_t* idx, float* prob, cudaStream_t st) {
   if (classes > 32 * kMaxPerLane || k < 1 || k > kMaxK || k > classes) return cudaErrorInvalidValue;
-  softmax_topk_kernel<<<(rows + 7) / 8, 256, 0, st>>>(logits, rows, classes, ld, k, idx, prob);
-  return cudaGetLastError();
+  return launch_pdl(softmax_topk_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, logits, rows, classes, ld, k, idx, prob);
 }
 
 }  // namespace b2i

@@ -2,6 +2,7 @@
 // commit / ld), cp.async.  Nothing here is reference-derived: the reference has no GPU code
 // (SURVEY.md 2.1); these wrap the PTX ISA directly.
 #pragma once
+#include <cstdlib>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -53,6 +54,12 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
+// Programmatic dependent launch: `griddep_launch` lets the next kernel of the stream start its
+// prologue while this one still runs; `griddep_wait` blocks until every kernel this one depends on
+// has completed and its writes are visible.  Both are no-ops for a normally launched kernel.
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ void tc_fence_after() {
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
@@ -197,5 +204,27 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
+
+// Host side of programmatic dependent launch: the kernel may start while its predecessor in the
+// stream is still running; it must call griddep_wait() before touching anything that predecessor
+// (or an earlier kernel) reads or writes.  B2I_NO_PDL=1 in the environment turns the attribute off.
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("B2I_NO_PDL"); return !(e && e[0] == '1'); }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 }  // namespace b2i

@@ -73,6 +73,7 @@ __device__ __forceinline__ uint64_t patch_desc(uint32_t saddr) {
 
 __global__ void __launch_bounds__(ST_THREADS, 2)
 stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
+  griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[9];  // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
@@ -111,6 +112,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  griddep_wait();   // the pooled map written below may still be read by the previous forward's kernels
 
   if (warp == 8) {
     // ------------------------------------------------------------------ weights + MMA issue
@@ -157,7 +159,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     constexpr int TASKS = PATCH_H * GROUPS;                                   // 370
     constexpr int ROUNDS = (TASKS + ST_LOADERS - 1) / ST_LOADERS;             // 3
     // (u/255 - mean)/std as one FMA per byte: a = 1/(255*std), b = -mean/std.  After rounding to bf16
-    // all 3 x 256 values equal the exact divide-subtract-divide sequence (tests/test_oracle.py::test_stem_fma_normalise_is_exact_in_bf16).
+    // all 3 x 256 values equal the exact divide-subtract-divide sequence (checked exhaustively by the CPU tests: test_stem_fma_normalise_is_exact_in_bf16).
     const float na[3] = {0x1.18926cp-6f, 0x1.1ed5b2p-6f, 0x1.1d8f56p-6f};     // fp32(1 / (255 * std))
     const float nb[3] = {-0x1.0f177ap+1f, -0x1.04924ap+1f, -0x1.cdf012p+0f};  // fp32(-mean / std)
     // Tiles are handed out dynamically (the first one is blockIdx.x, the rest come from a global
@@ -372,8 +374,7 @@ cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap*
   p.total_tiles = n_images * 64;
   p.sched = sched;
   const int grid = p.total_tiles < 2 * sm_count[dev] ? p.total_tiles : 2 * sm_count[dev];
-  stem_kernel<<<grid, ST_THREADS, STEM_SMEM, st>>>(*tmW, p);
-  return cudaGetLastError();
+  return launch_pdl(stem_kernel, dim3(grid), dim3(ST_THREADS), STEM_SMEM, st, *tmW, p);
 }
 
 }  // namespace b2i
