@@ -51,6 +51,7 @@ struct ConvArgs {
   void* out2 = nullptr;
   int ldo2 = 0, relu2 = 0, kb_first2 = 0, num_kb2 = 0;
   int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
+  int resident_b = 0;             // pair kernel: keep all weight k-blocks in shared memory when they fit (one N-tile)
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
   const CUtensorMap* tmO = nullptr;
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)

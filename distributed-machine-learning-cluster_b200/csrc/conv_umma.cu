@@ -44,6 +44,7 @@ struct KP {
   int tiles_n2, kb_first2, num_kb2, ldo2, relu2, Cout2;
   const float* bias2;
   void* out2;
+  int resb;   // pair kernel: this CTA's half of ALL weight k-blocks stays resident in shared memory
 };
 
 // Where one tile's results go.
@@ -98,15 +99,16 @@ __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, cons
   if (nb >= p.Cout) return;
   const size_t off = static_cast<size_t>(m) * p.ldo + nb;
   if (p.residual) {
-    const uint4* rp = reinterpret_cast<const uint4*>(p.residual + off);
+    // Written by an earlier kernel that may have overlapped this one's start: read it from L2, never L1,
+    // one whole 32-byte sector per load (row stride and channel offset are multiples of 32 channels).
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const uint4 rv = __ldcg(rp + q);   // written by an earlier kernel that may have overlapped this one's start: no L1
-      const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+    for (int q = 0; q < 2; ++q) {
+      uint32_t rr[8];
+      ldg256_cg(p.residual + off + q * 16, rr);
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        f[q * 8 + e * 2] += bf16_lo(rr[e]);
-        f[q * 8 + e * 2 + 1] += bf16_hi(rr[e]);
+      for (int e = 0; e < 8; ++e) {
+        f[q * 16 + e * 2] += bf16_lo(rr[e]);
+        f[q * 16 + e * 2 + 1] += bf16_hi(rr[e]);
       }
     }
   }
@@ -114,15 +116,13 @@ __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, cons
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
   }
-  uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+  __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint4 ov;
-    ov.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
-    ov.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
-    ov.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
-    ov.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
-    op[q] = ov;
+  for (int q = 0; q < 2; ++q) {
+    uint32_t ov[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ov[e] = pack_bf16x2(f[q * 16 + 2 * e], f[q * 16 + 2 * e + 1]);
+    stg256(op + q * 16, ov);
   }
 }
 
@@ -575,7 +575,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                       const __grid_constant__ CUtensorMap tmB2, const KP p) {
   griddep_launch();
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
+  __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 5];
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5;
@@ -587,12 +587,19 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int half_n = p.BN >> 1;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t b_tile_bytes = static_cast<uint32_t>(half_n) * 128u;
-  const uint32_t stage_bytes = A_TILE_BYTES + b_tile_bytes;
+  // Resident-weights mode (one N-tile per problem, e.g. ResNet layer2): this CTA's half of every weight
+  // k-block is loaded once, in front of the A ring, and only the A operand streams.  The MMA then reads
+  // 6 KB per K step and TMA writes 4 KB, instead of 8 KB + 8 KB for the one-CTA 128-wide tile.
+  const bool resb = p.resb != 0;
+  const uint32_t resb_bytes = resb ? static_cast<uint32_t>(p.num_kb + (p.tiles_n2 ? p.num_kb2 : 0)) * b_tile_bytes : 0u;
+  const uint32_t stage_bytes = resb ? A_TILE_BYTES : A_TILE_BYTES + b_tile_bytes;
+  const uint32_t ring_base = smem_base + resb_bytes;
   const uint32_t bar0 = smem_u32(bars);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
   auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + b); };
   auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
+  const uint32_t b_full_bar = bar0 + 8u * (2 * MAX_STAGES + 4);
   const int tn_all = p.tiles_n + p.tiles_n2;
   const int total_tiles = p.tiles_m * tn_all;       // tiles_m counts 256-row tiles here
 
@@ -605,6 +612,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       mbar_init(acc_full_bar(b), 1);
       mbar_init(acc_empty_bar(b), 16);  // 8 epilogue warps in each of the two CTAs
     }
+    mbar_init(b_full_bar, 2);
     mbar_fence_init();
   }
   if (warp == 0 && lane == 0) {
@@ -622,6 +630,15 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  if (resb && warp == 0 && lane == 0) {   // weights do not depend on the previous kernel: fetch them before waiting for it
+    if (leader) mbar_expect_tx(b_full_bar, 2u * resb_bytes);
+    else mbar_arrive_cluster(b_full_bar, 0);
+    const int nrow = static_cast<int>(rank) * half_n;
+    for (int kb = 0; kb < p.num_kb; ++kb) tma_load_2d_2sm(smem_base + kb * b_tile_bytes, &tmB, b_full_bar, kb * BK, nrow);
+    if (p.tiles_n2)
+      for (int j = 0; j < p.num_kb2; ++j)
+        tma_load_2d_2sm(smem_base + (p.num_kb + j) * b_tile_bytes, &tmB2, b_full_bar, j * BK, nrow);
+  }
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
   if (warp == 0) {
@@ -651,7 +668,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         for (int j = 0; j < kb_count; ++j) {
           const int kb = kb_begin + j;
           mbar_wait(empty_bar(s), ph ^ 1);
-          const uint32_t a_s = smem_base + s * stage_bytes;
+          const uint32_t a_s = ring_base + s * stage_bytes;
           if (leader) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
           else mbar_arrive_cluster(full_bar(s), 0);
           if (AMODE == A_IM2COL) {
@@ -664,8 +681,10 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           } else {
             tma_load_2d_2sm(a_s, &tmA, full_bar(s), kb * BK, m0);
           }
-          if (second) tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
-          else tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          if (!resb) {
+            if (second) tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
+            else tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          }
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -673,20 +692,23 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   } else if (warp == 1) {
     if (leader) {
       const uint32_t idesc = umma_idesc_bf16(256, p.BN);
+      if (resb) mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
       for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
         const int buf = i & 1;
         mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
-        const int kb_count = (t % tn_all) >= p.tiles_n ? p.num_kb2 : p.num_kb;
+        const bool second = (t % tn_all) >= p.tiles_n;
+        const int kb_count = second ? p.num_kb2 : p.num_kb;
         for (int kb = 0; kb < kb_count; ++kb) {
           mbar_wait(full_bar(s), ph);
           tc_fence_after();
           {
-            const uint32_t a_s = smem_base + s * stage_bytes;
+            const uint32_t a_s = ring_base + s * stage_bytes;
             const uint64_t adesc = umma_smem_desc_sw128(a_s);
-            const uint64_t bdesc = umma_smem_desc_sw128(a_s + A_TILE_BYTES);
+            const uint64_t bdesc = umma_smem_desc_sw128(resb ? smem_base + static_cast<uint32_t>((second ? p.num_kb : 0) + kb) * b_tile_bytes
+                                                             : a_s + A_TILE_BYTES);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
               umma_bf16_2sm(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
@@ -992,6 +1014,7 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->Cout2 = g.Cout;
   p->bias2 = a.bias2;
   p->out2 = a.out2;
+  p->resb = 0;
 }
 
 template <int AMODE>
@@ -1050,7 +1073,13 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   p.tmem_cols = cols;
   const int total = p.tiles_m * (p.tiles_n + p.tiles_n2);
   int grid = std::min(2 * total, sm_count[dev] & ~1);
-  const size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
+  size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
+  const size_t resb_bytes = static_cast<size_t>(p.num_kb + (p.tiles_n2 ? p.num_kb2 : 0)) * (a.BN / 2) * 128;
+  if (a.resident_b && p.tiles_n == 1 && p.tiles_n2 <= 1 && resb_bytes + 4 * A_TILE_BYTES + 1024 <= 226 * 1024) {
+    p.resb = 1;
+    p.stages = std::min<int>(MAX_STAGES, static_cast<int>((226 * 1024 - 1024 - resb_bytes) / A_TILE_BYTES));
+    smem = resb_bytes + static_cast<size_t>(p.stages) * A_TILE_BYTES + 1024;
+  }
   return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
@@ -1135,7 +1164,7 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
   if (a.BN < 32 || a.BN > 256 || (a.BN & 31) || g.Cout_pad % a.BN || g.K % BK || a.stages < 3 ||
       a.stages > MAX_STAGES || g.M <= 0)
     return cudaErrorInvalidValue;
-  if (!a.out_fp32 && ((a.ldo & 7) || (g.Cout & 31))) return cudaErrorInvalidValue;
+  if (!a.out_fp32 && ((a.ldo & 15) || (g.Cout & 31))) return cudaErrorInvalidValue;
   if (a.tmB2 && !((a.amode == A_IM2COL) && (a.persistent || a.pair))) return cudaErrorInvalidValue;
   if (a.patch) {
     if (!conv_patch_applicable(g) || a.out_fp32 || a.ldo != 64 || !tmA || !tmB) return cudaErrorInvalidValue;

@@ -401,6 +401,15 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       if (d.patch) d.BN = 64;
       d.pair = (cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && d.BN >= cfg_.pair_mma &&
                 (d.amode == A_IM2COL || d.amode == A_TILED)) ? 1 : 0;
+      // One N-tile whose weights fit in shared memory next to four A stages (ResNet layer2): CTA pairs with
+      // resident weights, whatever pair_mma says about the tile width.  B2I_NO_RESB=1 turns this off.
+      static const bool resb_on = [] { const char* e = getenv("B2I_NO_RESB"); return !(e && e[0] == '1'); }();
+      if (resb_on && cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && !o.fc && d.amode == A_IM2COL &&
+          d.BN == c.Cout_pad && d.BN >= 64 &&
+          static_cast<size_t>(c.K / 64 + c.Cin_pad / 64) * (d.BN / 2) * 128 + 4 * 16384 + 1024 <= 226 * 1024) {
+        d.pair = 1;
+        d.resident_b = 1;
+      }
 
       const size_t wn = c.w.size();
       if (cfg_.precision == PREC_FP32) {
@@ -526,6 +535,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.tmO = &d.tmO;
         a.tmR = o.res >= 0 ? &d.tmR : nullptr;
         a.pair = d.pair;
+        a.resident_b = d.resident_b;
         if (d.fused_second >= 0) {
           const DevOp& s2 = ops_[d.fused_second];
           const int cpb = d.g.C >> 6;

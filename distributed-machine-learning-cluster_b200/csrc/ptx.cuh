@@ -54,6 +54,18 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
+// 32-byte global accesses (one full sector per thread): the load goes to L2 (.cg), never to L1.
+__device__ __forceinline__ void ldg256_cg(const void* p, uint32_t (&v)[8]) {
+  asm volatile("ld.global.cg.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void stg256(void* p, const uint32_t (&v)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+               "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
 // Programmatic dependent launch: `griddep_launch` lets the next kernel of the stream start its
 // prologue while this one still runs; `griddep_wait` blocks until every kernel this one depends on
 // has completed and its writes are visible.  Both are no-ops for a normally launched kernel.
