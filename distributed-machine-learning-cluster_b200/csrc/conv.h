@@ -55,8 +55,13 @@ struct ConvArgs {
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
   const CUtensorMap* tmO = nullptr;
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)
+  int flat = 0;                   // 3x3/s1/p1, one N tile: flattened-row CTA-pair kernel (tmA = make_tmap_flat, tmB with BN/2 box rows)
 };
 
+// Flattened-row CTA-pair kernel (ResNet layer2 convolutions).
+bool conv_flat_applicable(const ConvGeom& g, int BN);
+int conv_flat_pitch(int W);
+int make_tmap_flat(CUtensorMap* tm, const void* x, int N, int H, int W, int C, const char** err);
 // True when the halo-patch kernel handles this geometry (ResNet layer1 convolutions).
 bool conv_patch_applicable(const ConvGeom& g);
 int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);   // 18 x 10 halo patch

@@ -765,6 +765,203 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 }
 
 // ------------------------------------------------------------------------------------------------
+// 3x3 / stride 1 / pad 1 convolution over FLATTENED PADDED ROWS, CTA pair, resident weights
+// (ResNet layer2: 128 -> 128 channels on 28x28 maps).
+//
+// The im2col kernels above fetch every input pixel nine times from L2, and L2 -> SM bandwidth
+// (about 43 B/clk per SM) is what bounds them.  Here the batch is seen as one long sequence of padded
+// rows: row Y = n*(H+1) + y holds image n's row y as `pitch` pixels (pixel 0 = the left zero pad,
+// pixels 1..W the row, the rest zero), and row n*(H+1) + H is all zero - the bottom pad of image n
+// and the top pad of image n+1 at once.  Flatten those rows and a 3x3 tap (r, s) is a pure shift by
+// (r-1)*pitch + (s-1) positions, so the nine A operands of a tile are nine 128-byte-aligned views
+// of ONE halo patch (the absolute-address swizzle makes any such view valid, see the halo-patch
+// kernel below).  A CTA owns 128 consecutive positions = 128/pitch rows; its patch is those rows
+// plus one above and one below, fetched row by row with tiled TMA loads whose out-of-range rows and
+// columns arrive as zeros.  Each pixel is read from L2 (rows+2)/rows times instead of nine.
+// Positions in pad columns / pad rows are computed and dropped: W*H / (pitch*(H+1)) of the MMA
+// work is useful (84 % for 28x28 with pitch 32).
+// The two CTAs of a pair (cta_group::2, M = 256) each keep their half of ALL weight k-blocks in
+// shared memory (9 * C/64 blocks of BN/2 x 64), so only the patches stream.
+struct FlatP {
+  int H, W, N, slices, BN, pitch, rpt, box_w;   // rpt = rows per 128-position tile
+  int rows_total, total_pairs, nbuf;
+  int ldo, relu, Cout;
+  uint32_t tmem_cols;
+  const float* bias;
+  const __nv_bfloat16* residual;
+  void* out;
+};
+
+__device__ __forceinline__ void tma_load_4d_2sm(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst), "l"(tm), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+constexpr int FLAT_MAXBUF = 4;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
+conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB, const FlatP p) {
+  griddep_launch();
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * FLAT_MAXBUF + 5];   // full[], empty[], acc_full[2], acc_empty[2], b_full
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int half_n = p.BN >> 1;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_tile_bytes = static_cast<uint32_t>(half_n) * 128u;
+  const int num_kb = 9 * p.slices;
+  const uint32_t resb_bytes = static_cast<uint32_t>(num_kb) * b_tile_bytes;
+  const uint32_t row_bytes = static_cast<uint32_t>(p.pitch) * 128u;
+  // one 64-channel slice; the view of tap (2, 2) runs two pixels past the last patch row (they only feed
+  // dropped pad-column outputs), hence the extra KB that keeps those reads inside the buffer
+  const uint32_t patch_bytes = static_cast<uint32_t>(p.rpt + 2) * row_bytes + 1024u;
+  const uint32_t tx_bytes = static_cast<uint32_t>(p.rpt + 2) * static_cast<uint32_t>(p.box_w) * 128u;
+  const uint32_t ring_base = smem_base + resb_bytes;
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (FLAT_MAXBUF + s); };
+  auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * FLAT_MAXBUF + b); };
+  auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * FLAT_MAXBUF + 2 + b); };
+  const uint32_t b_full_bar = bar0 + 8u * (2 * FLAT_MAXBUF + 4);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.nbuf; ++s) {
+      mbar_init(full_bar(s), 2);    // leader's expect_tx arrive + the peer's arrive
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full_bar(b), 1);
+      mbar_init(acc_empty_bar(b), 16);  // 8 epilogue warps in each of the two CTAs
+    }
+    mbar_init(b_full_bar, 2);
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  if (warp == 0 && lane == 0) {   // weights do not depend on the previous kernel: fetch them before waiting for it
+    if (leader) mbar_expect_tx(b_full_bar, 2u * resb_bytes);
+    else mbar_arrive_cluster(b_full_bar, 0);
+    const int nrow = static_cast<int>(rank) * half_n;
+    for (int kb = 0; kb < num_kb; ++kb) tma_load_2d_2sm(smem_base + kb * b_tile_bytes, &tmB, b_full_bar, kb * BK, nrow);
+  }
+  griddep_wait();
+
+  const int hp = p.H + 1;   // padded rows per image
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0, ph = 0;
+      for (int t = cluster_id; t < p.total_pairs; t += num_clusters) {
+        const int y0 = (2 * t + static_cast<int>(rank)) * p.rpt - 1;   // first patch row (one above the tile)
+        for (int sl = 0; sl < p.slices; ++sl) {
+          mbar_wait(empty_bar(s), ph ^ 1);
+          const uint32_t a_s = ring_base + s * patch_bytes;
+          if (leader) mbar_expect_tx(full_bar(s), 2u * tx_bytes);
+          else mbar_arrive_cluster(full_bar(s), 0);
+          for (int j = 0; j < p.rpt + 2; ++j) {
+            const int Y = y0 + j;
+            int n = -1, y = 0;                       // Y = -1: above the first image, all out of range -> zeros
+            if (Y >= 0) { n = Y / hp; y = Y - n * hp; }   // y == H (or n >= N) is out of range too -> the shared zero row
+            tma_load_4d_2sm(a_s + j * row_bytes, &tmX, full_bar(s), sl * 64, -1, y, n);
+          }
+          if (++s == p.nbuf) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader) {
+      const uint32_t idesc = umma_idesc_bf16(256, p.BN);
+      mbar_wait(b_full_bar, 0);
+      int s = 0, ph = 0, i = 0;
+      for (int t = cluster_id; t < p.total_pairs; t += num_clusters, ++i) {
+        const int buf = i & 1;
+        mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
+        for (int sl = 0; sl < p.slices; ++sl) {
+          mbar_wait(full_bar(s), ph);
+          tc_fence_after();
+          const uint32_t a_s = ring_base + s * patch_bytes;
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const uint64_t adesc = umma_smem_desc_sw128(a_s + static_cast<uint32_t>((tap / 3) * p.pitch + (tap % 3)) * 128u);
+            const uint64_t bdesc = umma_smem_desc_sw128(smem_base + static_cast<uint32_t>(tap * p.slices + sl) * b_tile_bytes);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_2sm(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (sl | tap | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_2sm(empty_bar(s));
+          if (++s == p.nbuf) { s = 0; ph ^= 1; }
+        }
+        umma_commit_2sm(acc_full_bar(buf));
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int n_chunks = p.BN >> 5;
+    const int last_c = ((n_chunks - 1 - half) & ~1) + half;
+    Epi epi;
+    epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout;
+    int i = 0;
+    for (int t = cluster_id; t < p.total_pairs; t += num_clusters, ++i) {
+      const int buf = i & 1;
+      const int pos = q * 32 + lane;                                  // position inside this CTA's tile
+      const int Y = (2 * t + static_cast<int>(rank)) * p.rpt + pos / p.pitch;
+      const int xo = pos % p.pitch;
+      const int n = Y / hp, y = Y - n * hp;
+      const bool row_ok = xo < p.W && y < p.H && n < p.N;
+      const int m = (n * p.H + y) * p.W + xo;
+      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
+      for (int c = half; c < n_chunks; c += 2) {
+        uint32_t v[32];
+        tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+        tmem_ld_wait();
+        if (c == last_c) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (leader) mbar_arrive(acc_empty_bar(buf));
+            else mbar_arrive_cluster(acc_empty_bar(buf), 0);
+          }
+        }
+        if (row_ok) epilogue_chunk(epi, m, c * 32, v);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // 3x3 / stride 1 / pad 1 convolution with 64 input and 64 output channels (ResNet layer1), reading
 // the nine filter taps as SHIFTED VIEWS of one halo patch instead of nine im2col loads.
 //
@@ -1114,6 +1311,42 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   return launch_pdl(conv3x3_c64_patch_kernel, dim3(grid), dim3(PATCH_THREADS), smem, st, *tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
 }
 
+cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmB, cudaStream_t st) {
+  static bool attr_set[16] = {};
+  static int sm_count[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 16) return cudaErrorInvalidDevice;
+  if (!attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_flat_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  const ConvGeom& g = a.g;
+  FlatP p;
+  p.H = g.H; p.W = g.W; p.N = g.N; p.slices = g.C / 64; p.BN = a.BN;
+  p.pitch = conv_flat_pitch(g.W);
+  p.rpt = 128 / p.pitch;
+  p.box_w = p.pitch;
+  p.rows_total = g.N * (g.H + 1);
+  p.total_pairs = (p.rows_total + 2 * p.rpt - 1) / (2 * p.rpt);
+  const size_t resb = static_cast<size_t>(9) * p.slices * (a.BN / 2) * 128;
+  const size_t patch = static_cast<size_t>(p.rpt + 2) * p.pitch * 128 + 1024;
+  p.nbuf = static_cast<int>(std::min<size_t>(FLAT_MAXBUF, (226 * 1024 - 1024 - resb) / patch));
+  p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout;
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.bias = a.bias;
+  p.residual = static_cast<const __nv_bfloat16*>(a.residual);
+  p.out = a.out;
+  const int grid = std::min(2 * p.total_pairs, sm_count[dev] & ~1);
+  const size_t smem = resb + p.nbuf * patch + 1024;
+  return launch_pdl(conv3x3_flat_pair_kernel, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmX, *tmB, p);
+}
+
 template <int AMODE, bool B_TMA>
 cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
                      cudaStream_t st) {
@@ -1166,6 +1399,10 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
     return cudaErrorInvalidValue;
   if (!a.out_fp32 && ((a.ldo & 15) || (g.Cout & 31))) return cudaErrorInvalidValue;
   if (a.tmB2 && !((a.amode == A_IM2COL) && (a.persistent || a.pair))) return cudaErrorInvalidValue;
+  if (a.flat) {
+    if (!conv_flat_applicable(g, a.BN) || a.out_fp32 || a.ldo != g.Cout || !tmA || !tmB) return cudaErrorInvalidValue;
+    return launch_flat(a, tmA, tmB, st);
+  }
   if (a.patch) {
     if (!conv_patch_applicable(g) || a.out_fp32 || a.ldo != 64 || !tmA || !tmB) return cudaErrorInvalidValue;
     return launch_patch(a, tmA, tmB, st);
@@ -1233,6 +1470,35 @@ int make_tmap_rows(CUtensorMap* tm, const void* a, int rows, int K, int box_rows
 int make_tmap_weights(CUtensorMap* tm, const void* w, int Cout_pad, int K, int BN,
                       const char** err) {
   return make_tmap_rows(tm, w, Cout_pad, K, BN, err);
+}
+
+// Padded-row pitch of the flattened-row kernel: the smallest of 16 / 32 / 64 pixels holding W + 2.
+int conv_flat_pitch(int W) { return W + 2 <= 16 ? 16 : (W + 2 <= 32 ? 32 : 64); }
+
+// True when the flattened-row CTA-pair kernel handles this geometry: 3x3 / s1 / p1, channels a multiple of
+// 64, one N tile, and this CTA's half of the weights plus two halo patches fitting in shared memory.
+bool conv_flat_applicable(const ConvGeom& g, int BN) {
+  if (g.R != 3 || g.S != 3 || g.stride != 1 || g.pad != 1 || g.OH != g.H || g.OW != g.W) return false;
+  if (g.C % 64 || g.K != 9 * g.C || BN != g.Cout_pad || BN != g.Cout || BN < 64 || BN > 256 || (BN & 31) || g.W + 2 > 64) return false;
+  const int pitch = conv_flat_pitch(g.W);
+  const size_t resb = static_cast<size_t>(9) * (g.C / 64) * (BN / 2) * 128;
+  const size_t patch = static_cast<size_t>(128 / pitch + 2) * pitch * 128 + 1024;
+  return resb + 2 * patch + 1024 <= 226 * 1024;
+}
+
+// Tiled 4-D map over NHWC [N][H][W][C] whose box is one 64-channel slice of `box_w` pixels of one row.
+int make_tmap_flat(CUtensorMap* tm, const void* x, int N, int H, int W, int C, const char** err) {
+  static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
+  if (!fn) { *err = "cuTensorMapEncodeTiled entry point not found"; return -1; }
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(N)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2, static_cast<cuuint64_t>(H) * W * C * 2};
+  cuuint32_t box[4] = {64, static_cast<cuuint32_t>(conv_flat_pitch(W)), 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { *err = "cuTensorMapEncodeTiled (flattened rows) failed"; return static_cast<int>(r); }
+  return 0;
 }
 
 bool conv_patch_applicable(const ConvGeom& g) {

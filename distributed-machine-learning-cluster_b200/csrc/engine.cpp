@@ -410,6 +410,14 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         d.pair = 1;
         d.resident_b = 1;
       }
+      // 3x3 / s1 convs of that kind go one step further: flattened padded rows, each pixel fetched from L2
+      // 1.5 times instead of nine.  B2I_NO_FLAT=1 turns this off.
+      static const bool flat_on = [] { const char* e = getenv("B2I_NO_FLAT"); return !(e && e[0] == '1'); }();
+      if (flat_on && cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && !o.fc && d.amode == A_IM2COL &&
+          conv_flat_applicable(g, d.BN)) {
+        d.flat = 1;
+        d.pair = 1;
+      }
 
       const size_t wn = c.w.size();
       if (cfg_.precision == PREC_FP32) {
@@ -441,6 +449,9 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           if (make_tmap_patch(&d.tmA, xin, mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
           if (make_tmap_tile(&d.tmO, bufs_[tensor_buf_[o.out]], mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
           if (o.res >= 0 && make_tmap_tile(&d.tmR, bufs_[tensor_buf_[o.res]], mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
+          d.has_tmA = true;
+        } else if (d.flat) {
+          if (make_tmap_flat(&d.tmA, xin, mb_, g.H, g.W, g.C, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_IM2COL) {
           if (make_tmap_im2col(&d.tmA, xin, g, mb_, &terr)) { *err = c.name + ": " + terr; return false; }
@@ -536,6 +547,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.tmR = o.res >= 0 ? &d.tmR : nullptr;
         a.pair = d.pair;
         a.resident_b = d.resident_b;
+        a.flat = d.flat;
         if (d.fused_second >= 0) {
           const DevOp& s2 = ops_[d.fused_second];
           const int cpb = d.g.C >> 6;
