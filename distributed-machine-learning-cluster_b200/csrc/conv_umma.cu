@@ -68,7 +68,9 @@ __device__ __forceinline__ Epi epi_of(const KP& p, bool second) {
 
 
 // One output row x 32 consecutive channels: acc + bias (+ residual) -> ReLU -> store.
-__device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, const uint32_t (&v)[32]) {
+// `rpre`: the residual's 32 channels already in registers (see prefetch_residual), or null to load them here.
+__device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, const uint32_t (&v)[32],
+                                               const uint32_t (*rpre)[16] = nullptr) {
   float f[32];
   const float4* b4 = reinterpret_cast<const float4*>(p.bias + nb);   // bias is padded to Cout_pad: always in range
 #pragma unroll
@@ -101,14 +103,22 @@ __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, cons
   if (p.residual) {
     // Written by an earlier kernel that may have overlapped this one's start: read it from L2, never L1,
     // one whole 32-byte sector per load (row stride and channel offset are multiples of 32 channels).
+    if (rpre) {
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      uint32_t rr[8];
-      ldg256_cg(p.residual + off + q * 16, rr);
+      for (int e = 0; e < 16; ++e) {
+        f[e * 2] += bf16_lo((*rpre)[e]);
+        f[e * 2 + 1] += bf16_hi((*rpre)[e]);
+      }
+    } else {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        f[q * 16 + e * 2] += bf16_lo(rr[e]);
-        f[q * 16 + e * 2 + 1] += bf16_hi(rr[e]);
+      for (int q = 0; q < 2; ++q) {
+        uint32_t rr[8];
+        ldg256_cg(p.residual + off + q * 16, rr);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          f[q * 16 + e * 2] += bf16_lo(rr[e]);
+          f[q * 16 + e * 2 + 1] += bf16_hi(rr[e]);
+        }
       }
     }
   }
@@ -124,6 +134,17 @@ __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, cons
     for (int e = 0; e < 8; ++e) ov[e] = pack_bf16x2(f[q * 16 + 2 * e], f[q * 16 + 2 * e + 1]);
     stg256(op + q * 16, ov);
   }
+}
+
+// Issue the residual loads of one output row x 32 channels early (before the accumulator is ready), so
+// their L2 latency overlaps the wait instead of following it.
+__device__ __forceinline__ void prefetch_residual(const Epi& p, int m, int nb, uint32_t (&r)[16]) {
+  const __nv_bfloat16* src = p.residual + static_cast<size_t>(m) * p.ldo + nb;
+  uint32_t lo[8], hi[8];
+  ldg256_cg(src, lo);
+  ldg256_cg(src + 16, hi);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { r[e] = lo[e]; r[8 + e] = hi[e]; }
 }
 
 template <int AMODE, bool B_TMA>
@@ -733,12 +754,21 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int m0 = tm * 256 + static_cast<int>(rank) * BM;
       const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
       const Epi epi = epi_of(p, second);
-      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
-      tc_fence_after();
       const int m = m0 + q * 32 + lane;
       const bool row_ok = m < p.M;
+      const bool pre = row_ok && epi.residual != nullptr && !epi.out_fp32;
+      uint32_t rr[4][16];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (pre && half + 2 * j < n_chunks && n0 + (half + 2 * j) * 32 < epi.Cout)
+          prefetch_residual(epi, m, n0 + (half + 2 * j) * 32, rr[j]);
+      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
+      tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
-      for (int c = half; c < n_chunks; c += 2) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = half + 2 * j;
+        if (c >= n_chunks) break;
         uint32_t v[32];
         tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
         tmem_ld_wait();
@@ -750,7 +780,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             else mbar_arrive_cluster(acc_empty_bar(buf), 0);
           }
         }
-        if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v);
+        if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
       }
     }
   }
@@ -932,10 +962,18 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       const int n = Y / hp, y = Y - n * hp;
       const bool row_ok = xo < p.W && y < p.H && n < p.N;
       const int m = (n * p.H + y) * p.W + xo;
+      const bool pre = row_ok && epi.residual != nullptr;
+      uint32_t rr[4][16];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (pre && half + 2 * j < n_chunks) prefetch_residual(epi, m, (half + 2 * j) * 32, rr[j]);
       mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
-      for (int c = half; c < n_chunks; c += 2) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = half + 2 * j;
+        if (c >= n_chunks) break;
         uint32_t v[32];
         tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
         tmem_ld_wait();
@@ -947,7 +985,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
             else mbar_arrive_cluster(acc_empty_bar(buf), 0);
           }
         }
-        if (row_ok) epilogue_chunk(epi, m, c * 32, v);
+        if (row_ok) epilogue_chunk(epi, m, c * 32, v, pre ? &rr[j] : nullptr);
       }
     }
   }
