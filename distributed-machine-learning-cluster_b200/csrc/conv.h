@@ -67,6 +67,7 @@ bool conv_patch_applicable(const ConvGeom& g);
 int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);   // 18 x 10 halo patch
 int make_tmap_tile(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);    // 16 x 8 tile (residual in / result out)
 int make_tmap_nhwc64(CUtensorMap* tm, const void* x, int N, int H, int W, int box_w, int box_h, const char** err);
+int make_tmap_pixrow(CUtensorMap* tm, const void* x, int N, int H, int W, int C, int box_w, int stride, const char** err);
 
 // bf16 tcgen05 path.  tmA / tmB may be null when the corresponding operand is gathered.
 cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,

@@ -1539,6 +1539,22 @@ int make_tmap_flat(CUtensorMap* tm, const void* x, int N, int H, int W, int C, c
   return 0;
 }
 
+// Tiled 4-D map over NHWC [N][H][W][C]: one 64-channel slice of `box_w` pixels of one row, taking every
+// `stride`-th pixel (the input pixels of `box_w` consecutive output pixels of a stride-`stride` conv).
+int make_tmap_pixrow(CUtensorMap* tm, const void* x, int N, int H, int W, int C, int box_w, int stride, const char** err) {
+  static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
+  if (!fn) { *err = "cuTensorMapEncodeTiled entry point not found"; return -1; }
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(N)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2, static_cast<cuuint64_t>(H) * W * C * 2};
+  cuuint32_t box[4] = {64, static_cast<cuuint32_t>(box_w * stride), 1, 1};
+  cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(stride), 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { *err = "cuTensorMapEncodeTiled (pixel row) failed"; return static_cast<int>(r); }
+  return 0;
+}
+
 bool conv_patch_applicable(const ConvGeom& g) {
   return g.C == 64 && g.Cout == 64 && g.Cout_pad == 64 && g.R == 3 && g.S == 3 && g.stride == 1 &&
          g.pad == 1 && g.K == 576 && g.OH == g.H && g.OW == g.W;
