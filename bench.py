@@ -28,6 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BATCH = 256
+NCU_DRAM_BYTES_PER_CONV_LAUNCH = 97886862   # see roofline["traffic"] below
 K_TOP = 5
 MODEL = "resnet18"
 WORKLOAD = "ResNet-18 (resnet18.ot layout, seeded synthetic weights) synthetic 224x224 u8, batch 256 per GPU, bf16"
@@ -310,9 +311,13 @@ def main():
     all_ms = sum(ms for _, ms in prof)
     achieved = flops_img * mb / (conv_ms / 1000.0) / 1e12 if conv_ms > 0 else 0.0
     roofline = {
-        "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM; all %d conv/FC launches of a step)" % conv_launches,
+        "kernel": "tcgen05 implicit-GEMM family (stem_kernel, conv3x3_c64_patch_kernel, conv3x3_flat_pair_kernel, "
+                  "conv_umma_pair_kernel): all %d conv/FC launches of a step" % conv_launches,
         "bound": "tensor", "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
-        "traffic": None, "peak_source": pk["source"],
+        # dram__bytes_read.sum + dram__bytes_write.sum averaged over the 18 conv/FC launches of one batch-256 step
+        # (ncu, profiles/r02_ncu_dram_tensor_per_launch.csv); only meaningful for the default workload
+        "traffic": NCU_DRAM_BYTES_PER_CONV_LAUNCH if (mb == BATCH and conv_launches == 18) else None,
+        "peak_source": pk["source"],
         "flops_per_launch_avg": flops_img * mb / max(1, conv_launches),
         "ms_per_launch_avg": conv_ms / max(1, conv_launches),
         "share_of_step": conv_ms / all_ms if all_ms else None,

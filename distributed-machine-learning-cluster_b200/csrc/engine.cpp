@@ -609,9 +609,15 @@ bool DeviceModel::profile(const uint8_t* d_u8, int n, int k, int32_t* d_idx, flo
   if (ok) {
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) { *err = std::string("profile sync: ") + cudaGetErrorString(e); }
-    ms->assign(evs.size() - 1, 0.f);
-    for (size_t i = 0; i + 1 < evs.size(); ++i) cudaEventElapsedTime(&(*ms)[i], evs[i], evs[i + 1]);
-    *labels = op_names_;
+    ms->clear();
+    labels->clear();
+    for (size_t i = 0; i + 1 < evs.size(); ++i) {
+      if (i < ops_.size() && ops_[i].skip) continue;   // computed inside another op's kernel: no launch of its own
+      float t = 0.f;
+      cudaEventElapsedTime(&t, evs[i], evs[i + 1]);
+      ms->push_back(t);
+      labels->push_back(op_names_[i]);
+    }
   }
   for (auto& e : evs) cudaEventDestroy(e);
   return ok;
