@@ -480,7 +480,14 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   a.amode = cs.smallc ? A_SMALLC : (conv_mode >= 1 ? A_IM2COL : A_GATHER);
   a.persistent = conv_mode == 2 ? 0 : 1;
   a.b_tma = (a.amode == A_IM2COL) ? 1 : weights_tma;
-  if (conv_mode == 5) a.pair = 1;
+  if (conv_mode == 5 || conv_mode == 7) a.pair = 1;
+  if (conv_mode == 7) a.resident_b = 1;   // the launcher falls back to streamed weights when they do not fit
+  if (conv_mode == 6) {
+    a.BN = cs.Cout_pad <= 256 ? cs.Cout_pad : a.BN;
+    if (!bf16 || !conv_flat_applicable(g, a.BN)) return fail(B2I_EINVAL, "conv_mode 6 (flattened rows) needs bf16, 3x3 s1 p1, C % 64 == 0, one N tile of 64..256 channels, W <= 62");
+    a.flat = 1;
+    a.pair = 1;
+  }
   if (conv_mode == 3) {
     if (!bf16 || !conv_patch_applicable(g)) return fail(B2I_EINVAL, "conv_mode 3 (halo patch) needs bf16, 3x3 s1 p1, 64 -> 64 channels");
     a.patch = 1;
@@ -498,10 +505,12 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
       if (residual && make_tmap_tile(&tmR, dr.p, N, H, W, &terr)) return fail(B2I_ECUDA, terr);
       a.tmO = &tmO;
       a.tmR = residual ? &tmR : nullptr;
+    } else if (a.flat) {
+      if (make_tmap_flat(&tmA, dx.p, N, H, W, g.C, &terr)) return fail(B2I_ECUDA, terr);
     } else if (a.amode == A_IM2COL && make_tmap_im2col(&tmA, dx.p, g, N, &terr)) {
       return fail(B2I_ECUDA, terr);
     }
-    CAPI_CUDA(launch_conv_umma(a, (a.patch || a.amode == A_IM2COL) ? &tmA : nullptr, a.b_tma ? &tmB : nullptr, nullptr));
+    CAPI_CUDA(launch_conv_umma(a, (a.patch || a.flat || a.amode == A_IM2COL) ? &tmA : nullptr, a.b_tma ? &tmB : nullptr, nullptr));
   }
   CAPI_CUDA(cudaDeviceSynchronize());
   CAPI_CUDA(download(dout.p, out, nout, out32 ? B2I_PREC_FP32 : precision));

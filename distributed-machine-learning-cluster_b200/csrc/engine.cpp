@@ -388,6 +388,15 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       g.N = mb_; g.Cout = c.Cout; g.Cout_pad = c.Cout_pad; g.K = c.K; g.M = 0;
       // tile-N: largest multiple of 32 <= bn_max dividing Cout_pad
       int bn = std::min(cfg_.bn_max, 256) / 32 * 32;
+      // FC layers have few rows (one micro-batch): 256-wide tiles would occupy a handful of SMs and run their
+      // whole K loop in sequence; 64-wide tiles spread the same work over 4x the CTAs (ResNet fc 19 -> 12 us,
+      // AlexNet classifier 132 -> 89 us at batch 256).  B2I_FC_BN overrides.
+      static const int fc_bn = [] { const char* e = getenv("B2I_FC_BN"); return e ? atoi(e) : 0; }();
+      if (o.fc) {
+        const int tiles256 = ((mb_ + 127) / 128) * ((c.Cout_pad + 255) / 256);
+        if (fc_bn >= 32) bn = std::min(bn, fc_bn / 32 * 32);
+        else if (tiles256 < 148) bn = std::min(bn, 64);
+      }
       while (bn > 32 && c.Cout_pad % bn) bn -= 32;
       d.BN = bn;
       d.stages = conv_umma_pick_stages(bn);

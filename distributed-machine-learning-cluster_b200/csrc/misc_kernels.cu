@@ -177,18 +177,32 @@ __global__ void __launch_bounds__(256) global_avgpool_kernel(const void* __restr
   griddep_launch();
   griddep_wait();   // launched under the tail of the last conv; its output is read below, past L1 (__ldcg)
   if (g < groups) {
-    for (int px = g; px < HW; px += groups) {
-      const size_t off = (static_cast<size_t>(n) * HW + px) * C + c * vec;
-      if (F32) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(static_cast<const float*>(in) + off));
-        a[0] += v.x; a[1] += v.y; a[2] += v.z; a[3] += v.w;
-      } else {
-        const uint4 v = __ldcg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(in) + off));
-        const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+    // four loads in flight per thread (the sum keeps its pixel order, so the result does not change)
+    for (int px0 = g; px0 < HW; px0 += 4 * groups) {
+      uint4 v[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          a[2 * e] += __uint_as_float(u[e] << 16);
-          a[2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+      for (int i = 0; i < 4; ++i) {
+        const int px = px0 + i * groups;
+        v[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (px < HW) {
+          const size_t off = (static_cast<size_t>(n) * HW + px) * C + c * vec;
+          if (F32) v[i] = __ldcg(reinterpret_cast<const uint4*>(static_cast<const float*>(in) + off));
+          else v[i] = __ldcg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(in) + off));
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (px0 + i * groups >= HW) break;
+        const uint32_t u[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        if (F32) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) a[e] += __uint_as_float(u[e]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            a[2 * e] += __uint_as_float(u[e] << 16);
+            a[2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+          }
         }
       }
     }

@@ -135,6 +135,27 @@ def test_conv3x3_c64_halo_patch_kernel(ctx, variant=3):
     conv_case(ctx, 5, 7, 8, 64, 64, 3, 1, 1, precision=BF16, conv_mode=variant, bias=True, relu=True, seed=202)
 
 
+def test_conv3x3_flattened_rows_kernel(ctx):
+    """3x3 / s1 / p1 through the flattened padded-row kernel (conv_mode 6): nine shifted views of one
+    row patch, CTA pair, resident weights.  Row pitch 32 (W = 28), 16 (W <= 14) and 64 (W <= 62); tiles
+    that straddle images, a last tile that runs past the batch, odd sizes, residual / ReLU / plain bias."""
+    conv_case(ctx, 3, 28, 28, 128, 128, 3, 1, 1, precision=BF16, conv_mode=6, bn=True, residual=True, relu=True, seed=300)
+    conv_case(ctx, 37, 28, 28, 128, 128, 3, 1, 1, precision=BF16, conv_mode=6, bn=True, relu=True, seed=301)   # several tiles per CTA pair
+    conv_case(ctx, 5, 14, 14, 128, 128, 3, 1, 1, precision=BF16, conv_mode=6, bn=True, residual=True, seed=302)   # pitch 16
+    conv_case(ctx, 2, 9, 13, 64, 64, 3, 1, 1, precision=BF16, conv_mode=6, bias=True, relu=True, seed=303)       # H != W, one slice
+    conv_case(ctx, 1, 56, 56, 64, 64, 3, 1, 1, precision=BF16, conv_mode=6, bn=True, residual=True, relu=True, seed=304)   # pitch 64
+    conv_case(ctx, 2, 30, 30, 64, 128, 3, 1, 1, precision=BF16, conv_mode=6, bias=True, seed=305)                # W + 2 == pitch
+
+
+def test_conv_pair_resident_weights(ctx):
+    """CTA-pair im2col kernel keeping all weight k-blocks resident (conv_mode 7): the stride-2 first conv of
+    ResNet layer2, a 1x1, and a layer whose weights do not fit (falls back to streaming them)."""
+    conv_case(ctx, 3, 56, 56, 64, 128, 3, 2, 1, precision=BF16, conv_mode=7, bn=True, relu=True, seed=310)
+    conv_case(ctx, 9, 28, 28, 128, 128, 3, 1, 1, precision=BF16, conv_mode=7, bn=True, residual=True, relu=True, seed=311)
+    conv_case(ctx, 5, 56, 56, 64, 128, 1, 2, 0, precision=BF16, conv_mode=7, bn=True, seed=312)
+    conv_case(ctx, 3, 14, 14, 256, 256, 3, 1, 1, precision=BF16, conv_mode=7, tile_n=256, bn=True, residual=True, relu=True, seed=313)
+
+
 @pytest.mark.parametrize("btma", [0, 1], ids=["smallc_cpasyncB", "smallc_tmaB"])
 def test_conv_first_layers_rgb(ctx, btma):
     """C = 3 layers: ResNet conv1 (7x7 s2 p3) and AlexNet features.0 (11x11 s4 p2)."""
