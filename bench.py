@@ -161,6 +161,19 @@ def run_reference(args, rank, world):
     }))
 
 
+def bind_to_gpu_numa_node(gpu_index):
+    """Pin this process to the CPUs NVML reports as local to its GPU before any pinned host memory is
+    touched: with eight ranks streaming 38.5 MB per step each, buffers that land on the other socket
+    make the end-to-end number a measurement of the inter-socket link.  Returns the CPU count or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(gpu_index))
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -192,6 +205,7 @@ def main():
     from oracle import synth  # synthetic weights/images only; the oracle is never on the timed path
 
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ot = synth.ensure_ot(MODEL, os.path.join(ROOT, "tests", "_cache", "resnet18.ot")) if rank == 0 else None
@@ -334,7 +348,8 @@ def main():
         "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "micro_batch": mb, "top_k": K_TOP,
                    "l2": "inputs rotate over %d distinct batches (%d MB) > 126 MB L2; activations (> 1 GB per step) never fit" %
                          (ROTATE, ROTATE * BATCH * b2.IMAGE_BYTES // 2 ** 20),
-                   "parallelism": "independent batch shards, one process per GPU, no collective"},
+                   "parallelism": "independent batch shards, one process per GPU, no collective",
+                   "host_cpus_bound_to_gpu_numa_node": numa},
         "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": BATCH * b2.IMAGE_BYTES,
                 "d2h_bytes_per_step": BATCH * K_TOP * 8,
                 "api": "b2i_submit_u8 / b2i_wait, two requests in flight, pinned host buffers",
