@@ -1091,13 +1091,15 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  if (warp == 0 && lane == 0) {   // the weights do not depend on the previous kernel: fetch them before waiting for it
+    mbar_expect_tx(w_full, PT_WBYTES);
+    for (int tap = 0; tap < 9; ++tap) tma_load_2d(w_smem + tap * 8192u, &tmW, w_full, tap * 64, 0);
+  }
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_expect_tx(w_full, PT_WBYTES);
-      for (int tap = 0; tap < 9; ++tap) tma_load_2d(w_smem + tap * 8192u, &tmW, w_full, tap * 64, 0);
       int i = 0;
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
         const int pb = i % PT_BUFS;
