@@ -18,26 +18,27 @@ __device__ __forceinline__ void tma4d(uint32_t dst, const CUtensorMap* tm, uint3
 
 // mode 0/1: im2col (tm), 2/3: pixel rows (tm, rows_per_tile loads of row_px pixels), 4: 2-D weights
 __global__ void __launch_bounds__(32, 1) rate_kernel(const __grid_constant__ CUtensorMap tm, int mode, int iters, int H, int W, int OH, int OW,
-                                                      int stride, int cslices, int nimg, int rows_per_tile, long long* cycles) {
+                                                      int stride, int cslices, int nimg, int rows_per_tile, int px, long long* cycles) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[8];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int lane = threadIdx.x;
   if (lane == 0) { for (int s = 0; s < 8; ++s) mbar_init(smem_u32(&bars[s]), 1); mbar_fence_init(); }
   __syncwarp();
-  const uint32_t stage_bytes = 20 * 1024;
+  const uint32_t stage_bytes = px > 128 ? px * 128 + 4096 : 20 * 1024;
+  const int nst = px > 128 ? (px > 256 ? 2 : 4) : 8;
   long long t0 = clock64();
   uint32_t bytes_per = 0;
   for (int it = 0; it < iters; ++it) {
-    const int s = it & 7;
-    if (it >= 8) mbar_wait(smem_u32(&bars[s]), ((it >> 3) - 1) & 1);
+    const int s = it % nst;
+    if (it >= nst) mbar_wait(smem_u32(&bars[s]), ((it / nst) - 1) & 1);
     const uint32_t dst = base + s * stage_bytes + 2048;
     const uint32_t bar = smem_u32(&bars[s]);
     const int tile = (blockIdx.x * 131 + it / 9) % ((nimg * OH * OW) / 128);
     const int tap = it % 9, r = tap / 3, sx = tap % 3, cb = (it / 9) % cslices;
     const int m0 = tile * 128;
     if (mode <= 1) {
-      bytes_per = 128 * 128;
+      bytes_per = px * 128;
       if (lane == 0) {
         mbar_expect_tx(bar, bytes_per);
         const int n = m0 / (OH * OW), rem = m0 % (OH * OW), oh = rem / OW, ow = rem % OW;
@@ -57,9 +58,9 @@ __global__ void __launch_bounds__(32, 1) rate_kernel(const __grid_constant__ CUt
     }
     __syncwarp();
   }
-  for (int s = 0; s < 8; ++s) {                 // the last fill of stage s was iteration it_last = largest it < iters with it % 8 == s
-    const int it_last = iters - 1 - ((iters - 1 - s) & 7);
-    mbar_wait(smem_u32(&bars[s]), (it_last >> 3) & 1);
+  for (int s = 0; s < nst; ++s) {               // the last fill of stage s was the largest it < iters with it % nst == s
+    const int it_last = iters - 1 - ((iters - 1 - s) % nst + nst) % nst;
+    mbar_wait(smem_u32(&bars[s]), (it_last / nst) & 1);
   }
   long long t1 = clock64();
   if (blockIdx.x == 0 && lane == 0) { cycles[0] = t1 - t0; cycles[1] = (long long)bytes_per * iters; }
@@ -69,7 +70,11 @@ int main() {
   const int nimg = 64;
   long long* d_c; cudaMalloc(&d_c, 16);
   cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  struct Cfg { const char* name; int mode, H, W, C, stride; } cfgs[] = {
+  struct Cfg { const char* name; int mode, H, W, C, stride, px; } cfgs[] = {
+      {"im2col  s1  14x14x256, 256 pixels per load", 0, 14, 14, 256, 1, 256},
+      {"im2col  s1  14x14x256, 512 pixels per load", 0, 14, 14, 256, 1, 512},
+      {"im2col  s1  14x14x256, 64 pixels per load ", 0, 14, 14, 256, 1, 64},
+      {"im2col  s1  14x14x256, 32 pixels per load ", 0, 14, 14, 256, 1, 32},
       {"im2col  s1  14x14x256 (layer3 convs)      ", 0, 14, 14, 256, 1},
       {"im2col  s2  28x28x128 -> 14x14 (layer3.0) ", 1, 28, 28, 128, 2},
       {"im2col  s2  56x56x64  -> 28x28 (layer2.0) ", 1, 56, 56, 64, 2},
@@ -95,12 +100,12 @@ int main() {
       if (c.mode <= 1) {
         ConvGeom g{}; g.N = nimg; g.H = c.H; g.W = c.W; g.C = c.C; g.OH = OH; g.OW = OW; g.R = g.S = g.Sp = 3; g.stride = c.stride; g.pad = 1;
         g.Cout = g.Cout_pad = 256; g.K = 9 * c.C; g.M = nimg * OH * OW;
-        if (make_tmap_im2col(&tm, d_x, g, nimg, &err)) { printf("tmap %s\n", err); return 1; }
+        if (make_tmap_im2col_px(&tm, d_x, g, nimg, c.px ? c.px : 128, &err)) { printf("tmap %s\n", err); return 1; }
       } else if (make_tmap_pixrow(&tm, d_x, nimg, c.H, c.W, c.C, OW, c.stride, &err)) { printf("tmap %s\n", err); return 1; }
     }
     const int iters = 4000;
     for (int rep = 0; rep < 2; ++rep) {
-      rate_kernel<<<148, 32, 200 * 1024>>>(tm, c.mode, iters, c.H, c.W, OH, OW, c.stride, c.C / 64, nimg, rows, d_c);
+      rate_kernel<<<148, 32, 200 * 1024>>>(tm, c.mode, iters, c.H, c.W, OH, OW, c.stride, c.C / 64, nimg, rows, c.px ? c.px : 128, d_c);
       cudaError_t e = cudaDeviceSynchronize();
       long long h[2]; cudaMemcpy(h, d_c, 16, cudaMemcpyDeviceToHost);
       if (rep) printf("%s: %6.1f B/clk/SM (%lld cycles per load of %lld B) [%s]\n", c.name, (double)h[1] / h[0], h[0] / iters, h[1] / iters, cudaGetErrorString(e));
