@@ -52,6 +52,7 @@ struct ConvArgs {
   int ldo2 = 0, relu2 = 0, kb_first2 = 0, num_kb2 = 0;
   int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
   int resident_b = 0;             // pair kernel: keep all weight k-blocks in shared memory when they fit (one N-tile)
+  int msub = 1;                   // pair im2col kernel: 2 = two 128-row sub-tiles per CTA; tmA must then be a 256-pixel im2col map
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
   const CUtensorMap* tmO = nullptr;
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)
@@ -90,6 +91,7 @@ cudaError_t launch_conv_fp32(const ConvArgs& a, cudaStream_t st);
 // Return 0 on success, else a CUresult / negative code; message in *err.
 int make_tmap_weights(CUtensorMap* tm, const void* w, int Cout_pad, int K, int BN, const char** err);
 int make_tmap_im2col(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax, const char** err);
+int make_tmap_im2col_px(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax, int pixels, const char** err);   // `pixels` rows per request
 int make_tmap_rows(CUtensorMap* tm, const void* a, int rows, int K, int box_rows, const char** err);
 
 }  // namespace b2i

@@ -45,6 +45,7 @@ struct KP {
   const float* bias2;
   void* out2;
   int resb;   // pair kernel: this CTA's half of ALL weight k-blocks stays resident in shared memory
+  int msub;   // pair kernel: 128-row sub-tiles per CTA (1 or 2)
 };
 
 // Where one tile's results go.
@@ -613,7 +614,15 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   // 6 KB per K step and TMA writes 4 KB, instead of 8 KB + 8 KB for the one-CTA 128-wide tile.
   const bool resb = p.resb != 0;
   const uint32_t resb_bytes = resb ? static_cast<uint32_t>(p.num_kb + (p.tiles_n2 ? p.num_kb2 : 0)) * b_tile_bytes : 0u;
-  const uint32_t stage_bytes = resb ? A_TILE_BYTES : A_TILE_BYTES + b_tile_bytes;
+  // msub = 2: each CTA owns TWO 128-row sub-tiles (a 512-row tile per pair).  An im2col-mode TMA request costs
+  // about 700 cycles whatever its size (tools/microbench/tma_rate.cu), more than the MMAs of one 128-row k-block
+  // (512 / 256 cycles for N = 256 / 128): one 256-pixel request per k-block feeds twice the MMAs.
+  const int msub = p.msub;
+  const uint32_t a_bytes = static_cast<uint32_t>(msub) * A_TILE_BYTES;
+  const uint32_t stage_bytes = resb ? a_bytes : a_bytes + b_tile_bytes;
+  const int rows_cta = msub * BM;                       // output rows per CTA and tile
+  const int acc_cols = msub * p.BN;                     // TMEM columns of one tile's accumulators
+  const bool acc2 = 2 * acc_cols <= 512;                // two tiles' accumulators fit: epilogue overlaps the next tile
   const uint32_t ring_base = smem_base + resb_bytes;
   const uint32_t bar0 = smem_u32(bars);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
@@ -622,7 +631,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
   const uint32_t b_full_bar = bar0 + 8u * (2 * MAX_STAGES + 4);
   const int tn_all = p.tiles_n + p.tiles_n2;
-  const int total_tiles = p.tiles_m * tn_all;       // tiles_m counts 256-row tiles here
+  const int total_tiles = p.tiles_m * tn_all;       // tiles_m counts pair tiles (2 * msub * 128 rows) here
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -671,7 +680,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const int tm = t / tn_all;
         const int nn = t - tm * tn_all;
         const bool second = nn >= p.tiles_n;
-        const int m0 = tm * 256 + static_cast<int>(rank) * BM;
+        const int m0 = (tm * 2 + static_cast<int>(rank)) * rows_cta;
         const int n0 = (second ? nn - p.tiles_n : nn) * p.BN + static_cast<int>(rank) * half_n;
         const int kb_begin = second ? p.kb_first2 : 0;
         const int kb_count = second ? p.num_kb2 : p.num_kb;
@@ -703,8 +712,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             tma_load_2d_2sm(a_s, &tmA, full_bar(s), kb * BK, m0);
           }
           if (!resb) {
-            if (second) tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
-            else tma_load_2d_2sm(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+            if (second) tma_load_2d_2sm(a_s + a_bytes, &tmB2, full_bar(s), j * BK, n0);
+            else tma_load_2d_2sm(a_s + a_bytes, &tmB, full_bar(s), kb * BK, n0);
           }
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
@@ -716,10 +725,11 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       if (resb) mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
       for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
-        const int buf = i & 1;
-        mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
+        const int buf = acc2 ? (i & 1) : 0;
+        const int use = acc2 ? (i >> 1) : i;          // how often this accumulator buffer has been used before
+        mbar_wait(acc_empty_bar(buf), (use & 1) ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * acc_cols);
         const bool second = (t % tn_all) >= p.tiles_n;
         const int kb_count = second ? p.num_kb2 : p.num_kb;
         for (int kb = 0; kb < kb_count; ++kb) {
@@ -729,10 +739,14 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             const uint32_t a_s = ring_base + s * stage_bytes;
             const uint64_t adesc = umma_smem_desc_sw128(a_s);
             const uint64_t bdesc = umma_smem_desc_sw128(resb ? smem_base + static_cast<uint32_t>((second ? p.num_kb : 0) + kb) * b_tile_bytes
-                                                             : a_s + A_TILE_BYTES);
+                                                             : a_s + a_bytes);
+            for (int sb = 0; sb < msub; ++sb) {        // the sub-tiles share the weight tile
+              const uint64_t ad = adesc + static_cast<uint64_t>(sb * (A_TILE_BYTES >> 4));
+              const uint32_t dt = d_tmem + static_cast<uint32_t>(sb * p.BN);
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k)
-              umma_bf16_2sm(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < BK / 16; ++k)
+                umma_bf16_2sm(dt, ad + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
             umma_commit_2sm(empty_bar(s));
             if (kb == kb_count - 1) umma_commit_2sm(acc_full_bar(buf));
           }
@@ -747,40 +761,49 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
     int i = 0;
     for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
-      const int buf = i & 1;
+      const int buf = acc2 ? (i & 1) : 0;
+      const int use = acc2 ? (i >> 1) : i;
       const int tm = t / tn_all;
       const int nn = t - tm * tn_all;
       const bool second = nn >= p.tiles_n;
-      const int m0 = tm * 256 + static_cast<int>(rank) * BM;
+      const int m0 = (tm * 2 + static_cast<int>(rank)) * rows_cta;
       const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
       const Epi epi = epi_of(p, second);
-      const int m = m0 + q * 32 + lane;
-      const bool row_ok = m < p.M;
-      const bool pre = row_ok && epi.residual != nullptr && !epi.out_fp32;
+      // the residual of the first sub-tile is fetched before the accumulator is waited for
+      int m = m0 + q * 32 + lane;
+      bool row_ok = m < p.M;
+      bool pre = row_ok && epi.residual != nullptr && !epi.out_fp32;
       uint32_t rr[4][16];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         if (pre && half + 2 * j < n_chunks && n0 + (half + 2 * j) * 32 < epi.Cout)
           prefetch_residual(epi, m, n0 + (half + 2 * j) * 32, rr[j]);
-      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
+      mbar_wait(acc_full_bar(buf), use & 1);
       tc_fence_after();
-      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int c = half + 2 * j;
-        if (c >= n_chunks) break;
-        uint32_t v[32];
-        tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
-        tmem_ld_wait();
-        if (c == last_c) {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) {
-            if (leader) mbar_arrive(acc_empty_bar(buf));
-            else mbar_arrive_cluster(acc_empty_bar(buf), 0);
-          }
+      for (int sb = 0; sb < msub; ++sb) {
+        if (sb > 0) {
+          m = m0 + sb * BM + q * 32 + lane;
+          row_ok = m < p.M;
+          pre = false;
         }
-        if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * acc_cols + sb * p.BN);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c = half + 2 * j;
+          if (c >= n_chunks) break;
+          uint32_t v[32];
+          tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+          tmem_ld_wait();
+          if (c == last_c && sb == msub - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if (leader) mbar_arrive(acc_empty_bar(buf));
+              else mbar_arrive_cluster(acc_empty_bar(buf), 0);
+            }
+          }
+          if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
+        }
       }
     }
   }
@@ -1252,6 +1275,7 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->bias2 = a.bias2;
   p->out2 = a.out2;
   p->resb = 0;
+  p->msub = 1;
 }
 
 template <int AMODE>
@@ -1302,21 +1326,24 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   }
   KP p;
   fill_kp(&p, a);
-  p.tiles_m = (a.g.M + 255) / 256;
-  const int stage = A_TILE_BYTES + (a.BN / 2) * 128;
+  p.msub = (AMODE == A_IM2COL && a.msub == 2) ? 2 : 1;
+  p.tiles_m = (a.g.M + 256 * p.msub - 1) / (256 * p.msub);
+  const int a_bytes = p.msub * A_TILE_BYTES;
+  const int stage = a_bytes + (a.BN / 2) * 128;
   p.stages = std::min(MAX_STAGES, (210 * 1024) / stage);
   uint32_t cols = 32;
-  while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
+  while (cols < static_cast<uint32_t>(std::min(512, 2 * p.msub * a.BN))) cols <<= 1;   // two tiles' accumulators when they fit
   p.tmem_cols = cols;
   const int total = p.tiles_m * (p.tiles_n + p.tiles_n2);
   int grid = std::min(2 * total, sm_count[dev] & ~1);
   size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
   const size_t resb_bytes = static_cast<size_t>(p.num_kb + (p.tiles_n2 ? p.num_kb2 : 0)) * (a.BN / 2) * 128;
-  if (a.resident_b && p.tiles_n == 1 && p.tiles_n2 <= 1 && resb_bytes + 4 * A_TILE_BYTES + 1024 <= 226 * 1024) {
+  if (a.resident_b && p.tiles_n == 1 && p.tiles_n2 <= 1 && resb_bytes + 3 * a_bytes + 1024 <= 226 * 1024) {
     p.resb = 1;
-    p.stages = std::min<int>(MAX_STAGES, static_cast<int>((226 * 1024 - 1024 - resb_bytes) / A_TILE_BYTES));
-    smem = resb_bytes + static_cast<size_t>(p.stages) * A_TILE_BYTES + 1024;
+    p.stages = std::min<int>(MAX_STAGES, static_cast<int>((226 * 1024 - 1024 - resb_bytes) / a_bytes));
+    smem = resb_bytes + static_cast<size_t>(p.stages) * a_bytes + 1024;
   }
+  if (p.stages < 3) return cudaErrorInvalidValue;
   return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
@@ -1588,6 +1615,11 @@ int make_tmap_nhwc64(CUtensorMap* tm, const void* x, int N, int H, int W, int bo
 
 int make_tmap_im2col(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax,
                      const char** err) {
+  return make_tmap_im2col_px(tm, x, g, Nmax, BM, err);
+}
+
+int make_tmap_im2col_px(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax, int pixels,
+                        const char** err) {
   static EncodeIm2colFn fn =
       reinterpret_cast<EncodeIm2colFn>(driver_fn("cuTensorMapEncodeIm2col"));
   if (!fn) { *err = "cuTensorMapEncodeIm2col entry point not found"; return -1; }
@@ -1601,7 +1633,7 @@ int make_tmap_im2col(CUtensorMap* tm, const void* x, const ConvGeom& g, int Nmax
   int upper[2] = {g.pad - (g.S - 1), g.pad - (g.R - 1)};
   cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(g.stride), static_cast<cuuint32_t>(g.stride), 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides,
-                  lower, upper, /*channelsPerPixel=*/BK, /*pixelsPerColumn=*/BM, estr,
+                  lower, upper, /*channelsPerPixel=*/BK, /*pixelsPerColumn=*/static_cast<cuuint32_t>(pixels), estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { *err = "cuTensorMapEncodeIm2col failed"; return static_cast<int>(r); }

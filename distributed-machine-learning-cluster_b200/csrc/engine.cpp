@@ -463,7 +463,30 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           if (make_tmap_flat(&d.tmA, xin, mb_, g.H, g.W, g.C, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_IM2COL) {
-          if (make_tmap_im2col(&d.tmA, xin, g, mb_, &terr)) { *err = c.name + ": " + terr; return false; }
+          // CTA-pair im2col layers: an im2col TMA request costs ~700 cycles whatever its size, so a CTA that owns two
+          // 128-row sub-tiles (one 256-pixel request per k-block) feeds twice the MMAs per request.  It also halves
+          // the number of tiles, and with 256-wide tiles leaves room for one accumulator set only (the epilogue no
+          // longer overlaps the next tile): take it where this estimate of the launch time says so (it does for
+          // layer2.0.conv1 and the 3x3 convs of layer4 at batch 256, not for layer3).  B2I_MSUB=1 / 2 forces it.
+          static const int msub_env = [] { const char* e = getenv("B2I_MSUB"); return e ? atoi(e) : 0; }();
+          d.msub = 1;
+          if (d.pair) {
+            const long long M = static_cast<long long>(mb_) * g.OH * g.OW;
+            const int kb = c.K / 64;
+            // (the fused downsample is detected later; its few extra k-blocks do not change the choice)
+            // a 3x3 / s2 conv will carry its block's 1x1 / s2 downsample as extra tiles of Cin/64 k-blocks each
+            const bool carries = cfg_.fuse_downsample && g.R == 3 && g.stride == 2;
+            auto est = [&](int ms) {
+              const long long units = ((M + 256 * ms - 1) / (256 * ms)) * (c.Cout_pad / d.BN) * (carries ? 2 : 1);
+              const long long waves = (units + 73) / 74;
+              const long long kb_cycles = std::max<long long>(700, static_cast<long long>(ms) * 4 * (d.BN / 2));
+              const long long epi = (2 * ms * d.BN > 512) ? 10000 : 0;
+              const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
+              return waves * (kb_avg * kb_cycles + epi);
+            };
+            d.msub = (msub_env == 1 || msub_env == 2) ? msub_env : (est(2) < est(1) ? 2 : 1);
+          }
+          if (make_tmap_im2col_px(&d.tmA, xin, g, mb_, 128 * d.msub, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_TILED) {
           if (make_tmap_rows(&d.tmA, xin, mb_, c.K, 128, &terr)) { *err = c.name + ": " + terr; return false; }
@@ -557,6 +580,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.pair = d.pair;
         a.resident_b = d.resident_b;
         a.flat = d.flat;
+        a.msub = d.msub;
         if (d.fused_second >= 0) {
           const DevOp& s2 = ops_[d.fused_second];
           const int cpb = d.g.C >> 6;

@@ -123,7 +123,7 @@ class DeviceModel {
     std::vector<float> bias_host;   // fused stem only: its bias travels as kernel parameters
     CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};
     bool has_tmA = false, has_tmB = false;
-    int amode = 0, BN = 0, stages = 0, b_tma = 0, patch = 0, pair = 0, resident_b = 0, flat = 0;
+    int amode = 0, BN = 0, stages = 0, b_tma = 0, patch = 0, pair = 0, resident_b = 0, flat = 0, msub = 1;
     int fused_second = -1;   // index of a 1x1 conv computed inside this op's kernel
     bool skip = false;       // computed by another op's kernel
   };
