@@ -480,7 +480,8 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   a.amode = cs.smallc ? A_SMALLC : (conv_mode >= 1 ? A_IM2COL : A_GATHER);
   a.persistent = conv_mode == 2 ? 0 : 1;
   a.b_tma = (a.amode == A_IM2COL) ? 1 : weights_tma;
-  if (conv_mode == 5 || conv_mode == 7) a.pair = 1;
+  if (conv_mode == 5 || conv_mode == 7 || conv_mode == 8) a.pair = 1;
+  if (conv_mode == 8) a.msub = 2;   // CTA pair, two 128-row sub-tiles per CTA (256-pixel im2col requests)
   if (conv_mode == 7) a.resident_b = 1;   // the launcher falls back to streamed weights when they do not fit
   if (conv_mode == 6) {
     a.BN = cs.Cout_pad <= 256 ? cs.Cout_pad : a.BN;
@@ -507,7 +508,7 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
       a.tmR = residual ? &tmR : nullptr;
     } else if (a.flat) {
       if (make_tmap_flat(&tmA, dx.p, N, H, W, g.C, &terr)) return fail(B2I_ECUDA, terr);
-    } else if (a.amode == A_IM2COL && make_tmap_im2col(&tmA, dx.p, g, N, &terr)) {
+    } else if (a.amode == A_IM2COL && make_tmap_im2col_px(&tmA, dx.p, g, N, 128 * a.msub, &terr)) {
       return fail(B2I_ECUDA, terr);
     }
     CAPI_CUDA(launch_conv_umma(a, (a.patch || a.flat || a.amode == A_IM2COL) ? &tmA : nullptr, a.b_tma ? &tmB : nullptr, nullptr));

@@ -686,8 +686,9 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const int kb_count = second ? p.num_kb2 : p.num_kb;
         int iw_base = 0, ih_base = 0, n_base = 0;
         if (AMODE == A_IM2COL) {
-          n_base = m0 / ohw;
-          const int rem = m0 - n_base * ohw;
+          const int mc = m0 < p.M ? m0 : p.M;   // a CTA whose rows all lie past the batch still loads (zeros): start it just past the last image
+          n_base = mc / ohw;
+          const int rem = mc - n_base * ohw;
           const int oh = rem / p.OW;
           const int ow = rem - oh * p.OW;
           ih_base = oh * p.stride - p.pad;
@@ -1326,7 +1327,7 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   }
   KP p;
   fill_kp(&p, a);
-  p.msub = (AMODE == A_IM2COL && a.msub == 2) ? 2 : 1;
+  p.msub = (AMODE == A_IM2COL && (a.msub == 2 || a.msub == 4)) ? a.msub : 1;   // powers of two only: 384-pixel requests fault
   p.tiles_m = (a.g.M + 256 * p.msub - 1) / (256 * p.msub);
   const int a_bytes = p.msub * A_TILE_BYTES;
   const int stage = a_bytes + (a.BN / 2) * 128;

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 
 namespace b2i {
@@ -428,6 +429,51 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         d.pair = 1;
       }
 
+      // CTA-pair im2col layers: an im2col TMA request costs ~700 cycles whatever its size (tools/microbench/
+      // tma_rate.cu), so a CTA that owns `msub` 128-row sub-tiles (one request of msub * 128 pixels per k-block)
+      // feeds msub times the MMAs per request.  It also divides the number of tiles, and when msub * BN exceeds 256
+      // TMEM columns only one accumulator set fits (the epilogue no longer overlaps the next tile).  Pick tile-N and
+      // msub by an estimate of the launch time at the full micro-batch: waves x (k-blocks x max(request, MMAs) +
+      // exposed epilogue).  At batch 256 it keeps (256, 1) for layer3, takes (128, 2) for layer2.0.conv1 and
+      // (256, 2) for the 3x3 convs of layer4.  msub is 1, 2 or 4: a 384-pixel request faults on B200 (measured).
+      // B2I_MSUB=1 / 2 / 4 forces msub (tile-N unchanged).
+      d.msub = 1;
+      if (d.pair && !d.flat && !o.fc && d.amode == A_IM2COL && g.R > 1) {
+        static const int msub_env = [] { const char* e = getenv("B2I_MSUB"); return e ? atoi(e) : 0; }();
+        const long long M = static_cast<long long>(mb_) * g.OH * g.OW;
+        const int kb = c.K / 64;
+        // a 3x3 / s2 conv will carry its block's 1x1 / s2 downsample as extra tiles of Cin/64 k-blocks each
+        const bool carries = cfg_.fuse_downsample && g.R == 3 && g.stride == 2;
+        auto fits = [&](int bn, int ms) {
+          return ms * bn <= 512 && 3 * (ms * 16384 + (d.resident_b ? 0 : bn / 2 * 128)) <= 210 * 1024;
+        };
+        auto est = [&](int bn, int ms) {
+          const long long units = ((M + 256 * ms - 1) / (256 * ms)) * (c.Cout_pad / bn) * (carries ? 2 : 1);
+          const long long waves = (units + 73) / 74;
+          const long long req = ms <= 2 ? 700 : (ms == 3 ? 730 : 764);
+          const long long kb_cycles = std::max<long long>(req, static_cast<long long>(ms) * 4 * (bn / 2));
+          const long long epi = (2 * ms * bn > 512) ? 10000 : 0;
+          const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
+          return waves * (kb_avg * kb_cycles + epi);
+        };
+        if (msub_env == 1 || msub_env == 2 || msub_env == 4) {
+          if (fits(d.BN, msub_env)) d.msub = msub_env;
+        } else {
+          long long best = est(d.BN, 1);
+          const int bn0 = d.BN;
+          for (int bn : {bn0, 128}) {
+            // the downsample riding on a stride-2 conv shares its tile-N: leave that one alone
+            if (bn > bn0 || c.Cout_pad % bn || bn < cfg_.pair_mma / 2 || ((d.resident_b || carries) && bn != bn0)) continue;
+            for (int ms = 1; ms <= 4; ms *= 2) {   // 384-pixel requests fault: the pixel count must be a power of two
+              if (!fits(bn, ms)) continue;
+              const long long t = est(bn, ms);
+              if (t < best - best / 50) { best = t; d.BN = bn; d.msub = ms; }   // needs a 2 % edge over the simpler choice
+            }
+          }
+        }
+      }
+
+      if (getenv("B2I_PLAN_DEBUG")) fprintf(stderr, "[plan] %s BN %d pair %d msub %d resb %d flat %d patch %d\n", c.name.c_str(), d.BN, d.pair, d.msub, d.resident_b, d.flat, d.patch);
       const size_t wn = c.w.size();
       if (cfg_.precision == PREC_FP32) {
         B2I_CUDA(cudaMalloc(&d.w, wn * 4));
@@ -463,29 +509,6 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           if (make_tmap_flat(&d.tmA, xin, mb_, g.H, g.W, g.C, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_IM2COL) {
-          // CTA-pair im2col layers: an im2col TMA request costs ~700 cycles whatever its size, so a CTA that owns two
-          // 128-row sub-tiles (one 256-pixel request per k-block) feeds twice the MMAs per request.  It also halves
-          // the number of tiles, and with 256-wide tiles leaves room for one accumulator set only (the epilogue no
-          // longer overlaps the next tile): take it where this estimate of the launch time says so (it does for
-          // layer2.0.conv1 and the 3x3 convs of layer4 at batch 256, not for layer3).  B2I_MSUB=1 / 2 forces it.
-          static const int msub_env = [] { const char* e = getenv("B2I_MSUB"); return e ? atoi(e) : 0; }();
-          d.msub = 1;
-          if (d.pair) {
-            const long long M = static_cast<long long>(mb_) * g.OH * g.OW;
-            const int kb = c.K / 64;
-            // (the fused downsample is detected later; its few extra k-blocks do not change the choice)
-            // a 3x3 / s2 conv will carry its block's 1x1 / s2 downsample as extra tiles of Cin/64 k-blocks each
-            const bool carries = cfg_.fuse_downsample && g.R == 3 && g.stride == 2;
-            auto est = [&](int ms) {
-              const long long units = ((M + 256 * ms - 1) / (256 * ms)) * (c.Cout_pad / d.BN) * (carries ? 2 : 1);
-              const long long waves = (units + 73) / 74;
-              const long long kb_cycles = std::max<long long>(700, static_cast<long long>(ms) * 4 * (d.BN / 2));
-              const long long epi = (2 * ms * d.BN > 512) ? 10000 : 0;
-              const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
-              return waves * (kb_avg * kb_cycles + epi);
-            };
-            d.msub = (msub_env == 1 || msub_env == 2) ? msub_env : (est(2) < est(1) ? 2 : 1);
-          }
           if (make_tmap_im2col_px(&d.tmA, xin, g, mb_, 128 * d.msub, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_TILED) {

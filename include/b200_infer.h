@@ -201,7 +201,7 @@ int b2i_model_tensor_shape(const b2i_model* m, int tensor_id, int* h, int* w, in
  * [Cout][C][R][S]; bn: NULL or [4][Cout] = gamma, beta, running_mean, running_var; residual/out:
  * [N][OH][OW][Cout]. conv_mode as in b2i_model_config (0, 1 or 2), or one of the kernels the model
  * chooses by geometry: 3 halo patch (3x3 s1 p1, 64 -> 64), 5 CTA pair, 6 flattened padded rows (3x3 s1 p1,
- * C % 64 == 0, one N tile, W <= 62), 7 CTA pair with resident weights; C <= 4 always uses the
+ * C % 64 == 0, one N tile, W <= 62), 7 CTA pair with resident weights, 8 CTA pair with two sub-tiles per CTA; C <= 4 always uses the
  * small-channel gather. tile_n 0 = default. */
 int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weights_tma, int tile_n,
                   const float* x, int N, int H, int W, int C, const float* w, const float* bias,

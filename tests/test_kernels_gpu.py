@@ -147,6 +147,15 @@ def test_conv3x3_flattened_rows_kernel(ctx):
     conv_case(ctx, 2, 30, 30, 64, 128, 3, 1, 1, precision=BF16, conv_mode=6, bias=True, seed=305)                # W + 2 == pitch
 
 
+def test_conv_pair_multi_subtile(ctx):
+    """CTA-pair im2col kernel with two 128-row sub-tiles per CTA (conv_mode 8): one 256-pixel im2col request
+    per k-block, one or two accumulator sets, tiles that end inside or past the batch."""
+    conv_case(ctx, 9, 7, 7, 512, 512, 3, 1, 1, precision=BF16, conv_mode=8, tile_n=256, bn=True, residual=True, relu=True, seed=320)
+    conv_case(ctx, 37, 7, 7, 512, 512, 3, 1, 1, precision=BF16, conv_mode=8, tile_n=128, bn=True, residual=True, relu=True, seed=321)
+    conv_case(ctx, 3, 56, 56, 64, 128, 3, 2, 1, precision=BF16, conv_mode=8, tile_n=128, bn=True, relu=True, seed=322)
+    conv_case(ctx, 2, 14, 14, 256, 256, 3, 1, 1, precision=BF16, conv_mode=8, tile_n=128, bias=True, seed=323)
+
+
 def test_conv_pair_resident_weights(ctx):
     """CTA-pair im2col kernel keeping all weight k-blocks resident (conv_mode 7): the stride-2 first conv of
     ResNet layer2, a 1x1, and a layer whose weights do not fit (falls back to streaming them)."""
