@@ -822,8 +822,9 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 // 3x3 / stride 1 / pad 1 convolution over FLATTENED PADDED ROWS, CTA pair, resident weights
 // (ResNet layer2: 128 -> 128 channels on 28x28 maps).
 //
-// The im2col kernels above fetch every input pixel nine times from L2, and L2 -> SM bandwidth
-// (about 43 B/clk per SM) is what bounds them.  Here the batch is seen as one long sequence of padded
+// The im2col kernels above fetch every input pixel nine times, through im2col-mode TMA requests that cost
+// about 700 cycles each whatever their size: with 128-wide tiles that is 2.7x the MMA time of a k-block.
+// Here the batch is seen as one long sequence of padded
 // rows: row Y = n*(H+1) + y holds image n's row y as `pitch` pixels (pixel 0 = the left zero pad,
 // pixels 1..W the row, the rest zero), and row n*(H+1) + H is all zero - the bottom pad of image n
 // and the top pad of image n+1 at once.  Flatten those rows and a 3x3 tap (r, s) is a pure shift by
