@@ -182,7 +182,7 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   NetSpec net;
   const bool fused = cfg.fused_stem != 0 && cfg.precision == B2I_PREC_BF16;
   const bool ok = name == "resnet18" ? build_resnet18(tensors, fused, &net, &err)
-                                     : build_alexnet(tensors, cfg.alexnet_geometry, &net, &err);
+                                     : build_alexnet(tensors, cfg.alexnet_geometry, fused, &net, &err);
   if (!ok) return fail(B2I_EIO, err);
   tensors.clear();
 
@@ -231,7 +231,8 @@ int b2i_model_reload(b2i_model* m, const char* ot_path) {
   if (!read_ot_archive(ot_path, &tensors, &err)) return fail(B2I_EIO, err);
   NetSpec net;
   const bool ok = m->name == "resnet18" ? build_resnet18(tensors, m->engine_cfg.fused_stem != 0, &net, &err)
-                                        : build_alexnet(tensors, m->engine_cfg.alexnet_geometry, &net, &err);
+                                        : build_alexnet(tensors, m->engine_cfg.alexnet_geometry,
+                                                        m->engine_cfg.fused_stem != 0 && m->engine_cfg.precision == PREC_BF16, &net, &err);
   if (!ok) return fail(B2I_EIO, err);
   tensors.clear();
   // build the new device copies first (the old ones keep serving), then swap them in under the lock

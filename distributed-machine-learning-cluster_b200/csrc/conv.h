@@ -84,6 +84,11 @@ int conv_umma_pick_stages(int BN);
 cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
                         const float* bias_host, int n_images, unsigned int* sched, cudaStream_t st);
 
+// Fused AlexNet stem (bf16 path): u8 [n][224][224][3] -> normalise -> features.0 11x11/4 pad 2 + bias + ReLU -> bf16
+// [n][55][55][64].  tmW: weight map over [64][704] (K order: filter row, plane (R,G)/(B,0), 16 taps, 2 channels).
+cudaError_t launch_alex_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
+                             const float* bias_host, int n_images, cudaStream_t st);
+
 // fp32 FFMA path (the 1e-4 parity mode; also the on-device cross-check for the tcgen05 path).
 cudaError_t launch_conv_fp32(const ConvArgs& a, cudaStream_t st);
 

@@ -218,11 +218,12 @@ bool build_resnet18(const std::map<std::string, HostTensor>& t, bool fused_stem,
   return true;
 }
 
-bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, NetSpec* net,
+bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, bool fused_stem, NetSpec* net,
                    std::string* err) {
   net->model = "alexnet";
-  const int in0 = new_tensor(net, 224, 224, 4);
-  {
+  int in0 = -1;
+  if (!fused_stem) {
+    in0 = new_tensor(net, 224, 224, 4);
     OpSpec op;
     op.kind = OpSpec::NORMALIZE;
     op.out = in0;
@@ -234,7 +235,19 @@ bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, Net
     return push_pool(net, OpSpec::MAXPOOL, in, 3, 2, 0, conv_out(s.H, 3, 2, 0), conv_out(s.W, 3, 2, 0));
   };
   if (!add_conv_bias(t, "features.0", 64, 3, 11, 4, 2, 0, net, err)) return false;
-  int cur = pool(push_conv(net, last(), in0, -1, true));
+  int cur;
+  if (fused_stem) {   // normalise + features.0 + ReLU in one kernel (stem_alex.cu); the weights are re-packed at load
+    OpSpec op;
+    op.kind = OpSpec::STEM_ALEX;
+    op.conv = last();
+    op.relu = true;
+    op.out = new_tensor(net, 55, 55, 64);
+    net->ops.push_back(op);
+    net->flops_per_image += 2.0 * 55 * 55 * 64 * 3 * 121;
+    cur = pool(op.out);
+  } else {
+    cur = pool(push_conv(net, last(), in0, -1, true));
+  }
   // features.3: tch 0.4.1 builds it as (k5, pad 1, stride 2); torchvision as (k5, pad 2, stride 1).
   // Same weight shape either way.
   const int p3 = geometry == ALEX_TORCHVISION ? 2 : 1, s3 = geometry == ALEX_TORCHVISION ? 1 : 2;
@@ -365,6 +378,30 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       B2I_CUDA(cudaMemset(sp, 0, 256));
       owned_.push_back(sp);
       stem_sched_ = static_cast<unsigned int*>(sp);
+    }
+    if (o.kind == OpSpec::STEM_ALEX) {
+      const ConvSpec& c = net.convs[o.conv];
+      if (cfg_.precision != PREC_BF16 || c.R != 11 || c.S != 11 || c.Cin_pad != 4 || c.Cout != 64 || c.stride != 4 || c.pad != 2) {
+        *err = "fused AlexNet stem needs the bf16 path and features.0 as 11x11, 3 -> 64";
+        return false;
+      }
+      // [64][(r, s < 12, c < 4)] -> [64][704]: filter row r, plane (R,G) / (B,0), 16 taps (11 real), 2 channels
+      std::vector<uint16_t> wb(static_cast<size_t>(64) * 704, 0);
+      for (int oc = 0; oc < 64; ++oc)
+        for (int r = 0; r < 11; ++r)
+          for (int s = 0; s < 11; ++s)
+            for (int ch = 0; ch < 3; ++ch) {
+              const float v = c.w[static_cast<size_t>(oc) * c.K + (r * c.Sp + s) * c.Cin_pad + ch];
+              wb[static_cast<size_t>(oc) * 704 + r * 64 + (ch >> 1) * 32 + s * 2 + (ch & 1)] = f32_to_bf16_rne(v);
+            }
+      B2I_CUDA(cudaMalloc(&d.w, wb.size() * 2));
+      B2I_CUDA(cudaMemcpy(d.w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
+      owned_.push_back(d.w);
+      weight_bytes_ += wb.size() * 2;
+      d.bias_host.assign(c.bias.begin(), c.bias.begin() + 64);
+      const char* terr = "";
+      if (make_tmap_weights(&d.tmB, d.w, 64, 704, 64, &terr)) { *err = std::string("alexnet stem: ") + terr; return false; }
+      d.has_tmB = true;
     }
     if (o.kind == OpSpec::CONV) {
       const ConvSpec& c = net.convs[o.conv];
@@ -521,6 +558,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
     switch (o.kind) {
       case OpSpec::NORMALIZE: op_names_.push_back("normalize"); break;
       case OpSpec::STEM: op_names_.push_back("conv:stem(normalize+conv1+maxpool)"); break;
+      case OpSpec::STEM_ALEX: op_names_.push_back("conv:stem(normalize+features.0)"); break;
       case OpSpec::MAXPOOL: op_names_.push_back("maxpool"); break;
       case OpSpec::AVGPOOL: op_names_.push_back("avgpool"); break;
       case OpSpec::CONV: op_names_.push_back((o.fc ? "fc:" : "conv:") + net.convs[o.conv].name); break;
@@ -563,6 +601,9 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     switch (o.kind) {
       case OpSpec::STEM:
         B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, st));
+        break;
+      case OpSpec::STEM_ALEX:
+        B2I_CUDA(launch_alex_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, st));
         break;
       case OpSpec::NORMALIZE:
         B2I_CUDA(launch_normalize_u8(d_u8, buf(o.out), dt, static_cast<long long>(nb) * 224 * 224, st));

@@ -58,7 +58,7 @@ void build_conv_spec(ConvSpec* cs, const std::string& name, const float* w_oihw,
 struct TensorShape { int H = 0, W = 0, C = 0; size_t elems() const { return size_t(H) * W * C; } };
 
 struct OpSpec {
-  enum Kind { NORMALIZE, CONV, MAXPOOL, AVGPOOL, STEM } kind = CONV;
+  enum Kind { NORMALIZE, CONV, MAXPOOL, AVGPOOL, STEM, STEM_ALEX } kind = CONV;
   int in = -1, out = -1, res = -1;  // activation tensor ids
   int conv = -1;                    // index into NetSpec::convs
   bool relu = false, fc = false, logits = false;
@@ -77,7 +77,7 @@ struct NetSpec {
 
 bool build_resnet18(const std::map<std::string, HostTensor>& t, bool fused_stem, NetSpec* net,
                     std::string* err);
-bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, NetSpec* net,
+bool build_alexnet(const std::map<std::string, HostTensor>& t, int geometry, bool fused_stem, NetSpec* net,
                    std::string* err);
 
 // Device-resident instance of a NetSpec on one GPU.

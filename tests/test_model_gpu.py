@@ -166,6 +166,29 @@ def test_fused_stem_matches_unfused_and_oracle(pkg, ctx, resnet18_ot):
     assert np.abs(lg_f - lg_u).max() <= tol_for(BF16, lg_u)
 
 
+def test_alexnet_fused_stem_matches_unfused(pkg, ctx, alexnet_ot):
+    """normalise + features.0 + ReLU as ONE kernel (two-plane 4-byte pixels, descriptors straight into the input
+    patch): its 55 x 55 x 64 map against the two-kernel path (same roundings, different K order), and the logits
+    of both paths against each other; zeroed / saturated borders exercise the zero-padding edges."""
+    from oracle import synth
+    img = synth.synthetic_images(6, seed=18)
+    img[0, :5] = 0
+    img[1, :, -7:] = 255
+    img[2, -3:, :] = 255
+    with pkg.Model(ctx, "alexnet", alexnet_ot, precision=BF16, max_batch=6, keep_tensors=True, fused_stem=True) as m:
+        _, _, lg_f = m.predict_u8(img, k=5, want_logits=True)
+        assert m.tensor_shape(0) == (55, 55, 64)
+        fused = m.read_tensor(0, 6)
+    with pkg.Model(ctx, "alexnet", alexnet_ot, precision=BF16, max_batch=6, keep_tensors=True, fused_stem=False) as m:
+        _, _, lg_u = m.predict_u8(img, k=5, want_logits=True)
+        assert m.tensor_shape(1) == (55, 55, 64)
+        unfused = m.read_tensor(1, 6)
+    scale = float(np.abs(unfused).max())
+    print("alexnet stem: fused vs unfused %.5f of scale %.2f" % (np.abs(fused - unfused).max() / scale, scale))
+    assert np.abs(fused - unfused).max() <= 2.0 ** -7 * scale      # at most one bf16 ulp flip at the top of the range
+    assert np.abs(lg_f - lg_u).max() <= tol_for(BF16, lg_u)
+
+
 def test_kernel_variants_agree(pkg, ctx, resnet18_ot):
     """Every optional kernel path (fused stem, halo patch, CTA pairs, fused downsample) against the
     plain persistent im2col configuration: same roundings, so logits agree to bf16 noise."""
