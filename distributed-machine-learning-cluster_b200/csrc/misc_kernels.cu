@@ -77,6 +77,37 @@ __global__ void __launch_bounds__(256) maxpool_kernel(const void* __restrict__ i
     float m[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) m[j] = -FLT_MAX;
+    if (k == 3) {
+      // 3x3 window, branch-free: taps outside the image are clamped onto the nearest valid row / column (a
+      // duplicate tap leaves the max unchanged; every window holds at least one valid pixel), so the nine loads
+      // are all in flight together
+      uint4 v[9];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int ih = min(max(h0 + r, 0), H - 1);
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          const int iw = min(max(w0 + s, 0), W - 1);
+          const size_t off = ((static_cast<size_t>(n) * H + ih) * W + iw) * C + c * vec;
+          if (F32) v[r * 3 + s] = __ldg(reinterpret_cast<const uint4*>(static_cast<const float*>(in) + off));
+          else v[r * 3 + s] = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(in) + off));
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const uint32_t u[4] = {v[t].x, v[t].y, v[t].z, v[t].w};
+        if (F32) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) m[e] = fmaxf(m[e], __uint_as_float(u[e]));
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            m[2 * e] = fmaxf(m[2 * e], __uint_as_float(u[e] << 16));
+            m[2 * e + 1] = fmaxf(m[2 * e + 1], __uint_as_float(u[e] & 0xFFFF0000u));
+          }
+        }
+      }
+    } else
     for (int r = 0; r < k; ++r) {
       const int ih = h0 + r;
       if (ih < 0 || ih >= H) continue;
