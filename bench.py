@@ -188,6 +188,8 @@ def main():
     ap.add_argument("--patch-conv", type=int, default=None)
     ap.add_argument("--pair-mma", type=int, default=None)
     ap.add_argument("--fuse-downsample", type=int, default=None)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp16"],
+                    help="16-bit storage format of activations and weights (fp32 accumulate either way)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -214,7 +216,7 @@ def main():
         ot = os.path.join(ROOT, "tests", "_cache", "resnet18.ot")
 
     ctx = b2.Context((local,))
-    model = b2.Model(ctx, MODEL, ot, precision=b2.PREC_BF16, max_batch=BATCH, micro_batch=args.micro_batch,
+    model = b2.Model(ctx, MODEL, ot, precision=b2.PREC_FP16 if args.precision == "fp16" else b2.PREC_BF16, max_batch=BATCH, micro_batch=args.micro_batch,
                      tile_n_max=args.tile_n_max, conv_mode=args.conv_mode, patch_conv=args.patch_conv, pair_mma=args.pair_mma,
                      fuse_downsample=args.fuse_downsample)
     n_micro = (BATCH + (args.micro_batch or BATCH) - 1) // (args.micro_batch or BATCH)
@@ -344,8 +346,8 @@ def main():
     out = {
         "metric": "images/sec ResNet-18 bs=256", "value": value, "unit": "images/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "micro_batch": mb, "top_k": K_TOP,
+        "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+        "config": {"workload": WORKLOAD.replace(", bf16", ", " + args.precision), "batch_per_gpu": BATCH, "micro_batch": mb, "top_k": K_TOP,
                    "l2": "inputs rotate over %d distinct batches (%d MB) > 126 MB L2; activations (> 1 GB per step) never fit" %
                          (ROTATE, ROTATE * BATCH * b2.IMAGE_BYTES // 2 ** 20),
                    "parallelism": "independent batch shards, one process per GPU, no collective",

@@ -8,7 +8,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B2I_LIB") or os.path.join(_HERE, "libb200infer.so")
 
 OK, EINVAL, EIO, ECUDA, ENODEV, ENOMEM = 0, -1, -2, -3, -4, -5
-PREC_BF16, PREC_FP32 = 0, 1
+PREC_BF16, PREC_FP32, PREC_FP16 = 0, 1, 2
 ALEXNET_TCH, ALEXNET_TORCHVISION = 0, 1
 IMAGE_BYTES = 224 * 224 * 3
 CLASSES = 1000

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "engine.h"
+#include "half_host.h"
 #include "predict.h"
 #include "resize.h"
 
@@ -37,19 +38,9 @@ int cuda_fail(cudaError_t e, const char* what) {
     if (e_ != cudaSuccess) return cuda_fail(e_, #call);   \
   } while (0)
 
-inline uint16_t f2bf(float f) {
-  uint32_t u;
-  std::memcpy(&u, &f, 4);
-  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
-  u += 0x7fffu + ((u >> 16) & 1u);
-  return static_cast<uint16_t>(u >> 16);
-}
-inline float bf2f(uint16_t h) {
-  uint32_t u = static_cast<uint32_t>(h) << 16;
-  float f;
-  std::memcpy(&f, &u, 4);
-  return f;
-}
+inline uint16_t f2h16(float f, int prec) { return host_f32_to_16(f, prec == B2I_PREC_FP16); }
+inline float h162f(uint16_t h, int prec) { return host_16_to_f32(h, prec == B2I_PREC_FP16); }
+inline int dtype_of(int prec) { return prec == B2I_PREC_FP32 ? DT_F32 : (prec == B2I_PREC_FP16 ? DT_F16 : DT_BF16); }
 
 struct DevBuf {
   void* p = nullptr;
@@ -63,7 +54,7 @@ cudaError_t upload(DevBuf* d, const float* src, size_t n, int prec) {
   if (e != cudaSuccess) return e;
   if (prec == B2I_PREC_FP32) return cudaMemcpy(d->p, src, n * 4, cudaMemcpyHostToDevice);
   std::vector<uint16_t> t(n);
-  for (size_t i = 0; i < n; ++i) t[i] = f2bf(src[i]);
+  for (size_t i = 0; i < n; ++i) t[i] = f2h16(src[i], prec);
   return cudaMemcpy(d->p, t.data(), n * 2, cudaMemcpyHostToDevice);
 }
 cudaError_t download(const void* dsrc, float* dst, size_t n, int prec) {
@@ -71,7 +62,7 @@ cudaError_t download(const void* dsrc, float* dst, size_t n, int prec) {
   std::vector<uint16_t> t(n);
   cudaError_t e = cudaMemcpy(t.data(), dsrc, n * 2, cudaMemcpyDeviceToHost);
   if (e != cudaSuccess) return e;
-  for (size_t i = 0; i < n; ++i) dst[i] = bf2f(t[i]);
+  for (size_t i = 0; i < n; ++i) dst[i] = h162f(t[i], prec);
   return cudaSuccess;
 }
 
@@ -174,13 +165,13 @@ int b2i_model_load(b2i_ctx* ctx, const char* model_name, const char* ot_path,
   const std::string name(model_name);
   if (name != "resnet18" && name != "alexnet")
     return fail(B2I_EINVAL, "unknown model '" + name + "' (expected resnet18 or alexnet)");
-  if (cfg.precision != B2I_PREC_BF16 && cfg.precision != B2I_PREC_FP32) return fail(B2I_EINVAL, "bad precision");
+  if (cfg.precision != B2I_PREC_BF16 && cfg.precision != B2I_PREC_FP32 && cfg.precision != B2I_PREC_FP16) return fail(B2I_EINVAL, "bad precision");
   if (cfg.max_batch < 1) return fail(B2I_EINVAL, "max_batch must be >= 1");
   std::map<std::string, HostTensor> tensors;
   std::string err;
   if (!read_ot_archive(ot_path, &tensors, &err)) return fail(B2I_EIO, err);
   NetSpec net;
-  const bool fused = cfg.fused_stem != 0 && cfg.precision == B2I_PREC_BF16;
+  const bool fused = cfg.fused_stem != 0 && cfg.precision != B2I_PREC_FP32;
   const bool ok = name == "resnet18" ? build_resnet18(tensors, fused, &net, &err)
                                      : build_alexnet(tensors, cfg.alexnet_geometry, fused, &net, &err);
   if (!ok) return fail(B2I_EIO, err);
@@ -232,7 +223,7 @@ int b2i_model_reload(b2i_model* m, const char* ot_path) {
   NetSpec net;
   const bool ok = m->name == "resnet18" ? build_resnet18(tensors, m->engine_cfg.fused_stem != 0, &net, &err)
                                         : build_alexnet(tensors, m->engine_cfg.alexnet_geometry,
-                                                        m->engine_cfg.fused_stem != 0 && m->engine_cfg.precision == PREC_BF16, &net, &err);
+                                                        m->engine_cfg.fused_stem != 0 && m->engine_cfg.precision != PREC_FP32, &net, &err);
   if (!ok) return fail(B2I_EIO, err);
   tensors.clear();
   // build the new device copies first (the old ones keep serving), then swap them in under the lock
@@ -461,7 +452,7 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   CAPI_CUDA(upload(&dw, cs.w.data(), cs.w.size(), precision));
   CAPI_CUDA(upload(&db, cs.bias.data(), cs.bias.size(), B2I_PREC_FP32));
   const size_t nout = static_cast<size_t>(N) * OH * OW * Cout;
-  const bool bf16 = precision == B2I_PREC_BF16;
+  const bool bf16 = precision != B2I_PREC_FP32;   // either 16-bit storage format: the tcgen05 path
   const bool out32 = bf16 && (Cout % 32 != 0);
   if (out32 && residual) return fail(B2I_EINVAL, "bf16 conv with a residual needs Cout % 32 == 0");
   if (residual) CAPI_CUDA(upload(&dr, residual, nout, precision));
@@ -473,6 +464,7 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   g.stride = stride; g.pad = pad; g.Cout = Cout; g.Cout_pad = cs.Cout_pad; g.K = cs.K; g.M = N * OH * OW;
   a.x = dx.p; a.w = dw.p; a.bias = static_cast<const float*>(db.p); a.residual = residual ? dr.p : nullptr;
   a.out = dout.p; a.ldo = Cout; a.relu = relu; a.out_fp32 = out32 ? 1 : 0;
+  a.f16 = precision == B2I_PREC_FP16 ? 1 : 0;
   int bnv = tile_n > 0 ? tile_n : 128;
   bnv = std::min(bnv, 256) / 32 * 32;
   while (bnv > 32 && cs.Cout_pad % bnv) bnv -= 32;
@@ -541,6 +533,7 @@ int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float*
   g.Cout = Cout; g.Cout_pad = cs.Cout_pad; g.K = cs.K; g.M = M;
   a.x = dx.p; a.w = dw.p; a.bias = static_cast<const float*>(db.p); a.residual = nullptr; a.out = dout.p;
   a.ldo = Cout; a.relu = relu; a.out_fp32 = 1;
+  a.f16 = precision == B2I_PREC_FP16 ? 1 : 0;
   int bnv = tile_n > 0 ? tile_n : 128;
   bnv = std::min(bnv, 256) / 32 * 32;
   while (bnv > 32 && cs.Cout_pad % bnv) bnv -= 32;
@@ -567,7 +560,7 @@ int b2i_op_maxpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, 
   const size_t nin = static_cast<size_t>(N) * H * W * C, nout = static_cast<size_t>(N) * OH * OW * C;
   CAPI_CUDA(upload(&dx, x, nin, precision));
   CAPI_CUDA(dout.alloc(nout * 4));
-  CAPI_CUDA(launch_maxpool(dx.p, dout.p, precision == B2I_PREC_FP32 ? DT_F32 : DT_BF16, N, H, W, C, k, stride, pad, OH, OW, nullptr));
+  CAPI_CUDA(launch_maxpool(dx.p, dout.p, dtype_of(precision), N, H, W, C, k, stride, pad, OH, OW, nullptr));
   CAPI_CUDA(cudaDeviceSynchronize());
   CAPI_CUDA(download(dout.p, out, nout, precision));
   return B2I_OK;
@@ -580,7 +573,7 @@ int b2i_op_adaptive_avgpool(b2i_ctx* ctx, int dev, int precision, const float* x
   const size_t nin = static_cast<size_t>(N) * H * W * C, nout = static_cast<size_t>(N) * OH * OW * C;
   CAPI_CUDA(upload(&dx, x, nin, precision));
   CAPI_CUDA(dout.alloc(nout * 4));
-  CAPI_CUDA(launch_adaptive_avgpool(dx.p, dout.p, precision == B2I_PREC_FP32 ? DT_F32 : DT_BF16, N, H, W, C, OH, OW, nullptr));
+  CAPI_CUDA(launch_adaptive_avgpool(dx.p, dout.p, dtype_of(precision), N, H, W, C, OH, OW, nullptr));
   CAPI_CUDA(cudaDeviceSynchronize());
   CAPI_CUDA(download(dout.p, out, nout, precision));
   return B2I_OK;
@@ -594,7 +587,7 @@ int b2i_op_normalize(b2i_ctx* ctx, int dev, int precision, const uint8_t* images
   CAPI_CUDA(din.alloc(nin));
   CAPI_CUDA(cudaMemcpy(din.p, images, nin, cudaMemcpyHostToDevice));
   CAPI_CUDA(dout.alloc(nout * 4));
-  CAPI_CUDA(launch_normalize_u8(static_cast<const uint8_t*>(din.p), dout.p, precision == B2I_PREC_FP32 ? DT_F32 : DT_BF16,
+  CAPI_CUDA(launch_normalize_u8(static_cast<const uint8_t*>(din.p), dout.p, dtype_of(precision),
                                 static_cast<long long>(n) * 224 * 224, nullptr));
   CAPI_CUDA(cudaDeviceSynchronize());
   CAPI_CUDA(download(dout.p, out, nout, precision));

@@ -52,6 +52,7 @@ struct ConvArgs {
   int ldo2 = 0, relu2 = 0, kb_first2 = 0, num_kb2 = 0;
   int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
   int resident_b = 0;             // pair kernel: keep all weight k-blocks in shared memory when they fit (one N-tile)
+  int f16 = 0;                    // tcgen05 path: 16-bit tensors (activations, weights) are IEEE half instead of bf16
   int msub = 1;                   // pair im2col kernel: 2 = two 128-row sub-tiles per CTA; tmA must then be a 256-pixel im2col map
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
   const CUtensorMap* tmO = nullptr;
@@ -82,12 +83,12 @@ int conv_umma_pick_stages(int BN);
 // shared by launches that may overlap.  in_u8 must be 4-byte aligned.  bias_host: 64 floats in HOST memory
 // (they travel as kernel parameters).
 cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                        const float* bias_host, int n_images, unsigned int* sched, cudaStream_t st);
+                        const float* bias_host, int n_images, unsigned int* sched, int f16, cudaStream_t st);
 
 // Fused AlexNet stem (bf16 path): u8 [n][224][224][3] -> normalise -> features.0 11x11/4 pad 2 + bias + ReLU -> bf16
 // [n][55][55][64].  tmW: weight map over [64][704] (K order: filter row, plane (R,G)/(B,0), 16 taps, 2 channels).
 cudaError_t launch_alex_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                             const float* bias_host, int n_images, cudaStream_t st);
+                             const float* bias_host, int n_images, int f16, cudaStream_t st);
 
 // fp32 FFMA path (the 1e-4 parity mode; also the on-device cross-check for the tcgen05 path).
 cudaError_t launch_conv_fp32(const ConvArgs& a, cudaStream_t st);

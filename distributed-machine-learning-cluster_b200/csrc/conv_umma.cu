@@ -46,6 +46,7 @@ struct KP {
   void* out2;
   int resb;   // pair kernel: this CTA's half of ALL weight k-blocks stays resident in shared memory
   int msub;   // pair kernel: 128-row sub-tiles per CTA (1 or 2)
+  int f16;    // 16-bit tensors are IEEE half instead of bf16
 };
 
 // Where one tile's results go.
@@ -53,7 +54,7 @@ struct Epi {
   const float* bias;
   const __nv_bfloat16* residual;
   void* out;
-  int ldo, relu, out_fp32, Cout;
+  int ldo, relu, out_fp32, Cout, f16;
 };
 __device__ __forceinline__ Epi epi_of(const KP& p, bool second) {
   Epi e;
@@ -64,12 +65,53 @@ __device__ __forceinline__ Epi epi_of(const KP& p, bool second) {
   e.relu = second ? p.relu2 : p.relu;
   e.out_fp32 = second ? 0 : p.out_fp32;
   e.Cout = second ? p.Cout2 : p.Cout;
+  e.f16 = p.f16;
   return e;
 }
 
 
+// 16-bit tail of epilogue_chunk for one storage format: (+ residual) -> ReLU -> pack -> two 32-byte stores.
+template <bool F16>
+__device__ __forceinline__ void epilogue_store16(const Epi& p, size_t off, float (&f)[32], const uint32_t (*rpre)[16]) {
+  if (p.residual) {
+    // Written by an earlier kernel that may have overlapped this one's start: read it from L2, never L1,
+    // one whole 32-byte sector per load (row stride and channel offset are multiples of 32 channels).
+    if (rpre) {
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        f[e * 2] += lo16_t<F16>((*rpre)[e]);
+        f[e * 2 + 1] += hi16_t<F16>((*rpre)[e]);
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        uint32_t rr[8];
+        ldg256_cg(p.residual + off + q * 16, rr);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          f[q * 16 + e * 2] += lo16_t<F16>(rr[e]);
+          f[q * 16 + e * 2 + 1] += hi16_t<F16>(rr[e]);
+        }
+      }
+    }
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+  __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    uint32_t ov[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ov[e] = pack16x2_t<F16>(f[q * 16 + 2 * e], f[q * 16 + 2 * e + 1]);
+    stg256(op + q * 16, ov);
+  }
+}
+
 // One output row x 32 consecutive channels: acc + bias (+ residual) -> ReLU -> store.
 // `rpre`: the residual's 32 channels already in registers (see prefetch_residual), or null to load them here.
+template <bool F16>
 __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, const uint32_t (&v)[32],
                                                const uint32_t (*rpre)[16] = nullptr) {
   float f[32];
@@ -101,40 +143,7 @@ __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, cons
   }
   if (nb >= p.Cout) return;
   const size_t off = static_cast<size_t>(m) * p.ldo + nb;
-  if (p.residual) {
-    // Written by an earlier kernel that may have overlapped this one's start: read it from L2, never L1,
-    // one whole 32-byte sector per load (row stride and channel offset are multiples of 32 channels).
-    if (rpre) {
-#pragma unroll
-      for (int e = 0; e < 16; ++e) {
-        f[e * 2] += bf16_lo((*rpre)[e]);
-        f[e * 2 + 1] += bf16_hi((*rpre)[e]);
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        uint32_t rr[8];
-        ldg256_cg(p.residual + off + q * 16, rr);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          f[q * 16 + e * 2] += bf16_lo(rr[e]);
-          f[q * 16 + e * 2 + 1] += bf16_hi(rr[e]);
-        }
-      }
-    }
-  }
-  if (p.relu) {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-  }
-  __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + off;
-#pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    uint32_t ov[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) ov[e] = pack_bf16x2(f[q * 16 + 2 * e], f[q * 16 + 2 * e + 1]);
-    stg256(op + q * 16, ov);
-  }
+  epilogue_store16<F16>(p, off, f, rpre);
 }
 
 // Issue the residual loads of one output row x 32 channels early (before the accumulator is ready), so
@@ -148,7 +157,7 @@ __device__ __forceinline__ void prefetch_residual(const Epi& p, int m, int nb, u
   for (int e = 0; e < 8; ++e) { r[e] = lo[e]; r[8 + e] = hi[e]; }
 }
 
-template <int AMODE, bool B_TMA>
+template <int AMODE, bool B_TMA, bool F16>
 __global__ void __launch_bounds__(NTHREADS)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const KP p) {
@@ -296,7 +305,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t v[32];
       tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
       tmem_ld_wait();
-      if (row_ok) epilogue_chunk(epi_of(p, false), m, n0 + c * 32, v);
+      if (row_ok) epilogue_chunk<F16>(epi_of(p, false), m, n0 + c * 32, v);
     }
   } else if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
@@ -334,7 +343,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else {
     // ------------------------------------------------------------------ MMA issuer (warp 5)
-    const uint32_t idesc = umma_idesc_bf16(BM, p.BN);
+    const uint32_t idesc = umma_idesc_bf16(BM, p.BN, F16 ? 1 : 0);
     int s = 0, ph = 0;
     for (int kb = 0; kb < p.num_kb; ++kb) {
       mbar_wait(full_bar(s), ph);
@@ -371,7 +380,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 //   warp 0: TMA producer   warp 1: TMEM alloc + MMA issue   warps 2-9: epilogue
 constexpr int PTHREADS = 64 + 256;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
 
-template <int AMODE>
+template <int AMODE, bool F16>
 __global__ void __launch_bounds__(PTHREADS, 1)
 conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                             const __grid_constant__ CUtensorMap tmB,
@@ -463,7 +472,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = umma_idesc_bf16(BM, p.BN);
+    const uint32_t idesc = umma_idesc_bf16(BM, p.BN, F16 ? 1 : 0);
     int s = 0, ph = 0, i = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
       const int buf = i & 1;
@@ -520,7 +529,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
           __syncwarp();
           if (lane == 0) mbar_arrive(acc_empty_bar(buf));
         }
-        if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v);
+        if (row_ok) epilogue_chunk<F16>(epi, m, n0 + c * 32, v);
       }
     }
   }
@@ -591,7 +600,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
       : "memory");
 }
 
-template <int AMODE>
+template <int AMODE, bool F16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
 conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmB2, const KP p) {
@@ -722,7 +731,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
   } else if (warp == 1) {
     if (leader) {
-      const uint32_t idesc = umma_idesc_bf16(256, p.BN);
+      const uint32_t idesc = umma_idesc_bf16(256, p.BN, F16 ? 1 : 0);
       if (resb) mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
       for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
@@ -803,7 +812,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
               else mbar_arrive_cluster(acc_empty_bar(buf), 0);
             }
           }
-          if (row_ok) epilogue_chunk(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
+          if (row_ok) epilogue_chunk<F16>(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
         }
       }
     }
@@ -840,7 +849,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 struct FlatP {
   int H, W, N, slices, BN, pitch, rpt, box_w;   // rpt = rows per 128-position tile
   int rows_total, total_pairs, nbuf;
-  int ldo, relu, Cout;
+  int ldo, relu, Cout, f16;
   uint32_t tmem_cols;
   const float* bias;
   const __nv_bfloat16* residual;
@@ -856,6 +865,7 @@ __device__ __forceinline__ void tma_load_4d_2sm(uint32_t dst, const CUtensorMap*
 
 constexpr int FLAT_MAXBUF = 4;
 
+template <bool F16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
 conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB, const FlatP p) {
   griddep_launch();
@@ -945,7 +955,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     }
   } else if (warp == 1) {
     if (leader) {
-      const uint32_t idesc = umma_idesc_bf16(256, p.BN);
+      const uint32_t idesc = umma_idesc_bf16(256, p.BN, F16 ? 1 : 0);
       mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
       for (int t = cluster_id; t < p.total_pairs; t += num_clusters, ++i) {
@@ -977,7 +987,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     const int n_chunks = p.BN >> 5;
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
     Epi epi;
-    epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout;
+    epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
     int i = 0;
     for (int t = cluster_id; t < p.total_pairs; t += num_clusters, ++i) {
       const int buf = i & 1;
@@ -1010,7 +1020,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
             else mbar_arrive_cluster(acc_empty_bar(buf), 0);
           }
         }
-        if (row_ok) epilogue_chunk(epi, m, c * 32, v, pre ? &rr[j] : nullptr);
+        if (row_ok) epilogue_chunk<F16>(epi, m, c * 32, v, pre ? &rr[j] : nullptr);
       }
     }
   }
@@ -1040,7 +1050,7 @@ constexpr uint32_t PT_WBYTES = 9 * 64 * 128;                                // r
 constexpr int PT_BUFS = 3;   // patches (+ residual tiles) in flight
 
 struct PatchP {
-  int N, H, W, tiles_w, tiles_h, total_tiles, relu;
+  int N, H, W, tiles_w, tiles_h, total_tiles, relu, f16;
   const float* bias;
   const __nv_bfloat16* residual;
   __nv_bfloat16* out;
@@ -1067,6 +1077,7 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src
 // Epilogue without per-thread global traffic: the residual tile arrives by TMA next to the patch,
 // the result leaves by one TMA store from a 128B-swizzled staging tile (rows past the image edge
 // are clipped by the TMA unit).
+template <bool F16>
 __global__ void __launch_bounds__(PATCH_THREADS, 1)
 conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                          const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
@@ -1140,7 +1151,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = umma_idesc_bf16(128, 64);
+    const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
     mbar_wait(w_full, 0);
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
@@ -1208,8 +1219,8 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
                        : "r"(r_row + ((static_cast<uint32_t>(c * 4 + g) ^ sw) << 4)));
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            f[g * 8 + e * 2] += bf16_lo(rr[e]);
-            f[g * 8 + e * 2 + 1] += bf16_hi(rr[e]);
+            f[g * 8 + e * 2] += lo16_t<F16>(rr[e]);
+            f[g * 8 + e * 2 + 1] += hi16_t<F16>(rr[e]);
           }
         }
         __syncwarp();
@@ -1226,8 +1237,8 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
 #pragma unroll
       for (int g = 0; g < 4; ++g)
         asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(o_row + ((static_cast<uint32_t>(c * 4 + g) ^ sw) << 4)),
-                     "r"(pack_bf16x2(f[g * 8 + 0], f[g * 8 + 1])), "r"(pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3])),
-                     "r"(pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5])), "r"(pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]))
+                     "r"(pack16x2_t<F16>(f[g * 8 + 0], f[g * 8 + 1])), "r"(pack16x2_t<F16>(f[g * 8 + 2], f[g * 8 + 3])),
+                     "r"(pack16x2_t<F16>(f[g * 8 + 4], f[g * 8 + 5])), "r"(pack16x2_t<F16>(f[g * 8 + 6], f[g * 8 + 7]))
                      : "memory");
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -1278,9 +1289,10 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->out2 = a.out2;
   p->resb = 0;
   p->msub = 1;
+  p->f16 = a.f16;
 }
 
-template <int AMODE>
+template <int AMODE, bool F16>
 cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
                               cudaStream_t st) {
   static bool attr_set[16] = {};
@@ -1288,7 +1300,7 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
-  auto kern = conv_umma_persistent_kernel<AMODE>;
+  auto kern = conv_umma_persistent_kernel<AMODE, F16>;
   if (!attr_set[dev]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
     if (e != cudaSuccess) return e;
@@ -1311,14 +1323,14 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   return launch_pdl(kern, dim3(static_cast<unsigned>(grid2)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
-template <int AMODE>
+template <int AMODE, bool F16>
 cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
-  auto kern = conv_umma_pair_kernel<AMODE>;
+  auto kern = conv_umma_pair_kernel<AMODE, F16>;
   if (!attr_set[dev]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
     if (e != cudaSuccess) return e;
@@ -1349,6 +1361,7 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
+template <bool F16>
 cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmW,
                          cudaStream_t st) {
   if (!a.tmO || (a.residual && !a.tmR)) return cudaErrorInvalidValue;
@@ -1359,7 +1372,7 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   if (dev >= 16) return cudaErrorInvalidDevice;
   const size_t smem = PT_WBYTES + PT_BUFS * (PT_BYTES + PT_TILE_BYTES) + 2 * PT_TILE_BYTES + 1024;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_patch_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
@@ -1373,13 +1386,15 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   p.tiles_h = (g.H + 15) / 16;
   p.total_tiles = g.N * p.tiles_w * p.tiles_h;
   p.relu = a.relu;
+  p.f16 = a.f16;
   p.bias = a.bias;
   p.residual = static_cast<const __nv_bfloat16*>(a.residual);
   p.out = static_cast<__nv_bfloat16*>(a.out);
   const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
-  return launch_pdl(conv3x3_c64_patch_kernel, dim3(grid), dim3(PATCH_THREADS), smem, st, *tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
+  return launch_pdl(conv3x3_c64_patch_kernel<F16>, dim3(grid), dim3(PATCH_THREADS), smem, st, *tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
 }
 
+template <bool F16>
 cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmB, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
@@ -1387,7 +1402,7 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(conv3x3_flat_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_flat_pair_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
@@ -1404,7 +1419,7 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   const size_t resb = static_cast<size_t>(9) * p.slices * (a.BN / 2) * 128;
   const size_t patch = static_cast<size_t>(p.rpt + 2) * p.pitch * 128 + 1024;
   p.nbuf = static_cast<int>(std::min<size_t>(FLAT_MAXBUF, (226 * 1024 - 1024 - resb) / patch));
-  p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout;
+  p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout; p.f16 = a.f16;
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
   p.tmem_cols = cols;
@@ -1413,16 +1428,16 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   p.out = a.out;
   const int grid = std::min(2 * p.total_pairs, sm_count[dev] & ~1);
   const size_t smem = resb + p.nbuf * patch + 1024;
-  return launch_pdl(conv3x3_flat_pair_kernel, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmX, *tmB, p);
+  return launch_pdl(conv3x3_flat_pair_kernel<F16>, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmX, *tmB, p);
 }
 
-template <int AMODE, bool B_TMA>
+template <int AMODE, bool B_TMA, bool F16>
 cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
                      cudaStream_t st) {
   static bool attr_set[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
-  auto kern = conv_umma_kernel<AMODE, B_TMA>;
+  auto kern = conv_umma_kernel<AMODE, B_TMA, F16>;
   if (dev < 16 && !attr_set[dev]) {
     cudaError_t e =
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);  // 227 KB minus the static barriers
@@ -1460,8 +1475,9 @@ int conv_umma_pick_stages(int BN) {
   return s;
 }
 
-cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
-                             cudaStream_t st) {
+template <bool F16>
+static cudaError_t launch_conv_umma_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
+                                      cudaStream_t st) {
   const ConvGeom& g = a.g;
   if (a.BN < 32 || a.BN > 256 || (a.BN & 31) || g.Cout_pad % a.BN || g.K % BK || a.stages < 3 ||
       a.stages > MAX_STAGES || g.M <= 0)
@@ -1470,33 +1486,38 @@ cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CU
   if (a.tmB2 && !((a.amode == A_IM2COL) && (a.persistent || a.pair))) return cudaErrorInvalidValue;
   if (a.flat) {
     if (!conv_flat_applicable(g, a.BN) || a.out_fp32 || a.ldo != g.Cout || !tmA || !tmB) return cudaErrorInvalidValue;
-    return launch_flat(a, tmA, tmB, st);
+    return launch_flat<F16>(a, tmA, tmB, st);
   }
   if (a.patch) {
     if (!conv_patch_applicable(g) || a.out_fp32 || a.ldo != 64 || !tmA || !tmB) return cudaErrorInvalidValue;
-    return launch_patch(a, tmA, tmB, st);
+    return launch_patch<F16>(a, tmA, tmB, st);
   }
   switch (a.amode) {
     case A_GATHER:
       if (g.C % 64 || g.K != g.R * g.S * g.C) return cudaErrorInvalidValue;
-      return a.b_tma ? launch_t<A_GATHER, true>(a, nullptr, tmB, st)
-                     : launch_t<A_GATHER, false>(a, nullptr, nullptr, st);
+      return a.b_tma ? launch_t<A_GATHER, true, F16>(a, nullptr, tmB, st)
+                     : launch_t<A_GATHER, false, F16>(a, nullptr, nullptr, st);
     case A_SMALLC:
       if (g.C != 4 || g.K < g.R * g.Sp * 4) return cudaErrorInvalidValue;
-      return a.b_tma ? launch_t<A_SMALLC, true>(a, nullptr, tmB, st)
-                     : launch_t<A_SMALLC, false>(a, nullptr, nullptr, st);
+      return a.b_tma ? launch_t<A_SMALLC, true, F16>(a, nullptr, tmB, st)
+                     : launch_t<A_SMALLC, false, F16>(a, nullptr, nullptr, st);
     case A_IM2COL:
       if (g.C % 64 || g.K != g.R * g.S * g.C || !tmA || !tmB) return cudaErrorInvalidValue;
-      if (a.pair && a.BN >= 64) return launch_pair<A_IM2COL>(a, tmA, tmB, st);
-      return a.persistent ? launch_persistent<A_IM2COL>(a, tmA, tmB, st)
-                          : launch_t<A_IM2COL, true>(a, tmA, tmB, st);
+      if (a.pair && a.BN >= 64) return launch_pair<A_IM2COL, F16>(a, tmA, tmB, st);
+      return a.persistent ? launch_persistent<A_IM2COL, F16>(a, tmA, tmB, st)
+                          : launch_t<A_IM2COL, true, F16>(a, tmA, tmB, st);
     case A_TILED:
       if (!tmA || !tmB) return cudaErrorInvalidValue;
-      if (a.pair && a.BN >= 64) return launch_pair<A_TILED>(a, tmA, tmB, st);
-      return a.persistent ? launch_persistent<A_TILED>(a, tmA, tmB, st)
-                          : launch_t<A_TILED, true>(a, tmA, tmB, st);
+      if (a.pair && a.BN >= 64) return launch_pair<A_TILED, F16>(a, tmA, tmB, st);
+      return a.persistent ? launch_persistent<A_TILED, F16>(a, tmA, tmB, st)
+                          : launch_t<A_TILED, true, F16>(a, tmA, tmB, st);
   }
   return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_conv_umma(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
+                             cudaStream_t st) {
+  return a.f16 ? launch_conv_umma_t<true>(a, tmA, tmB, st) : launch_conv_umma_t<false>(a, tmA, tmB, st);
 }
 
 // ---------------------------------------------------------------------------- tensor maps

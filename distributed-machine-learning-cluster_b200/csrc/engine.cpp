@@ -1,5 +1,6 @@
 // See engine.h.
 #include "engine.h"
+#include "half_host.h"
 
 #include <algorithm>
 #include <cmath>
@@ -11,20 +12,6 @@ namespace b2i {
 namespace {
 
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
-
-inline uint16_t f32_to_bf16_rne(float f) {
-  uint32_t u;
-  std::memcpy(&u, &f, 4);
-  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;  // NaN
-  u += 0x7fffu + ((u >> 16) & 1u);
-  return static_cast<uint16_t>(u >> 16);
-}
-inline float bf16_to_f32(uint16_t h) {
-  uint32_t u = static_cast<uint32_t>(h) << 16;
-  float f;
-  std::memcpy(&f, &u, 4);
-  return f;
-}
 
 const HostTensor* find(const std::map<std::string, HostTensor>& t, const std::string& name,
                        std::string* err) {
@@ -352,14 +339,15 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
   }
 
   // ---- weights + per-op launch plan
+  const bool f16 = cfg_.precision == PREC_FP16;   // 16-bit tensors are IEEE half instead of bf16
   for (const OpSpec& o : net.ops) {
     DevOp d;
     d.spec = o;
     if (o.kind == OpSpec::STEM) {
       const ConvSpec& c = net.convs[o.conv];
-      if (cfg_.precision != PREC_BF16 || c.K != 256 || c.Cout != 64) { *err = "fused stem needs the bf16 path and conv1 as [64][256]"; return false; }
+      if (cfg_.precision == PREC_FP32 || c.K != 256 || c.Cout != 64) { *err = "fused stem needs the bf16 path and conv1 as [64][256]"; return false; }
       std::vector<uint16_t> wb(c.w.size());
-      for (size_t i = 0; i < wb.size(); ++i) wb[i] = f32_to_bf16_rne(c.w[i]);
+      for (size_t i = 0; i < wb.size(); ++i) wb[i] = host_f32_to_16(c.w[i], f16);
       B2I_CUDA(cudaMalloc(&d.w, wb.size() * 2));
       B2I_CUDA(cudaMemcpy(d.w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
       owned_.push_back(d.w);
@@ -381,7 +369,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
     }
     if (o.kind == OpSpec::STEM_ALEX) {
       const ConvSpec& c = net.convs[o.conv];
-      if (cfg_.precision != PREC_BF16 || c.R != 11 || c.S != 11 || c.Cin_pad != 4 || c.Cout != 64 || c.stride != 4 || c.pad != 2) {
+      if (cfg_.precision == PREC_FP32 || c.R != 11 || c.S != 11 || c.Cin_pad != 4 || c.Cout != 64 || c.stride != 4 || c.pad != 2) {
         *err = "fused AlexNet stem needs the bf16 path and features.0 as 11x11, 3 -> 64";
         return false;
       }
@@ -392,7 +380,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           for (int s = 0; s < 11; ++s)
             for (int ch = 0; ch < 3; ++ch) {
               const float v = c.w[static_cast<size_t>(oc) * c.K + (r * c.Sp + s) * c.Cin_pad + ch];
-              wb[static_cast<size_t>(oc) * 704 + r * 64 + (ch >> 1) * 32 + s * 2 + (ch & 1)] = f32_to_bf16_rne(v);
+              wb[static_cast<size_t>(oc) * 704 + r * 64 + (ch >> 1) * 32 + s * 2 + (ch & 1)] = host_f32_to_16(v, f16);
             }
       B2I_CUDA(cudaMalloc(&d.w, wb.size() * 2));
       B2I_CUDA(cudaMemcpy(d.w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
@@ -443,15 +431,15 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       else if (c.smallc) d.amode = A_SMALLC;
       else d.amode = (cfg_.conv_amode == A_GATHER) ? A_GATHER : A_IM2COL;
       if (d.amode == A_IM2COL || d.amode == A_TILED) d.b_tma = 1;
-      d.patch = (cfg_.patch_conv && cfg_.precision == PREC_BF16 && !o.fc && d.amode == A_IM2COL && conv_patch_applicable(g))
+      d.patch = (cfg_.patch_conv && cfg_.precision != PREC_FP32 && !o.fc && d.amode == A_IM2COL && conv_patch_applicable(g))
                     ? 1 : 0;
       if (d.patch) d.BN = 64;
-      d.pair = (cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && d.BN >= cfg_.pair_mma &&
+      d.pair = (cfg_.pair_mma && cfg_.precision != PREC_FP32 && !d.patch && d.BN >= cfg_.pair_mma &&
                 (d.amode == A_IM2COL || d.amode == A_TILED)) ? 1 : 0;
       // One N-tile whose weights fit in shared memory next to four A stages (ResNet layer2): CTA pairs with
       // resident weights, whatever pair_mma says about the tile width.  B2I_NO_RESB=1 turns this off.
       static const bool resb_on = [] { const char* e = getenv("B2I_NO_RESB"); return !(e && e[0] == '1'); }();
-      if (resb_on && cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && !o.fc && d.amode == A_IM2COL &&
+      if (resb_on && cfg_.pair_mma && cfg_.precision != PREC_FP32 && !d.patch && !o.fc && d.amode == A_IM2COL &&
           d.BN == c.Cout_pad && d.BN >= 64 &&
           static_cast<size_t>(c.K / 64 + c.Cin_pad / 64) * (d.BN / 2) * 128 + 4 * 16384 + 1024 <= 226 * 1024) {
         d.pair = 1;
@@ -460,7 +448,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       // 3x3 / s1 convs of that kind go one step further: flattened padded rows, each pixel fetched from L2
       // 1.5 times instead of nine.  B2I_NO_FLAT=1 turns this off.
       static const bool flat_on = [] { const char* e = getenv("B2I_NO_FLAT"); return !(e && e[0] == '1'); }();
-      if (flat_on && cfg_.pair_mma && cfg_.precision == PREC_BF16 && !d.patch && !o.fc && d.amode == A_IM2COL &&
+      if (flat_on && cfg_.pair_mma && cfg_.precision != PREC_FP32 && !d.patch && !o.fc && d.amode == A_IM2COL &&
           conv_flat_applicable(g, d.BN)) {
         d.flat = 1;
         d.pair = 1;
@@ -518,7 +506,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         weight_bytes_ += wn * 4;
       } else {
         std::vector<uint16_t> wb(wn);
-        for (size_t i = 0; i < wn; ++i) wb[i] = f32_to_bf16_rne(c.w[i]);
+        for (size_t i = 0; i < wn; ++i) wb[i] = host_f32_to_16(c.w[i], f16);
         B2I_CUDA(cudaMalloc(&d.w, wn * 2));
         B2I_CUDA(cudaMemcpy(d.w, wb.data(), wn * 2, cudaMemcpyHostToDevice));
         weight_bytes_ += wn * 2;
@@ -530,7 +518,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       owned_.push_back(bp);
       d.bias = static_cast<float*>(bp);
 
-      if (cfg_.precision == PREC_BF16) {
+      if (cfg_.precision != PREC_FP32) {
         const char* terr = "";
         if (d.b_tma) {
           if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.pair ? d.BN / 2 : d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
@@ -568,7 +556,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
   // A 1x1 / stride-s / pad-0 conv followed by a 3x3 / stride-s / pad-1 conv on the same input (the
   // ResNet downsample and the block's first conv) read the same pixels: the 1x1 conv's input is the
   // centre tap of the 3x3 window.  Compute the former as extra N-tiles of the latter's kernel.
-  if (cfg_.fuse_downsample && cfg_.precision == PREC_BF16) {
+  if (cfg_.fuse_downsample && cfg_.precision != PREC_FP32) {
     for (size_t i = 0; i + 1 < ops_.size(); ++i) {
       DevOp& a = ops_[i];
       DevOp& b = ops_[i + 1];
@@ -588,7 +576,8 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
 
 bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_idx, float* d_prob,
                                  float* d_logits, cudaStream_t st, std::string* err) {
-  const int dt = cfg_.precision == PREC_FP32 ? DT_F32 : DT_BF16;
+  const int dt = cfg_.precision == PREC_FP32 ? DT_F32 : (cfg_.precision == PREC_FP16 ? DT_F16 : DT_BF16);
+  const int f16 = cfg_.precision == PREC_FP16 ? 1 : 0;
   auto buf = [&](int tensor) { return tensor >= 0 ? bufs_[tensor_buf_[tensor]] : nullptr; };
   size_t ev = 0;
   auto mark = [&]() {
@@ -600,10 +589,10 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     if (d.skip) { mark(); continue; }
     switch (o.kind) {
       case OpSpec::STEM:
-        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, st));
+        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, f16, st));
         break;
       case OpSpec::STEM_ALEX:
-        B2I_CUDA(launch_alex_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, st));
+        B2I_CUDA(launch_alex_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, f16, st));
         break;
       case OpSpec::NORMALIZE:
         B2I_CUDA(launch_normalize_u8(d_u8, buf(o.out), dt, static_cast<long long>(nb) * 224 * 224, st));
@@ -645,6 +634,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.resident_b = d.resident_b;
         a.flat = d.flat;
         a.msub = d.msub;
+        a.f16 = f16;
         if (d.fused_second >= 0) {
           const DevOp& s2 = ops_[d.fused_second];
           const int cpb = d.g.C >> 6;
@@ -735,7 +725,7 @@ bool DeviceModel::read_tensor(int id, int n, std::vector<float>* out, std::strin
   } else {
     std::vector<uint16_t> tmp(ne);
     B2I_CUDA(cudaMemcpy(tmp.data(), src, ne * 2, cudaMemcpyDeviceToHost));
-    for (size_t i = 0; i < ne; ++i) (*out)[i] = bf16_to_f32(tmp[i]);
+    for (size_t i = 0; i < ne; ++i) (*out)[i] = host_16_to_f32(tmp[i], cfg_.precision == PREC_FP16);
   }
   return true;
 }

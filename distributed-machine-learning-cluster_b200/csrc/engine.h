@@ -18,7 +18,7 @@
 
 namespace b2i {
 
-enum Precision : int { PREC_BF16 = 0, PREC_FP32 = 1 };
+enum Precision : int { PREC_BF16 = 0, PREC_FP32 = 1, PREC_FP16 = 2 };   // FP16: the tcgen05 path with IEEE-half tensors
 enum AlexGeom : int { ALEX_TCH = 0, ALEX_TORCHVISION = 1 };
 
 struct EngineConfig {

@@ -12,10 +12,7 @@ namespace {
 
 constexpr int kSMs = 148;
 
-__device__ __forceinline__ uint32_t pack2(float a, float b) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
-}
+__device__ __forceinline__ uint32_t pack2(float a, float b, int f16) { return pack16x2(a, b, f16); }
 
 // ------------------------------------------------------------------ normalise
 // tch: x.to_kind(Float) / 255.0, then (x - mean) / std.  True
@@ -26,7 +23,7 @@ __constant__ float kStd[3] = {0.229f, 0.224f, 0.225f};
 template <bool F32>
 __global__ void __launch_bounds__(256) normalize_u8_kernel(const uint8_t* __restrict__ in,
                                                             void* __restrict__ out,
-                                                            long long quads) {
+                                                            long long quads, int f16) {
   // one thread = 4 pixels = 12 input bytes (three aligned 32-bit loads)
   for (long long q = blockIdx.x * 256ll + threadIdx.x; q < quads; q += 256ll * gridDim.x) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(in) + q * 3;
@@ -50,8 +47,8 @@ __global__ void __launch_bounds__(256) normalize_u8_kernel(const uint8_t* __rest
       for (int p = 0; p < 4; ++p) o[p] = make_float4(v[3 * p], v[3 * p + 1], v[3 * p + 2], 0.f);
     } else {
       uint4* o = reinterpret_cast<uint4*>(out) + q * 2;
-      o[0] = make_uint4(pack2(v[0], v[1]), pack2(v[2], 0.f), pack2(v[3], v[4]), pack2(v[5], 0.f));
-      o[1] = make_uint4(pack2(v[6], v[7]), pack2(v[8], 0.f), pack2(v[9], v[10]), pack2(v[11], 0.f));
+      o[0] = make_uint4(pack2(v[0], v[1], f16), pack2(v[2], 0.f, f16), pack2(v[3], v[4], f16), pack2(v[5], 0.f, f16));
+      o[1] = make_uint4(pack2(v[6], v[7], f16), pack2(v[8], 0.f, f16), pack2(v[9], v[10], f16), pack2(v[11], 0.f, f16));
     }
   }
 }
@@ -62,7 +59,7 @@ template <bool F32>
 __global__ void __launch_bounds__(256) maxpool_kernel(const void* __restrict__ in,
                                                        void* __restrict__ out, int N, int H, int W,
                                                        int C, int k, int stride, int pad, int OH,
-                                                       int OW) {
+                                                       int OW, int f16) {
   const int vec = F32 ? 4 : 8;
   const int cv = C / vec;
   const long long total = static_cast<long long>(N) * OH * OW * cv;
@@ -102,8 +99,8 @@ __global__ void __launch_bounds__(256) maxpool_kernel(const void* __restrict__ i
         } else {
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            m[2 * e] = fmaxf(m[2 * e], __uint_as_float(u[e] << 16));
-            m[2 * e + 1] = fmaxf(m[2 * e + 1], __uint_as_float(u[e] & 0xFFFF0000u));
+            m[2 * e] = fmaxf(m[2 * e], lo16(u[e], f16));
+            m[2 * e + 1] = fmaxf(m[2 * e + 1], hi16(u[e], f16));
           }
         }
       }
@@ -125,8 +122,8 @@ __global__ void __launch_bounds__(256) maxpool_kernel(const void* __restrict__ i
           const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            m[2 * e] = fmaxf(m[2 * e], __uint_as_float(u[e] << 16));
-            m[2 * e + 1] = fmaxf(m[2 * e + 1], __uint_as_float(u[e] & 0xFFFF0000u));
+            m[2 * e] = fmaxf(m[2 * e], lo16(u[e], f16));
+            m[2 * e + 1] = fmaxf(m[2 * e + 1], hi16(u[e], f16));
           }
         }
       }
@@ -137,7 +134,7 @@ __global__ void __launch_bounds__(256) maxpool_kernel(const void* __restrict__ i
           make_float4(m[0], m[1], m[2], m[3]);
     } else {
       *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + ooff) =
-          make_uint4(pack2(m[0], m[1]), pack2(m[2], m[3]), pack2(m[4], m[5]), pack2(m[6], m[7]));
+          make_uint4(pack2(m[0], m[1], f16), pack2(m[2], m[3], f16), pack2(m[4], m[5], f16), pack2(m[6], m[7], f16));
     }
   }
 }
@@ -147,7 +144,7 @@ template <bool F32>
 __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(const void* __restrict__ in,
                                                                 void* __restrict__ out, int N,
                                                                 int H, int W, int C, int OH,
-                                                                int OW) {
+                                                                int OW, int f16) {
   const int vec = F32 ? 4 : 8;
   const int cv = C / vec;
   const long long total = static_cast<long long>(N) * OH * OW * cv;
@@ -173,8 +170,8 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(const void* __res
           const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            a[2 * e] += __uint_as_float(u[e] << 16);
-            a[2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+            a[2 * e] += lo16(u[e], f16);
+            a[2 * e + 1] += hi16(u[e], f16);
           }
         }
       }
@@ -187,7 +184,7 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(const void* __res
           make_float4(a[0], a[1], a[2], a[3]);
     } else {
       *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + ooff) =
-          make_uint4(pack2(a[0], a[1]), pack2(a[2], a[3]), pack2(a[4], a[5]), pack2(a[6], a[7]));
+          make_uint4(pack2(a[0], a[1], f16), pack2(a[2], a[3], f16), pack2(a[4], a[5], f16), pack2(a[6], a[7], f16));
     }
   }
 }
@@ -197,7 +194,7 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(const void* __res
 // shared memory.  The generic kernel above gives one thread all 49 pixels of a chunk (64 CTAs total).
 template <bool F32>
 __global__ void __launch_bounds__(256) global_avgpool_kernel(const void* __restrict__ in,
-                                                              void* __restrict__ out, int HW, int C) {
+                                                              void* __restrict__ out, int HW, int C, int f16) {
   constexpr int vec = F32 ? 4 : 8;
   __shared__ float part[256][8];
   const int cv = C / vec;
@@ -231,8 +228,8 @@ __global__ void __launch_bounds__(256) global_avgpool_kernel(const void* __restr
         } else {
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            a[2 * e] += __uint_as_float(u[e] << 16);
-            a[2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+            a[2 * e] += lo16(u[e], f16);
+            a[2 * e + 1] += hi16(u[e], f16);
           }
         }
       }
@@ -253,7 +250,7 @@ __global__ void __launch_bounds__(256) global_avgpool_kernel(const void* __restr
       *reinterpret_cast<float4*>(static_cast<float*>(out) + ooff) = make_float4(a[0], a[1], a[2], a[3]);
     } else {
       *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + ooff) =
-          make_uint4(pack2(a[0], a[1]), pack2(a[2], a[3]), pack2(a[4], a[5]), pack2(a[6], a[7]));
+          make_uint4(pack2(a[0], a[1], f16), pack2(a[2], a[3], f16), pack2(a[4], a[5], f16), pack2(a[6], a[7], f16));
     }
   }
 }
@@ -336,9 +333,9 @@ cudaError_t launch_normalize_u8(const uint8_t* in, void* out, int dtype, long lo
   if (pixels % 4) return cudaErrorInvalidValue;
   const long long quads = pixels / 4;
   if (dtype == DT_F32)
-    normalize_u8_kernel<true><<<grid_for(quads), 256, 0, st>>>(in, out, quads);
+    normalize_u8_kernel<true><<<grid_for(quads), 256, 0, st>>>(in, out, quads, 0);
   else
-    normalize_u8_kernel<false><<<grid_for(quads), 256, 0, st>>>(in, out, quads);
+    normalize_u8_kernel<false><<<grid_for(quads), 256, 0, st>>>(in, out, quads, dtype == DT_F16);
   return cudaGetLastError();
 }
 
@@ -348,9 +345,9 @@ cudaError_t launch_maxpool(const void* in, void* out, int dtype, int N, int H, i
   if (C % vec) return cudaErrorInvalidValue;
   const long long total = static_cast<long long>(N) * OH * OW * (C / vec);
   if (dtype == DT_F32)
-    maxpool_kernel<true><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, k, stride, pad, OH, OW);
+    maxpool_kernel<true><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, k, stride, pad, OH, OW, 0);
   else
-    maxpool_kernel<false><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, k, stride, pad, OH, OW);
+    maxpool_kernel<false><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, k, stride, pad, OH, OW, dtype == DT_F16);
   return cudaGetLastError();
 }
 
@@ -360,14 +357,14 @@ cudaError_t launch_adaptive_avgpool(const void* in, void* out, int dtype, int N,
   if (C % vec) return cudaErrorInvalidValue;
   const int cv = C / vec;
   if (OH == 1 && OW == 1 && cv <= 256 && 256 % cv == 0) {
-    if (dtype == DT_F32) return launch_pdl(global_avgpool_kernel<true>, dim3(N), dim3(256), 0, st, in, out, H * W, C);
-    return launch_pdl(global_avgpool_kernel<false>, dim3(N), dim3(256), 0, st, in, out, H * W, C);
+    if (dtype == DT_F32) return launch_pdl(global_avgpool_kernel<true>, dim3(N), dim3(256), 0, st, in, out, H * W, C, 0);
+    return launch_pdl(global_avgpool_kernel<false>, dim3(N), dim3(256), 0, st, in, out, H * W, C, static_cast<int>(dtype == DT_F16));
   }
   const long long total = static_cast<long long>(N) * OH * OW * (C / vec);
   if (dtype == DT_F32)
-    adaptive_avgpool_kernel<true><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, OH, OW);
+    adaptive_avgpool_kernel<true><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, OH, OW, 0);
   else
-    adaptive_avgpool_kernel<false><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, OH, OW);
+    adaptive_avgpool_kernel<false><<<grid_for(total), 256, 0, st>>>(in, out, N, H, W, C, OH, OW, dtype == DT_F16);
   return cudaGetLastError();
 }
 

@@ -6,7 +6,7 @@
 
 namespace b2i {
 
-enum DType : int { DT_BF16 = 0, DT_F32 = 1 };
+enum DType : int { DT_BF16 = 0, DT_F32 = 1, DT_F16 = 2 };   // DT_F16: same kernels as DT_BF16, IEEE half storage
 
 // u8 [N,224,224,3] (HWC, already resized + centre-cropped) -> NHWC4, (x/255 - mean)/std, pad
 // channel = 0.  Replaces the normalise half of tch imagenet::load_image_and_resize

@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -200,11 +201,12 @@ __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t saddr) {
   return d;
 }
 // Instruction descriptor: bf16 x bf16 -> fp32, both operands K-major, M x N tile.
-__host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N) {
+// f16 != 0: both operands IEEE half (format code 0) instead of bf16 (format code 1); same MMA rate.
+__host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N, int f16 = 0) {
   uint32_t d = 0;
   d |= 1u << 4;                               // D format fp32
-  d |= 1u << 7;                               // A format bf16
-  d |= 1u << 10;                              // B format bf16
+  d |= (f16 ? 0u : 1u) << 7;                  // A format
+  d |= (f16 ? 0u : 1u) << 10;                 // B format
   d |= static_cast<uint32_t>(N >> 3) << 17;   // N / 8
   d |= static_cast<uint32_t>(M >> 4) << 24;   // M / 16
   return d;
@@ -216,6 +218,41 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
+// The 16-bit storage format is a run-time property of a model (bf16, or IEEE half in the fp16 mode):
+// pack two floats / unpack the low / high half of a word in either.
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ uint32_t pack16x2(float lo, float hi, int f16) {
+  return f16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi);
+}
+__device__ __forceinline__ float lo16(uint32_t v, int f16) {
+  return f16 ? __half2float(__ushort_as_half(static_cast<unsigned short>(v & 0xFFFFu))) : bf16_lo(v);
+}
+__device__ __forceinline__ float hi16(uint32_t v, int f16) {
+  return f16 ? __half2float(__ushort_as_half(static_cast<unsigned short>(v >> 16))) : bf16_hi(v);
+}
+// Compile-time versions for the hot loops: the kernels branch ONCE on the format (a warp-uniform branch around
+// the whole loop), never per element.
+template <bool F16> __device__ __forceinline__ uint32_t pack16x2_t(float lo, float hi) {
+  if constexpr (F16) return pack_f16x2(lo, hi); else return pack_bf16x2(lo, hi);
+}
+template <bool F16> __device__ __forceinline__ float lo16_t(uint32_t v) {
+  if constexpr (F16) return __half2float(__ushort_as_half(static_cast<unsigned short>(v & 0xFFFFu))); else return bf16_lo(v);
+}
+template <bool F16> __device__ __forceinline__ float hi16_t(uint32_t v) {
+  if constexpr (F16) return __half2float(__ushort_as_half(static_cast<unsigned short>(v >> 16))); else return bf16_hi(v);
+}
+template <bool F16> __device__ __forceinline__ uint32_t max16x2_t(uint32_t a, uint32_t b) {
+  if constexpr (F16) {
+    const __half2 r = __hmax2(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&r);
+  } else {
+    const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&r);
+  }
+}
 
 // Host side of programmatic dependent launch: the kernel may start while its predecessor in the
 // stream is still running; it must call griddep_wait() before touching anything that predecessor

@@ -56,6 +56,7 @@ struct StemParams {
   __nv_bfloat16* out;
   float bias[64];      // folded BN bias, by value: the drain warps read it as constant-bank operands
   int total_tiles;  // N * 64
+  int f16;          // activations / weights are IEEE half instead of bf16
   unsigned int* sched;  // [0] tiles handed out beyond the first gridDim.x, [1] CTAs done; both zero between launches
 };
 
@@ -71,6 +72,7 @@ __device__ __forceinline__ uint64_t patch_desc(uint32_t saddr) {
   return d;                                                        // layout type 0: no swizzle
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(ST_THREADS, 2)
 stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   griddep_launch();
@@ -122,7 +124,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(b_smem + kb * 8192u, &tmW, w_full, kb * 64, 0);
     }
     mbar_wait(w_full, 0);
-    const uint32_t idesc = umma_idesc_bf16(128, 64);
+    const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
     for (int i = 0;; ++i) {
       const int b = i & 1;
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
@@ -219,8 +221,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
           const float r = fmaf(byte_f(1 + 3 * j), na[0], nb[0]);
           const float gg = fmaf(byte_f(2 + 3 * j), na[1], nb[1]);
           const float bl = fmaf(byte_f(3 + 3 * j), na[2], nb[2]);
-          o[2 * j] = ok ? pack_bf16x2(r, gg) : 0u;
-          o[2 * j + 1] = ok ? pack_bf16x2(bl, 0.f) : 0u;
+          o[2 * j] = ok ? pack16x2_t<F16>(r, gg) : 0u;
+          o[2 * j + 1] = ok ? pack16x2_t<F16>(bl, 0.f) : 0u;
         }
         // two 16-byte stores; odd groups of four lanes write their halves in the other order so that
         // each store instruction covers all 32 banks once per eight lanes
@@ -276,8 +278,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(__uint_as_float(v[g * 8 + e]) + p.bias[c * 32 + g * 8 + e], 0.f);
             const uint32_t chunk = static_cast<uint32_t>(c * 4 + g);
             asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_row + ((chunk ^ sw) << 4)),
-                         "r"(pack_bf16x2(f[0], f[1])), "r"(pack_bf16x2(f[2], f[3])),
-                         "r"(pack_bf16x2(f[4], f[5])), "r"(pack_bf16x2(f[6], f[7])) : "memory");
+                         "r"(pack16x2_t<F16>(f[0], f[1])), "r"(pack16x2_t<F16>(f[2], f[3])),
+                         "r"(pack16x2_t<F16>(f[4], f[5])), "r"(pack16x2_t<F16>(f[6], f[7])) : "memory");
           }
         }
       }
@@ -306,16 +308,16 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
             tap[dy * 3 + dx] = *reinterpret_cast<const uint4*>(stage_gen + row * 128u + ((ch ^ (row & 7u)) << 4));
           }
         }
-        __nv_bfloat162 mx[4];
+        // packed 16-bit max in the model's storage format
+        uint32_t mx[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          mx[e] = *reinterpret_cast<const __nv_bfloat162*>(&reinterpret_cast<const uint32_t*>(&tap[0])[e]);
+          mx[e] = reinterpret_cast<const uint32_t*>(&tap[0])[e];
 #pragma unroll
-          for (int k = 1; k < 9; ++k)
-            mx[e] = __hmax2(mx[e], *reinterpret_cast<const __nv_bfloat162*>(&reinterpret_cast<const uint32_t*>(&tap[k])[e]));
+          for (int k = 1; k < 9; ++k) mx[e] = max16x2_t<F16>(mx[e], reinterpret_cast<const uint32_t*>(&tap[k])[e]);
         }
         const int ph = pty * 7 + py, pw = ptx * 7 + px;
-        const uint32_t* mw = reinterpret_cast<const uint32_t*>(mx);
+        const uint32_t* mw = mx;
         *reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + ch * 8) =
             make_uint4(mw[0], mw[1], mw[2], mw[3]);
       }
@@ -352,14 +354,16 @@ cudaError_t stem_cta_read(long long* host) { return cudaMemcpyFromSymbol(host, g
 #endif
 
 cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                        const float* bias_host, int n_images, unsigned int* sched, cudaStream_t st) {
+                        const float* bias_host, int n_images, unsigned int* sched, int f16, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEM_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(stem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, STEM_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(stem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, STEM_SMEM);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
@@ -373,8 +377,10 @@ cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap*
   for (int c = 0; c < 64; ++c) p.bias[c] = bias_host[c];
   p.total_tiles = n_images * 64;
   p.sched = sched;
+  p.f16 = f16;
   const int grid = p.total_tiles < 2 * sm_count[dev] ? p.total_tiles : 2 * sm_count[dev];
-  return launch_pdl(stem_kernel, dim3(grid), dim3(ST_THREADS), STEM_SMEM, st, *tmW, p);
+  if (f16) return launch_pdl(stem_kernel<true>, dim3(grid), dim3(ST_THREADS), STEM_SMEM, st, *tmW, p);
+  return launch_pdl(stem_kernel<false>, dim3(grid), dim3(ST_THREADS), STEM_SMEM, st, *tmW, p);
 }
 
 }  // namespace b2i

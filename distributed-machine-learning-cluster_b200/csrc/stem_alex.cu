@@ -44,6 +44,7 @@ struct AlexStemParams {
   __nv_bfloat16* out;
   float bias[64];
   int total_tiles;  // N * 28
+  int f16;          // activations / weights are IEEE half instead of bf16
 };
 
 __device__ __forceinline__ uint64_t plane_desc(uint32_t saddr) {
@@ -55,6 +56,7 @@ __device__ __forceinline__ uint64_t plane_desc(uint32_t saddr) {
   return d;                                                       // layout type 0: no swizzle
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(AS_THREADS, 1)
 alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p) {
   griddep_launch();
@@ -100,7 +102,7 @@ alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p
   if (warp == 8) {
     // ------------------------------------------------------------------ MMA issue
     mbar_wait(w_full, 0);
-    const uint32_t idesc = umma_idesc_bf16(128, 64);
+    const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
     int i = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
@@ -178,8 +180,8 @@ alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p
             const float r = fmaf(byte_f(2 + 3 * j), na[0], nb[0]);
             const float gg = fmaf(byte_f(3 + 3 * j), na[1], nb[1]);
             const float bl = fmaf(byte_f(4 + 3 * j), na[2], nb[2]);
-            rg[j] = ok ? pack_bf16x2(r, gg) : 0u;
-            bz[j] = ok ? pack_bf16x2(bl, 0.f) : 0u;
+            rg[j] = ok ? pack16x2_t<F16>(r, gg) : 0u;
+            bz[j] = ok ? pack16x2_t<F16>(bl, 0.f) : 0u;
           }
           const uint32_t off = static_cast<uint32_t>(py) * AP_ROW_BYTES + static_cast<uint32_t>(g) * 16u;
           *reinterpret_cast<uint4*>(dst + off) = make_uint4(rg[0], rg[1], rg[2], rg[3]);
@@ -218,7 +220,7 @@ alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p
             const int c = h2 * 16 + 2 * e;
             const float f0 = fmaxf(__uint_as_float(v[c]) + p.bias[half * 32 + c], 0.f);
             const float f1 = fmaxf(__uint_as_float(v[c + 1]) + p.bias[half * 32 + c + 1], 0.f);
-            ov[e] = pack_bf16x2(f0, f1);
+            ov[e] = pack16x2_t<F16>(f0, f1);
           }
           stg256(o + h2 * 16, ov);
         }
@@ -237,14 +239,16 @@ alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p
 }  // namespace
 
 cudaError_t launch_alex_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap* tmW,
-                             const float* bias_host, int n_images, cudaStream_t st) {
+                             const float* bias_host, int n_images, int f16, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(alex_stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AS_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(alex_stem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AS_SMEM);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(alex_stem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AS_SMEM);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
@@ -257,8 +261,10 @@ cudaError_t launch_alex_stem(const uint8_t* in_u8, void* out_bf16, const CUtenso
   p.out = static_cast<__nv_bfloat16*>(out_bf16);
   for (int c = 0; c < 64; ++c) p.bias[c] = bias_host[c];
   p.total_tiles = n_images * TILES_X * TILES_Y;
+  p.f16 = f16;
   const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
-  return launch_pdl(alex_stem_kernel, dim3(grid), dim3(AS_THREADS), AS_SMEM, st, *tmW, p);
+  if (f16) return launch_pdl(alex_stem_kernel<true>, dim3(grid), dim3(AS_THREADS), AS_SMEM, st, *tmW, p);
+  return launch_pdl(alex_stem_kernel<false>, dim3(grid), dim3(AS_THREADS), AS_SMEM, st, *tmW, p);
 }
 
 }  // namespace b2i

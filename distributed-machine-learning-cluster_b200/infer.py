@@ -5,7 +5,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from ._lib import (ALEXNET_TCH, ALEXNET_TORCHVISION, CLASSES, IMAGE_BYTES, PREC_BF16, PREC_FP32, B2IError,
+from ._lib import (ALEXNET_TCH, ALEXNET_TORCHVISION, CLASSES, IMAGE_BYTES, PREC_BF16, PREC_FP16, PREC_FP32, B2IError,
                    ModelConfig, check)
 
 

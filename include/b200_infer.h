@@ -29,6 +29,8 @@ extern "C" {
 
 #define B2I_PREC_BF16 0 /* tcgen05 bf16 in, fp32 accumulate; logits within 2e-2 of the fp32 reference */
 #define B2I_PREC_FP32 1 /* FFMA fp32; logits within 1e-4 */
+#define B2I_PREC_FP16 2 /* the tcgen05 path with IEEE-half activations and weights (fp32 accumulate): same speed as
+                          bf16, three more mantissa bits; logits within 2e-2 of the fp32 reference outright */
 
 #define B2I_ALEXNET_TCH 0         /* features.3 = k5 pad1 stride2, as tch 0.4.1 builds it */
 #define B2I_ALEXNET_TORCHVISION 1 /* features.3 = k5 pad2 stride1 */

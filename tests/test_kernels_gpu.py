@@ -13,12 +13,20 @@ import torch.nn.functional as F
 
 pytestmark = pytest.mark.gpu
 
-BF16, FP32 = 0, 1
+BF16, FP32, FP16 = 0, 1, 2
 GATHER, IM2COL = 0, 1
 
 
 def bf16_round(a):
     return torch.as_tensor(np.asarray(a, dtype=np.float32)).to(torch.bfloat16).to(torch.float32)
+
+
+def fp16_round(a):
+    return torch.as_tensor(np.asarray(a, dtype=np.float32)).to(torch.float16).to(torch.float32)
+
+
+def round16(a, precision):
+    return fp16_round(a) if precision == FP16 else bf16_round(a)
 
 
 def rnd(shape, seed, scale=1.0):
@@ -55,8 +63,8 @@ def conv_case(ctx, N, H, W, C, Cout, k, stride, pad, *, precision, conv_mode, we
                torch.randn(Cout, generator=g) * 0.1, torch.rand(Cout, generator=g) + 0.5)
     OH, OW = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
     res = rnd((N, OH, OW, Cout), seed + 4) if residual else None
-    if precision == BF16:
-        x, res = bf16_round(x), (bf16_round(res) if residual else None)
+    if precision != FP32:
+        x, res = round16(x, precision), (round16(res, precision) if residual else None)
     got = ctx.conv2d(x.numpy(), w.numpy(), bias=None if b is None else b.numpy(),
                      bn=None if bnp is None else [t.numpy() for t in bnp], stride=stride, pad=pad,
                      residual=None if res is None else res.numpy(), relu=relu, precision=precision,
@@ -68,8 +76,8 @@ def conv_case(ctx, N, H, W, C, Cout, k, stride, pad, *, precision, conv_mode, we
         inv = 1.0 / torch.sqrt(var.double() + 1e-5)
         wf = w * (gamma.double() * inv).float().view(-1, 1, 1, 1)
         shift = (beta.double() - mean.double() * gamma.double() * inv + shift.double() * gamma.double() * inv * (1 if b is not None else 0)).float()
-    if precision == BF16:
-        wf = bf16_round(wf)
+    if precision != FP32:
+        wf = round16(wf, precision)
     ref = F.conv2d(x.permute(0, 3, 1, 2).double(), wf.double(), shift.double(), stride, pad).permute(0, 2, 3, 1)
     if res is not None:
         ref = ref + res.double()
@@ -78,6 +86,8 @@ def conv_case(ctx, N, H, W, C, Cout, k, stride, pad, *, precision, conv_mode, we
     scale = float(ref.abs().max())
     if precision == BF16:
         report(got, ref.numpy(), 2.0 ** -7, 1e-3 * scale, "conv bf16")
+    elif precision == FP16:   # one rounding to half (relative 2^-11) after fp32 accumulation
+        report(got, ref.numpy(), 2.0 ** -10, 2e-4 * scale, "conv fp16")
     else:
         report(got, ref.numpy(), 0.0, 1e-5 * scale, "conv fp32")
 
@@ -156,6 +166,18 @@ def test_conv_pair_multi_subtile(ctx):
     conv_case(ctx, 2, 14, 14, 256, 256, 3, 1, 1, precision=BF16, conv_mode=8, tile_n=128, bias=True, seed=323)
 
 
+def test_conv_fp16_storage_mode(ctx):
+    """PREC_FP16: the same tcgen05 kernels with IEEE-half activations / weights (instruction descriptor formats,
+    epilogue pack / unpack, residual): every kernel family once, against fp32 math on half-rounded inputs."""
+    conv_case(ctx, 3, 56, 56, 64, 64, 3, 1, 1, precision=FP16, conv_mode=3, bn=True, residual=True, relu=True, seed=400)      # halo patch
+    conv_case(ctx, 5, 28, 28, 128, 128, 3, 1, 1, precision=FP16, conv_mode=6, bn=True, residual=True, relu=True, seed=401)   # flattened rows
+    conv_case(ctx, 3, 56, 56, 64, 128, 3, 2, 1, precision=FP16, conv_mode=7, bn=True, relu=True, seed=402)                  # pair, resident weights
+    conv_case(ctx, 9, 7, 7, 512, 512, 3, 1, 1, precision=FP16, conv_mode=8, tile_n=256, bn=True, residual=True, relu=True, seed=403)   # pair, two sub-tiles
+    conv_case(ctx, 3, 14, 14, 256, 256, 3, 1, 1, precision=FP16, conv_mode=IM2COL, bias=True, seed=404)                     # persistent im2col
+    conv_case(ctx, 2, 12, 12, 64, 64, 3, 1, 1, precision=FP16, conv_mode=GATHER, bn=True, relu=True, seed=405)              # one-tile gather
+    conv_case(ctx, 2, 67, 67, 3, 64, 11, 4, 2, precision=FP16, conv_mode=GATHER, bias=True, relu=True, seed=406)            # small-channel gather
+
+
 def test_conv_pair_resident_weights(ctx):
     """CTA-pair im2col kernel keeping all weight k-blocks resident (conv_mode 7): the stride-2 first conv of
     ResNet layer2, a 1x1, and a layer whose weights do not fit (falls back to streaming them)."""
@@ -182,6 +204,16 @@ def test_linear_tiled_bf16(ctx):
         report(got, ref, 0.0, 2e-5 * np.abs(ref).max() + 1e-6, "linear bf16 (fp32 out)")
 
 
+def test_linear_tiled_fp16(ctx):
+    for (M, K, Cout, seed) in [(5, 512, 1000, 83), (300, 1024, 4096, 84)]:
+        x = fp16_round(rnd((M, K), seed))
+        w = rnd((Cout, K), seed + 1, (1.0 / K) ** 0.5)
+        b = rnd((Cout,), seed + 2, 0.1)
+        got = ctx.linear(x.numpy(), w.numpy(), b.numpy(), relu=False, precision=FP16)
+        ref = (x.double() @ fp16_round(w).double().T + b.double()).numpy()
+        report(got, ref, 0.0, 2e-5 * np.abs(ref).max() + 1e-6, "linear fp16 (fp32 out)")
+
+
 def test_conv_and_linear_fp32_mode(ctx):
     conv_case(ctx, 2, 20, 20, 64, 128, 3, 1, 1, precision=FP32, conv_mode=GATHER, bn=True, residual=True, relu=True, seed=90)
     conv_case(ctx, 2, 33, 33, 3, 64, 7, 2, 3, precision=FP32, conv_mode=GATHER, bn=True, relu=True, seed=91)
@@ -193,28 +225,30 @@ def test_conv_and_linear_fp32_mode(ctx):
 
 
 # ---- bandwidth kernels --------------------------------------------------------------------
-@pytest.mark.parametrize("precision", [BF16, FP32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("precision", [BF16, FP32, FP16], ids=["bf16", "fp32", "fp16"])
 def test_maxpool(ctx, precision):
     for (N, H, W, C, k, s, p, seed) in [(2, 112, 112, 64, 3, 2, 1, 100), (3, 55, 55, 64, 3, 2, 0, 101), (2, 13, 13, 192, 3, 2, 0, 102),
                                         (1, 6, 6, 256, 3, 2, 0, 103)]:
         x = rnd((N, H, W, C), seed)
-        if precision == BF16:
-            x = bf16_round(x)
+        if precision != FP32:
+            x = round16(x, precision)
         got = ctx.maxpool(x.numpy(), k, s, p, precision=precision)
         ref = F.max_pool2d(x.permute(0, 3, 1, 2), k, s, p).permute(0, 2, 3, 1).numpy()
         assert np.array_equal(got, ref)  # max of representable values: exact in both dtypes
 
 
-@pytest.mark.parametrize("precision", [BF16, FP32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("precision", [BF16, FP32, FP16], ids=["bf16", "fp32", "fp16"])
 def test_adaptive_avgpool(ctx, precision):
     for (N, H, W, C, oh, ow, seed) in [(4, 7, 7, 512, 1, 1, 110), (3, 2, 2, 256, 6, 6, 111), (2, 6, 6, 256, 6, 6, 112), (2, 13, 13, 256, 6, 6, 113)]:
         x = rnd((N, H, W, C), seed)
-        if precision == BF16:
-            x = bf16_round(x)
+        if precision != FP32:
+            x = round16(x, precision)
         got = ctx.adaptive_avgpool(x.numpy(), oh, ow, precision=precision)
         ref = F.adaptive_avg_pool2d(x.permute(0, 3, 1, 2).double(), (oh, ow)).permute(0, 2, 3, 1).numpy()
         if precision == BF16:
             report(got, ref, 2.0 ** -8, 1e-6, "avgpool bf16")
+        elif precision == FP16:
+            report(got, ref, 2.0 ** -11, 1e-6, "avgpool fp16")
         else:
             report(got, ref, 0.0, 2e-6, "avgpool fp32")
 
@@ -228,6 +262,8 @@ def test_normalize(ctx):
     assert np.abs(got[..., :3] - ref).max() <= 2.4e-7 * 3  # same IEEE ops; torch may fuse the broadcast differently by 1 ulp
     gotb = ctx.normalize(img, precision=BF16)
     assert np.array_equal(gotb[..., :3], bf16_round(got[..., :3]).numpy())
+    goth = ctx.normalize(img, precision=FP16)
+    assert np.array_equal(goth[..., :3], fp16_round(got[..., :3]).numpy())
 
 
 def test_softmax_topk(ctx):

@@ -26,7 +26,7 @@ int main() {
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   for (int rep = 0; rep < 200; ++rep) {
     cudaEventRecord(e0);
-    cudaError_t e = launch_stem(d_in, d_out, &tm, h_bias, N, d_sched, 0);
+    cudaError_t e = launch_stem(d_in, d_out, &tm, h_bias, N, d_sched, /*f16=*/0, 0);
     cudaEventRecord(e1);
     cudaError_t s = cudaDeviceSynchronize();
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
