@@ -14,6 +14,8 @@ bf16 mode, two separate statements:
       distance of that bf16 evaluation itself (measured here 2.2-2.4 % of the logit std, the same
       2-4 % SURVEY.md Appendix E found for torch's own bf16 CPU path).  A flat 2e-2 against the fp32
       oracle is not reachable with bf16 activations at these logit scales; DESIGN.md says so.
+fp16 mode (PREC_FP16, the same tensor-core kernels with IEEE-half storage): against the FP32 oracle,
+2e-2 units, outright -- no dtype allowance (measured 0.24 % of the logit std).
 Top-5 indices must be identical wherever the oracle's margin between neighbouring ranks exceeds
 twice the logit tolerance."""
 import os
