@@ -25,6 +25,7 @@ pub struct b2i_model_config {
 pub const B2I_OK: c_int = 0;
 pub const B2I_PREC_BF16: c_int = 0;
 pub const B2I_PREC_FP32: c_int = 1;
+pub const B2I_PREC_FP16: c_int = 2;
 pub const B2I_IMAGE_BYTES: usize = 224 * 224 * 3;
 pub const B2I_CLASSES: usize = 1000;
 
