@@ -52,6 +52,7 @@ struct ConvArgs {
   int ldo2 = 0, relu2 = 0, kb_first2 = 0, num_kb2 = 0;
   int pair = 0;                   // TMA modes: CTA-pair kernel (cta_group::2); tmB must be built with BN/2 box rows
   int resident_b = 0;             // pair kernel: keep all weight k-blocks in shared memory when they fit (one N-tile)
+  int reverse = 0;                // halo-patch / pair / flattened-row kernels: walk the tiles from the last to the first
   int f16 = 0;                    // tcgen05 path: 16-bit tensors (activations, weights) are IEEE half instead of bf16
   int msub = 1;                   // pair im2col kernel: 2 = two 128-row sub-tiles per CTA; tmA must then be a 256-pixel im2col map
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output

@@ -47,6 +47,7 @@ struct KP {
   int resb;   // pair kernel: this CTA's half of ALL weight k-blocks stays resident in shared memory
   int msub;   // pair kernel: 128-row sub-tiles per CTA (1 or 2)
   int f16;    // 16-bit tensors are IEEE half instead of bf16
+  int rev;    // pair kernel: walk the tiles from the last to the first
 };
 
 // Where one tile's results go.
@@ -685,7 +686,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
       const int ohw = p.OH * p.OW;
       int s = 0, ph = 0;
-      for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+      for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters) {
+        const int t = p.rev ? total_tiles - 1 - t0 : t0;   // snake order: start with what the producer wrote last
         const int tm = t / tn_all;
         const int nn = t - tm * tn_all;
         const bool second = nn >= p.tiles_n;
@@ -734,7 +736,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const uint32_t idesc = umma_idesc_bf16(256, p.BN, F16 ? 1 : 0);
       if (resb) mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
-      for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
+      for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters, ++i) {
+        const int t = p.rev ? total_tiles - 1 - t0 : t0;
         const int buf = acc2 ? (i & 1) : 0;
         const int use = acc2 ? (i >> 1) : i;          // how often this accumulator buffer has been used before
         mbar_wait(acc_empty_bar(buf), (use & 1) ^ 1);
@@ -770,7 +773,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int n_chunks = p.BN >> 5;
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
     int i = 0;
-    for (int t = cluster_id; t < total_tiles; t += num_clusters, ++i) {
+    for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters, ++i) {
+      const int t = p.rev ? total_tiles - 1 - t0 : t0;
       const int buf = acc2 ? (i & 1) : 0;
       const int use = acc2 ? (i >> 1) : i;
       const int tm = t / tn_all;
@@ -849,7 +853,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 struct FlatP {
   int H, W, N, slices, BN, pitch, rpt, box_w;   // rpt = rows per 128-position tile
   int rows_total, total_pairs, nbuf;
-  int ldo, relu, Cout, f16;
+  int ldo, relu, Cout, f16, rev;
   uint32_t tmem_cols;
   const float* bias;
   const __nv_bfloat16* residual;
@@ -936,7 +940,8 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   if (warp == 0) {
     if (lane == 0) {
       int s = 0, ph = 0;
-      for (int t = cluster_id; t < p.total_pairs; t += num_clusters) {
+      for (int t0 = cluster_id; t0 < p.total_pairs; t0 += num_clusters) {
+        const int t = p.rev ? p.total_pairs - 1 - t0 : t0;
         const int y0 = (2 * t + static_cast<int>(rank)) * p.rpt - 1;   // first patch row (one above the tile)
         for (int sl = 0; sl < p.slices; ++sl) {
           mbar_wait(empty_bar(s), ph ^ 1);
@@ -958,7 +963,8 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       const uint32_t idesc = umma_idesc_bf16(256, p.BN, F16 ? 1 : 0);
       mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
-      for (int t = cluster_id; t < p.total_pairs; t += num_clusters, ++i) {
+      for (int t0 = cluster_id; t0 < p.total_pairs; t0 += num_clusters, ++i) {
+        const int t = p.rev ? p.total_pairs - 1 - t0 : t0;
         const int buf = i & 1;
         mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -989,7 +995,8 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     Epi epi;
     epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
     int i = 0;
-    for (int t = cluster_id; t < p.total_pairs; t += num_clusters, ++i) {
+    for (int t0 = cluster_id; t0 < p.total_pairs; t0 += num_clusters, ++i) {
+      const int t = p.rev ? p.total_pairs - 1 - t0 : t0;
       const int buf = i & 1;
       const int pos = q * 32 + lane;                                  // position inside this CTA's tile
       const int Y = (2 * t + static_cast<int>(rank)) * p.rpt + pos / p.pitch;
@@ -1050,7 +1057,7 @@ constexpr uint32_t PT_WBYTES = 9 * 64 * 128;                                // r
 constexpr int PT_BUFS = 3;   // patches (+ residual tiles) in flight
 
 struct PatchP {
-  int N, H, W, tiles_w, tiles_h, total_tiles, relu, f16;
+  int N, H, W, tiles_w, tiles_h, total_tiles, relu, f16, rev;
   const float* bias;
   const __nv_bfloat16* residual;
   __nv_bfloat16* out;
@@ -1140,8 +1147,9 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
         const int pb = i % PT_BUFS;
         const uint32_t par = ((i / PT_BUFS) & 1) ^ 1;
-        const int n = t / tiles_per_img;
-        const int rem = t - n * tiles_per_img;
+        const int tt = p.rev ? p.total_tiles - 1 - t : t;   // snake order: start with what the producer wrote last
+        const int n = tt / tiles_per_img;
+        const int rem = tt - n * tiles_per_img;
         const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
         mbar_wait(patch_empty(pb), par);
         if (has_res) mbar_wait(res_empty(pb), par);
@@ -1195,8 +1203,9 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
       const int pbuf = i % PT_BUFS;
-      const int n = t / tiles_per_img;
-      const int rem = t - n * tiles_per_img;
+      const int tt = p.rev ? p.total_tiles - 1 - t : t;
+      const int n = tt / tiles_per_img;
+      const int rem = tt - n * tiles_per_img;
       const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
       mbar_wait(acc_full(b), (i >> 1) & 1);
       tc_fence_after();
@@ -1290,6 +1299,7 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->resb = 0;
   p->msub = 1;
   p->f16 = a.f16;
+  p->rev = a.reverse;
 }
 
 template <int AMODE, bool F16>
@@ -1387,6 +1397,7 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   p.total_tiles = g.N * p.tiles_w * p.tiles_h;
   p.relu = a.relu;
   p.f16 = a.f16;
+  p.rev = a.reverse;
   p.bias = a.bias;
   p.residual = static_cast<const __nv_bfloat16*>(a.residual);
   p.out = static_cast<__nv_bfloat16*>(a.out);
@@ -1419,7 +1430,7 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   const size_t resb = static_cast<size_t>(9) * p.slices * (a.BN / 2) * 128;
   const size_t patch = static_cast<size_t>(p.rpt + 2) * p.pitch * 128 + 1024;
   p.nbuf = static_cast<int>(std::min<size_t>(FLAT_MAXBUF, (226 * 1024 - 1024 - resb) / patch));
-  p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout; p.f16 = a.f16;
+  p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout; p.f16 = a.f16; p.rev = a.reverse;
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
   p.tmem_cols = cols;

@@ -584,6 +584,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     if (prof_events_ && ev < prof_events_->size()) cudaEventRecord((*prof_events_)[ev++], st);
   };
   mark();
+  int patch_seq = 0;   // the stem writes ascending, so the first halo-patch conv walks descending, the next ascending, ...
   for (DevOp& d : ops_) {
     const OpSpec& o = d.spec;
     if (d.skip) { mark(); continue; }
@@ -634,6 +635,10 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.resident_b = d.resident_b;
         a.flat = d.flat;
         a.msub = d.msub;
+        // Snake order through the conv layers: a kernel starts with the tiles its producer wrote last, which are the
+        // ones still in L2 (a layer1 tensor is 103 MB at batch 256, L2 holds 126 MB).  B2I_NO_SNAKE=1: off.
+        static const bool snake = [] { const char* e = getenv("B2I_NO_SNAKE"); return !(e && e[0] == '1'); }();
+        a.reverse = (snake && (d.patch || d.flat || d.pair) && !o.fc) ? (patch_seq++ & 1) ^ 1 : 0;
         a.f16 = f16;
         if (d.fused_second >= 0) {
           const DevOp& s2 = ops_[d.fused_second];
