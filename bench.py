@@ -28,7 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BATCH = 256
-NCU_DRAM_BYTES_PER_CONV_LAUNCH = 97491001   # see roofline["traffic"] below
+NCU_DRAM_BYTES_PER_CONV_LAUNCH = 97420146   # see roofline["traffic"] below
 K_TOP = 5
 MODEL = "resnet18"
 WORKLOAD = "ResNet-18 (resnet18.ot layout, seeded synthetic weights) synthetic 224x224 u8, batch 256 per GPU, bf16"
