@@ -8,7 +8,7 @@ from . import _lib
 from ._lib import B2IError, LIB_PATH
 from .infer import (ALEXNET_TCH, ALEXNET_TORCHVISION, CLASSES, IMAGE_BYTES, PREC_BF16, PREC_FP16, PREC_FP32, Context, Model,
                     PinnedBuffer, device_count, ot_inspect, ot_read_tensor, resize_plan, resize_target)
-from .service import (Job, Leader, MemberState, assign_members, decode_image, jobs_report, load_labels, load_model,
+from .service import (MISSING, SKIPPED, UNDECODABLE, Job, Leader, MemberState, assign_members, decode_bytes, decode_image, jobs_report, load_labels, load_model,
                       predict_image, sample_predict)
 
 _lib.lib()  # fail at import time if the extension is missing

@@ -7,7 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # B2I_LIB: another build of the same library (A/B timing of two builds inside one GPU session)
 LIB_PATH = os.environ.get("B2I_LIB") or os.path.join(_HERE, "libb200infer.so")
 
-OK, EINVAL, EIO, ECUDA, ENODEV, ENOMEM = 0, -1, -2, -3, -4, -5
+OK, EINVAL, EIO, ECUDA, ENODEV, ENOMEM, EINTERNAL, EDECODE = 0, -1, -2, -3, -4, -5, -6, -7
 PREC_BF16, PREC_FP32, PREC_FP16 = 0, 1, 2
 ALEXNET_TCH, ALEXNET_TORCHVISION = 0, 1
 IMAGE_BYTES = 224 * 224 * 3
@@ -61,6 +61,10 @@ SIGNATURES = {
     "b2i_predict_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2i_predict_u8_on": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "b2i_predict_raw_u8": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "b2i_predict_raw_u8_status": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "b2i_predict_jpeg": (_i, [_vp, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "b2i_jpeg_decode_u8": (_i, [_vp, _i, _vp, _sz, _vp, _sz, _ip, _ip]),
+    "b2i_jpeg_backend": (_i, [_vp, _i, _c.c_char_p, _sz]),
     "b2i_submit_u8": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _c.POINTER(_ll)]),
     "b2i_wait": (_i, [_vp, _ll]),
     "b2i_forward_device": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),

@@ -3,6 +3,7 @@
 // carry a `<stem>/` prefix, archives may or may not be ZIP64.
 #include "ot_reader.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -58,12 +59,14 @@ bool zip_index(const Blob& b, std::map<std::string, ZipEntry>* idx, std::string*
   uint64_t cd_off = rd32(&v[eocd + 16]);
   if (eocd >= 20 && rd32(&v[eocd - 20]) == 0x07064b50u) {  // ZIP64 locator
     const uint64_t e64 = rd64(&v[eocd - 20 + 8]);
-    if (e64 + 56 > n || rd32(&v[e64]) != 0x06064b50u) { *err = "bad zip64 end record"; return false; }
+    if (e64 > n || n - e64 < 56 || rd32(&v[e64]) != 0x06064b50u) { *err = "bad zip64 end record"; return false; }
     count = rd64(&v[e64 + 32]);
     cd_size = rd64(&v[e64 + 40]);
     cd_off = rd64(&v[e64 + 48]);
   }
-  if (cd_off + cd_size > n) { *err = "zip central directory out of range"; return false; }
+  // every range check below is written as "size > n || offset > n - size": the 64-bit fields come from the
+  // file and a sum of two of them can wrap
+  if (cd_size > n || cd_off > n - cd_size) { *err = "zip central directory out of range"; return false; }
   size_t p = static_cast<size_t>(cd_off);
   for (uint64_t i = 0; i < count; ++i) {
     if (p + 46 > n || rd32(&v[p]) != 0x02014b50u) { *err = "bad zip central directory entry"; return false; }
@@ -80,21 +83,25 @@ bool zip_index(const Blob& b, std::map<std::string, ZipEntry>* idx, std::string*
     while (x + 4 <= xend) {
       const uint16_t id = rd16(&v[x]);
       const uint16_t sz = rd16(&v[x + 2]);
+      const size_t rend = std::min(x + 4 + static_cast<size_t>(sz), xend);   // a record never reaches past the extra field
       if (id == 0x0001) {
         size_t q = x + 4;
-        if (usize == 0xFFFFFFFFu && q + 8 <= x + 4 + sz) { usize = rd64(&v[q]); q += 8; }
-        if (csize == 0xFFFFFFFFu && q + 8 <= x + 4 + sz) { csize = rd64(&v[q]); q += 8; }
-        if (lho == 0xFFFFFFFFu && q + 8 <= x + 4 + sz) { lho = rd64(&v[q]); q += 8; }
+        if (usize == 0xFFFFFFFFu && q + 8 <= rend) { usize = rd64(&v[q]); q += 8; }
+        if (csize == 0xFFFFFFFFu && q + 8 <= rend) { csize = rd64(&v[q]); q += 8; }
+        if (lho == 0xFFFFFFFFu && q + 8 <= rend) { lho = rd64(&v[q]); q += 8; }
       }
-      x += 4 + sz;
+      x += 4 + static_cast<size_t>(sz);
     }
-    if (lho + 30 > n || rd32(&v[lho]) != 0x04034b50u) { *err = "bad zip local header for " + name; return false; }
+    if (lho > n || n - lho < 30 || rd32(&v[lho]) != 0x04034b50u) { *err = "bad zip local header for " + name; return false; }
     const size_t lnlen = rd16(&v[lho + 26]), lelen = rd16(&v[lho + 28]);
+    if (n - lho < 30 + lnlen + lelen) { *err = "zip local header overruns file for " + name; return false; }
     ZipEntry e;
     e.offset = lho + 30 + lnlen + lelen;
     e.size = usize;
     e.method = method;
-    if (method == 0 && e.offset + e.size > n) { *err = "zip payload out of range for " + name; return false; }
+    // the stored size of a payload is its compressed size; for STORED entries the two agree
+    const uint64_t stored = method == 0 ? usize : csize;
+    if (stored > n || e.offset > n - stored) { *err = "zip payload out of range for " + name; return false; }
     (*idx)[name] = e;
     p += 46 + nlen + elen + clen;
   }
@@ -356,9 +363,9 @@ float load_elem(const uint8_t* base, const std::string& st, int64_t i) {
   float f; std::memcpy(&f, &b, 4); return f;
 }
 
-void collect(const VP& v, const std::string& prefix, std::vector<std::pair<std::string, VP>>* out) {
-  if (!v) return;
-  if (v->kind == Val::OBJECT) { collect(v->state, prefix, out); return; }
+void collect(const VP& v, const std::string& prefix, std::vector<std::pair<std::string, VP>>* out, int depth = 0) {
+  if (!v || depth > 64) return;   // module trees are a few levels deep; a crafted archive must not recurse without bound
+  if (v->kind == Val::OBJECT) { collect(v->state, prefix, out, depth + 1); return; }
   if (v->kind == Val::DICT) {
     for (size_t i = 0; i + 1 < v->items.size(); i += 2) {
       const VP& k = v->items[i];
@@ -366,7 +373,7 @@ void collect(const VP& v, const std::string& prefix, std::vector<std::pair<std::
       if (k->kind != Val::STR) continue;
       const std::string name = prefix.empty() ? k->s : prefix + "." + k->s;
       if (val->kind == Val::TENSOR) out->emplace_back(name, val);
-      else if (val->kind == Val::DICT || val->kind == Val::OBJECT) collect(val, name, out);
+      else if (val->kind == Val::DICT || val->kind == Val::OBJECT) collect(val, name, out, depth + 1);
     }
   }
 }
@@ -415,15 +422,29 @@ bool read_ot_archive(const std::string& path, std::map<std::string, HostTensor>*
     const int64_t avail = static_cast<int64_t>(it->second.size / esz);
     HostTensor h;
     h.shape = t->sizes;
-    const int64_t numel = h.numel();
-    for (int64_t d : h.shape) if (d < 0) { *err = "negative dimension in " + nt.first; return false; }
-    // bound check of the strided view
-    int64_t max_index = t->offset;
-    for (size_t d = 0; d < h.shape.size(); ++d) {
-      if (t->strides[d] < 0) { *err = "negative stride in " + nt.first; return false; }
-      if (h.shape[d] > 0) max_index += (h.shape[d] - 1) * t->strides[d];
+    // sizes, strides and the offset come from the file: every product / sum is checked against `avail`
+    // (at most the file size) before it is formed, so nothing here can wrap
+    int64_t numel = 1;
+    bool empty = false;
+    for (int64_t d : h.shape) {
+      if (d < 0) { *err = "negative dimension in " + nt.first; return false; }
+      if (d == 0) empty = true;
     }
-    if (numel > 0 && (t->offset < 0 || max_index >= avail)) { *err = "tensor view exceeds its storage: " + nt.first; return false; }
+    if (empty) numel = 0;
+    else
+      for (int64_t d : h.shape) {
+        if (numel > avail / d) { *err = "tensor larger than its storage: " + nt.first; return false; }
+        numel *= d;
+      }
+    if (t->offset < 0 || t->offset > avail) { *err = "tensor view exceeds its storage: " + nt.first; return false; }
+    int64_t max_index = t->offset;
+    for (size_t d = 0; d < h.shape.size() && !empty; ++d) {
+      if (t->strides[d] < 0) { *err = "negative stride in " + nt.first; return false; }
+      const int64_t steps = h.shape[d] - 1;
+      if (steps > 0 && t->strides[d] > (avail - max_index) / steps) { *err = "tensor view exceeds its storage: " + nt.first; return false; }
+      max_index += steps * t->strides[d];
+    }
+    if (numel > 0 && max_index >= avail) { *err = "tensor view exceeds its storage: " + nt.first; return false; }
     h.data.resize(static_cast<size_t>(numel));
     const uint8_t* base = blob.bytes.data() + it->second.offset;
     std::vector<int64_t> ix(h.shape.size(), 0);

@@ -6,7 +6,16 @@
 #include <thread>
 
 #include "../../include/b200_infer.h"
+#include "jpeg_decode.h"
 #include "resize.h"
+
+b2i_ctx::~b2i_ctx() {
+  for (size_t i = 0; i < jpeg.size(); ++i)
+    if (jpeg[i]) {
+      cudaSetDevice(devices[i]);
+      b2i::jpeg_decoder_destroy(jpeg[i]);
+    }
+}
 
 namespace b2i {
 
@@ -174,7 +183,10 @@ void slot_free(DevSlot* s) {
   if (s->raw.d_tab) cudaFree(s->raw.d_tab);
   if (s->raw.h_tab) cudaFreeHost(s->raw.h_tab);
   if (s->raw.d_tmp) cudaFree(s->raw.d_tmp);
+  if (s->raw.d_jimg) cudaFree(s->raw.d_jimg);
   s->raw = RawScratch();
+  if (s->jpeg) jpeg_decoder_destroy(s->jpeg);
+  s->jpeg = nullptr;
   for (auto& kv : s->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   s->graphs.clear();
   if (s->copy_st) cudaStreamDestroy(s->copy_st);
@@ -254,8 +266,12 @@ bool grow(void** dev, void** host, size_t* cap, size_t need, std::string* err) {
 
 // One GPU's share: plan every image on the host, ship images + tables in two copies, run the two
 // resize passes per image into lane 0's device batch, then the usual chunked forward.
-void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const int* ws, int n, int k,
-               int32_t* idx, float* prob, float* logits, Shard* out) {
+//   images != null: decoded pixels in host memory, sizes in hs / ws
+//   jpeg   != null: encoded streams; decoded on this GPU (jpeg_decode.h) straight into the packed image
+//                   buffer, sizes from the header probe, one status per image
+void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* jpeg, const size_t* jpeg_len,
+               const int* hs_in, const int* ws_in, int n, int k, int32_t* idx, float* prob, float* logits,
+               int* status, Shard* out) {
   if (n == 0) return;
   auto cu = [&](cudaError_t e, const char* what) {
     if (e == cudaSuccess) return false;
@@ -266,11 +282,29 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const in
   if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
   Lane& L = s.lane[0];
   RawScratch& R = s.raw;
+  std::vector<int> hbuf, wbuf, stbuf;
+  const int* hs = hs_in;
+  const int* ws = ws_in;
+  if (jpeg) {
+    if (!s.jpeg) {
+      s.jpeg = jpeg_decoder_create(&out->err);
+      if (!s.jpeg) { out->rc = B2I_ENODEV; return; }
+    }
+    hbuf.resize(n); wbuf.resize(n);
+    if (!status) { stbuf.resize(n); status = stbuf.data(); }
+    jpeg_probe(s.jpeg, jpeg, jpeg_len, n, hbuf.data(), wbuf.data(), status);
+    hs = hbuf.data();
+    ws = wbuf.data();
+  }
+  auto usable = [&](int i) { return jpeg ? status[i] == B2I_OK : true; };
   std::vector<AxisPlan> px(n), py(n);
   std::vector<size_t> img_off(n), tab_off(n);
   size_t img_bytes = 0, tab_bytes = 0, tmp_elems = 0;
   for (int i = 0; i < n; ++i) {
-    if (!images[i] || hs[i] < 1 || ws[i] < 1) { out->rc = B2I_EINVAL; out->err = "image " + std::to_string(i) + " is empty"; return; }
+    img_off[i] = img_bytes;
+    tab_off[i] = tab_bytes;
+    if (!usable(i)) continue;
+    if (!jpeg && (!images[i] || hs[i] < 1 || ws[i] < 1)) { out->rc = B2I_EINVAL; out->err = "image " + std::to_string(i) + " is empty"; return; }
     plan_image(hs[i], ws[i], &px[i], &py[i]);
     img_off[i] = img_bytes;
     img_bytes += (static_cast<size_t>(hs[i]) * ws[i] * 3 + 255) & ~static_cast<size_t>(255);
@@ -278,7 +312,8 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const in
     tab_bytes += ((4 * 224 * 4 + (px[i].idx.size() + py[i].idx.size()) * 8) + 255) & ~static_cast<size_t>(255);
     tmp_elems = std::max(tmp_elems, static_cast<size_t>(hs[i]) * 224 * 3);
   }
-  if (!grow(reinterpret_cast<void**>(&R.d_img), reinterpret_cast<void**>(&R.h_img), &R.img_cap, img_bytes, &out->err) ||
+  if (!(jpeg ? grow(reinterpret_cast<void**>(&R.d_jimg), nullptr, &R.jimg_cap, img_bytes, &out->err)
+             : grow(reinterpret_cast<void**>(&R.d_img), reinterpret_cast<void**>(&R.h_img), &R.img_cap, img_bytes, &out->err)) ||
       !grow(reinterpret_cast<void**>(&R.d_tab), reinterpret_cast<void**>(&R.h_tab), &R.tab_cap, tab_bytes, &out->err) ||
       !grow(reinterpret_cast<void**>(&R.d_tmp), nullptr, &R.tmp_cap, tmp_elems * 4, &out->err)) {
     out->rc = B2I_ENOMEM;
@@ -286,13 +321,14 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const in
   }
   std::vector<ResizeJob> jobs(n);
   for (int i = 0; i < n; ++i) {
-    std::memcpy(R.h_img + img_off[i], images[i], static_cast<size_t>(hs[i]) * ws[i] * 3);
+    if (!usable(i)) continue;
+    if (!jpeg) std::memcpy(R.h_img + img_off[i], images[i], static_cast<size_t>(hs[i]) * ws[i] * 3);
     uint8_t* ht = R.h_tab + tab_off[i];
     uint8_t* dt = R.d_tab + tab_off[i];
     size_t o = 0;
     auto put = [&](const void* src, size_t bytes) { std::memcpy(ht + o, src, bytes); const size_t at = o; o += bytes; return at; };
     ResizeJob& j = jobs[i];
-    j.d_img = R.d_img + img_off[i]; j.h = hs[i]; j.w = ws[i];
+    j.d_img = (jpeg ? R.d_jimg : R.d_img) + img_off[i]; j.h = hs[i]; j.w = ws[i];
     j.xf = reinterpret_cast<const int*>(dt + put(px[i].first.data(), 224 * 4));
     j.xc = reinterpret_cast<const int*>(dt + put(px[i].count.data(), 224 * 4));
     j.yf = reinterpret_cast<const int*>(dt + put(py[i].first.data(), 224 * 4));
@@ -304,10 +340,16 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const in
     j.d_tmp = R.d_tmp;
     j.d_out = L.d_in + static_cast<size_t>(i) * B2I_IMAGE_BYTES;
   }
-  if (cu(cudaMemcpyAsync(R.d_img, R.h_img, img_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D raw images")) return;
+  if (jpeg) {
+    std::vector<uint8_t*> dst(n);
+    for (int i = 0; i < n; ++i) dst[i] = R.d_jimg + img_off[i];
+    if (!jpeg_decode_batch(s.jpeg, jpeg, jpeg_len, n, dst.data(), hs, ws, status, s.comp_st, &out->err)) { out->rc = B2I_ECUDA; return; }
+  } else if (cu(cudaMemcpyAsync(R.d_img, R.h_img, img_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D raw images")) {
+    return;
+  }
   if (cu(cudaMemcpyAsync(R.d_tab, R.h_tab, tab_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D resize tables")) return;
   for (int i = 0; i < n; ++i)
-    if (cu(launch_resize_job(jobs[i], s.comp_st), "resize kernels")) return;
+    if (usable(i) && cu(launch_resize_job(jobs[i], s.comp_st), "resize kernels")) return;
   const int classes = s.dm->classes();
   if (logits && !L.d_logits) {
     const size_t cap = static_cast<size_t>(s.dm->max_batch());
@@ -331,9 +373,40 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const int* hs, const in
   std::memcpy(idx, L.h_idx, nk * 4);
   std::memcpy(prob, L.h_prob, nk * 4);
   if (logits) std::memcpy(logits, L.h_logits, static_cast<size_t>(n) * classes * 4);
+  if (jpeg)
+    for (int i = 0; i < n; ++i)
+      if (status[i] != B2I_OK) {   // its slot of the device batch held no image: blank the answer
+        for (int j = 0; j < k; ++j) { idx[static_cast<size_t>(i) * k + j] = -1; prob[static_cast<size_t>(i) * k + j] = 0.f; }
+        if (logits) std::fill(logits + static_cast<size_t>(i) * classes, logits + static_cast<size_t>(i + 1) * classes, 0.f);
+      }
 }
 
 }  // namespace
+
+int predict_jpeg(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* jpeg, const size_t* len, int n, int k,
+                 int32_t* idx, float* prob, float* logits, int* status, std::string* err) {
+  if (n < 0 || (n > 0 && (!jpeg || !len || !idx || !prob || !status))) { *err = "null buffer"; return B2I_EINVAL; }
+  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
+  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size())) { *err = "device range outside the model's context"; return B2I_EINVAL; }
+  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch) { *err = "batch exceeds GPUs x max_batch"; return B2I_EINVAL; }
+  if (m->pending[0].active || m->pending[1].active) { *err = "an asynchronous request is still in flight; b2i_wait for it first"; return B2I_EINVAL; }
+  const int per = (n + n_dev - 1) / n_dev;
+  std::vector<Shard> sh(n_dev);
+  auto work = [&](int g) {
+    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
+    raw_shard(m->slots[first_dev + g], nullptr, jpeg + lo, len + lo, nullptr, nullptr, hi - lo, k, idx + static_cast<size_t>(lo) * k,
+              prob + static_cast<size_t>(lo) * k, logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, status + lo, &sh[g]);
+  };
+  if (n_dev == 1) work(0);
+  else {
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
+    for (auto& x : th) x.join();
+  }
+  for (int g = 0; g < n_dev; ++g)
+    if (sh[g].rc != B2I_OK) { *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].err; return sh[g].rc; }
+  return B2I_OK;
+}
 
 int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
                 const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, std::string* err) {
@@ -346,8 +419,8 @@ int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* im
   std::vector<Shard> sh(n_dev);
   auto work = [&](int g) {
     const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
-    raw_shard(m->slots[first_dev + g], images + lo, heights + lo, widths + lo, hi - lo, k, idx + static_cast<size_t>(lo) * k,
-              prob + static_cast<size_t>(lo) * k, logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, &sh[g]);
+    raw_shard(m->slots[first_dev + g], images + lo, nullptr, nullptr, heights + lo, widths + lo, hi - lo, k, idx + static_cast<size_t>(lo) * k,
+              prob + static_cast<size_t>(lo) * k, logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, nullptr, &sh[g]);
   };
   if (n_dev == 1) work(0);
   else {
@@ -357,6 +430,42 @@ int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* im
   }
   for (int g = 0; g < n_dev; ++g)
     if (sh[g].rc != B2I_OK) { *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].err; return sh[g].rc; }
+  return B2I_OK;
+}
+
+int predict_raw_status(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
+                       const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, int* status,
+                       std::string* err) {
+  if (n < 0 || (n > 0 && (!images || !heights || !widths || !idx || !prob || !status))) { *err = "null buffer"; return B2I_EINVAL; }
+  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
+  // images that cannot be used are set aside with a status of their own; the rest go through as one batch
+  std::vector<const uint8_t*> img;
+  std::vector<int> hs, ws, at;
+  for (int i = 0; i < n; ++i) {
+    if (!images[i] || heights[i] < 1 || widths[i] < 1) { status[i] = B2I_EDECODE; continue; }
+    if (heights[i] > kMaxRawSide || widths[i] > kMaxRawSide) { status[i] = B2I_EINVAL; continue; }
+    status[i] = B2I_OK;
+    img.push_back(images[i]); hs.push_back(heights[i]); ws.push_back(widths[i]); at.push_back(i);
+  }
+  const int nv = static_cast<int>(at.size());
+  for (int i = 0; i < n; ++i)
+    if (status[i] != B2I_OK) {
+      for (int j = 0; j < k; ++j) { idx[static_cast<size_t>(i) * k + j] = -1; prob[static_cast<size_t>(i) * k + j] = 0.f; }
+      if (logits) std::fill(logits + static_cast<size_t>(i) * B2I_CLASSES, logits + static_cast<size_t>(i + 1) * B2I_CLASSES, 0.f);
+    }
+  if (nv == 0) return B2I_OK;
+  if (nv == n) return predict_raw(m, first_dev, n_dev, images, heights, widths, n, k, idx, prob, logits, err);
+  std::vector<int32_t> ci(static_cast<size_t>(nv) * k);
+  std::vector<float> cp(static_cast<size_t>(nv) * k), cl(logits ? static_cast<size_t>(nv) * B2I_CLASSES : 0);
+  const int rc = predict_raw(m, first_dev, n_dev, img.data(), hs.data(), ws.data(), nv, k, ci.data(), cp.data(),
+                             logits ? cl.data() : nullptr, err);
+  if (rc != B2I_OK) return rc;
+  for (int v = 0; v < nv; ++v) {
+    const size_t i = static_cast<size_t>(at[v]);
+    std::memcpy(idx + i * k, &ci[static_cast<size_t>(v) * k], static_cast<size_t>(k) * 4);
+    std::memcpy(prob + i * k, &cp[static_cast<size_t>(v) * k], static_cast<size_t>(k) * 4);
+    if (logits) std::memcpy(logits + i * B2I_CLASSES, &cl[static_cast<size_t>(v) * B2I_CLASSES], B2I_CLASSES * 4);
+  }
   return B2I_OK;
 }
 

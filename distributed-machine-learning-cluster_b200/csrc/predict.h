@@ -14,8 +14,13 @@
 
 #include "engine.h"
 
+namespace b2i { struct JpegDecoder; }
+
 struct b2i_ctx {
   std::vector<int> devices;
+  std::mutex jpeg_mu;                          // guards the decoders below (b2i_jpeg_decode_u8)
+  std::vector<b2i::JpegDecoder*> jpeg;         // one per device, created on first use
+  ~b2i_ctx();
 };
 
 namespace b2i {
@@ -52,11 +57,15 @@ struct RawScratch {
   uint8_t* h_img = nullptr; uint8_t* d_img = nullptr; size_t img_cap = 0;   // pinned / device
   uint8_t* h_tab = nullptr; uint8_t* d_tab = nullptr; size_t tab_cap = 0;
   float* d_tmp = nullptr; size_t tmp_cap = 0;
+  uint8_t* d_jimg = nullptr; size_t jimg_cap = 0;   // decoded images of the JPEG path (device only)
 };
+
+struct JpegDecoder;
 
 struct DevSlot {
   std::unique_ptr<DeviceModel> dm;
   RawScratch raw;
+  JpegDecoder* jpeg = nullptr;                 // created by the first b2i_predict_jpeg on this GPU
   cudaStream_t copy_st = nullptr, comp_st = nullptr;
   Lane lane[2];
   int chunk = 0;
@@ -97,6 +106,17 @@ int predict_submit(b2i_model* m, int first_dev, int n_dev, const uint8_t* images
 // device batch -> forward -> results.  images[i] is u8 [heights[i]][widths[i]][3] in host memory.
 int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
                 const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, std::string* err);
+// Same with one status per image (B2I_OK, B2I_EDECODE for a null / empty image, B2I_EINVAL for one larger
+// than kMaxRawSide on a side): a bad image costs its own answer, not the batch's (the reference loses one
+// query per bad file because it sends one id per RPC, reference src/services.rs:421,490-492).
+constexpr int kMaxRawSide = 16384;
+int predict_raw_status(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
+                       const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, int* status,
+                       std::string* err);
+// Blocking: encoded JPEG streams -> decode on the GPU (nvJPEG) -> resize + centre crop -> forward -> results,
+// one status per image (B2I_EDECODE for a stream that cannot be decoded).
+int predict_jpeg(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* jpeg, const size_t* len, int n, int k,
+                 int32_t* idx, float* prob, float* logits, int* status, std::string* err);
 // Block until the request is complete and its results are in the arrays given at submit time.
 int predict_wait(b2i_model* m, long long ticket, std::string* err);
 

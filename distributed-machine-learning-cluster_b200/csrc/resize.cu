@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <mutex>
 
 namespace b2i {
@@ -106,17 +107,21 @@ void plan_axis(int in_size, int out_size, int crop, AxisPlan* p) {
     n0[n] = first;
     n1[n] = last;
   }
+  // n0 and n1 never decrease with n, and j grows with jj: the contributors of output j are a window
+  // [lo, ...) that only moves forward.  Sums run over ascending n exactly as a full scan would.
+  int lo = 0;
   for (int jj = 0; jj < 224; ++jj) {
     const int j = jj + crop;
+    while (lo < ncontrib && n1[lo] < j && n0[lo] <= j) ++lo;
     float total = 0.0f;
-    for (int n = 0; n < ncontrib; ++n) {
+    for (int n = lo; n < ncontrib; ++n) {
       if (j >= n0[n] && j <= n1[n]) total += cf[off[n] + (j - n0[n])];
       else if (j < n0[n]) break;
     }
     const float fs = 1.0f / total;
     p->first[jj] = static_cast<int>(p->idx.size());
     int cnt = 0;
-    for (int n = 0; n < ncontrib; ++n) {
+    for (int n = lo; n < ncontrib; ++n) {
       if (j >= n0[n] && j <= n1[n]) {
         const float v = cf[off[n] + (j - n0[n])] * fs;
         if (v != 0.0f) {
@@ -242,8 +247,8 @@ cudaError_t launch_resize_job(const ResizeJob& j, cudaStream_t st) {
 
 // ------------------------------------------------------------------------------------------------
 // Allocation-free variant.  Some hosts of this library may not allocate GPU memory at run time: a
-// serving process whose memory pool is carved up once at start-up, code running between stream
-// capture calls, or a tenant under a fixed memory budget.  For them the scratch of the resize (the
+// serving process whose memory pool is carved up once at start-up, or a tenant under a fixed memory
+// budget.  For them the scratch of the resize (the
 // horizontally resampled rows and the two resampling plans) lives in one file-scope device array
 // instead of cudaMalloc'ed buffers.  Every GPU that loads the library carries the array until the
 // process exits.
@@ -294,32 +299,36 @@ bool resize_crop_224_static(const uint8_t* d_image, int h, int w, uint8_t* d_out
            " taps per axis (image " + std::to_string(h) + "x" + std::to_string(w) + "); use b2i_resize_crop_u8";
     return false;
   }
-  // carve the array: [tmp rows][x plan][y plan]; every byte a kernel reads below is written
-  // earlier in this same call, so nothing has to be cleared between calls
+  // Refuse to run under stream capture: the plans below depend on this image's size and are uploaded from
+  // host memory that dies with this call, so a captured copy would replay garbage.
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) {
+    *err = "the stream is capturing; b2i_resize_crop_u8_static cannot be recorded into a CUDA graph";
+    return false;
+  }
+  cudaGetLastError();
+  // carve the array: [tmp rows][plans]; the plans are packed [xf xc yf yc | xi | yi | xw | yw] so that they
+  // go up in ONE copy.  Every byte a kernel reads below is written earlier in this same call, so nothing
+  // has to be cleared between calls.
   float* d_tmp = reinterpret_cast<float*>(scratch);
-  auto carve = [&](int axis, int** first, int** count, int** idx, float** coef) {
-    unsigned char* b = scratch + kStaticTmpBytes + axis * kStaticAxisBytes;
-    *first = reinterpret_cast<int*>(b);
-    *count = *first + 224;
-    *idx = *count + 224;
-    *coef = reinterpret_cast<float*>(*idx + kStaticMaxTaps);
-  };
-  int *xf, *xc, *xi, *yf, *yc, *yi;
-  float *xw, *yw;
-  carve(0, &xf, &xc, &xi, &xw);
-  carve(1, &yf, &yc, &yi, &yw);
-  auto put = [&](void* dst, const void* src, size_t bytes) {
-    if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
-  };
-  e = cudaSuccess;
-  put(xf, px.first.data(), 224 * sizeof(int));
-  put(xc, px.count.data(), 224 * sizeof(int));
-  put(xi, px.idx.data(), px.idx.size() * sizeof(int));
-  put(xw, px.coef.data(), px.coef.size() * sizeof(float));
-  put(yf, py.first.data(), 224 * sizeof(int));
-  put(yc, py.count.data(), 224 * sizeof(int));
-  put(yi, py.idx.data(), py.idx.size() * sizeof(int));
-  put(yw, py.coef.data(), py.coef.size() * sizeof(float));
+  const size_t nx = px.idx.size(), ny = py.idx.size();
+  std::vector<int> pack(4 * 224 + 2 * (nx + ny));
+  std::memcpy(&pack[0], px.first.data(), 224 * sizeof(int));
+  std::memcpy(&pack[224], px.count.data(), 224 * sizeof(int));
+  std::memcpy(&pack[448], py.first.data(), 224 * sizeof(int));
+  std::memcpy(&pack[672], py.count.data(), 224 * sizeof(int));
+  std::memcpy(&pack[896], px.idx.data(), nx * sizeof(int));
+  std::memcpy(&pack[896 + nx], py.idx.data(), ny * sizeof(int));
+  std::memcpy(&pack[896 + nx + ny], px.coef.data(), nx * sizeof(float));
+  std::memcpy(&pack[896 + 2 * nx + ny], py.coef.data(), ny * sizeof(float));
+  int* d_plan = reinterpret_cast<int*>(scratch + kStaticTmpBytes);
+  const int *xf = d_plan, *xc = d_plan + 224, *yf = d_plan + 448, *yc = d_plan + 672;
+  const int *xi = d_plan + 896, *yi = xi + nx;
+  const float *xw = reinterpret_cast<const float*>(yi + ny), *yw = xw + nx;
+  // `pack` is pageable and local: a host-to-device cudaMemcpyAsync from pageable memory returns only after
+  // the runtime has copied the source into its own staging buffer, so the vector may die when this
+  // function returns.  (That staging step is the one host-side wait in this call.)
+  e = cudaMemcpyAsync(d_plan, pack.data(), pack.size() * sizeof(int), cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) { *err = std::string("plan upload: ") + cudaGetErrorString(e); return false; }
   long long blocks = (static_cast<long long>(h) * 224 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;

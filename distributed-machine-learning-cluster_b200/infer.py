@@ -111,6 +111,23 @@ class Context:
         check(_lib.lib().b2i_resize_crop_u8(self._h, dev, _ptr(img), h, w, _ptr(out)))
         return out
 
+    def jpeg_decode(self, data, dev=0):
+        """One encoded JPEG (bytes) -> u8 [H,W,3] RGB as the GPU decoder produces it (the decode stage of
+        Model.predict_jpeg alone; raises B2IError with code EDECODE for a stream it cannot decode)."""
+        buf = np.frombuffer(data, dtype=np.uint8)
+        h, w = ctypes.c_int(), ctypes.c_int()
+        check(_lib.lib().b2i_jpeg_decode_u8(self._h, dev, _ptr(buf), buf.size, None, 0, ctypes.byref(h), ctypes.byref(w)))
+        out = np.empty((h.value, w.value, 3), np.uint8)
+        check(_lib.lib().b2i_jpeg_decode_u8(self._h, dev, _ptr(buf), buf.size, _ptr(out), out.size, ctypes.byref(h),
+                                            ctypes.byref(w)))
+        return out
+
+    def jpeg_backend(self, dev=0):
+        """Which nvJPEG backends opened on this GPU ("hardware+gpu_hybrid+hybrid", ...)."""
+        buf = ctypes.create_string_buffer(128)
+        check(_lib.lib().b2i_jpeg_backend(self._h, dev, buf, len(buf)))
+        return buf.value.decode()
+
     def resize_crop_static(self, d_image, h, w, d_out224, stream=None, dev=0):
         """Allocation-free resize + crop for callers that may not allocate GPU memory: `d_image`
         (u8 [h,w,3]) and `d_out224` (u8 [224,224,3]) are device addresses (ints) owned by the
@@ -246,6 +263,41 @@ class Model:
         first, count = devices if devices is not None else (0, 0)
         check(_lib.lib().b2i_predict_raw_u8(self._h, first, count, ptrs, hs, ws, n, k, _ptr(idx), _ptr(prob), _ptr(logits)))
         return (idx, prob, logits) if want_logits else (idx, prob)
+
+    def predict_raw_status(self, images, k=5, want_logits=False, devices=None):
+        """predict_raw with one status per image: entries of `images` may be None (the caller's decoder
+        failed); those come back with status EDECODE and idx -1 while the rest are answered.
+        -> (idx, prob[, logits], status int32 [n])."""
+        imgs = [None if im is None else np.ascontiguousarray(im, dtype=np.uint8) for im in images]
+        n = len(imgs)
+        ptrs = (ctypes.c_void_p * max(n, 1))(*[None if im is None else im.ctypes.data for im in imgs])
+        hs = (ctypes.c_int * max(n, 1))(*[0 if im is None else im.shape[0] for im in imgs])
+        ws = (ctypes.c_int * max(n, 1))(*[0 if im is None else im.shape[1] for im in imgs])
+        idx = np.empty((n, k), np.int32)
+        prob = np.empty((n, k), np.float32)
+        status = np.zeros(n, np.int32)
+        logits = np.empty((n, CLASSES), np.float32) if want_logits else None
+        first, count = devices if devices is not None else (0, 0)
+        check(_lib.lib().b2i_predict_raw_u8_status(self._h, first, count, ptrs, hs, ws, n, k, _ptr(idx), _ptr(prob),
+                                                   _ptr(logits), _ptr(status)))
+        return (idx, prob, logits, status) if want_logits else (idx, prob, status)
+
+    def predict_jpeg(self, blobs, k=5, want_logits=False, devices=None):
+        """Encoded JPEG streams (list of bytes; None / b"" = nothing to decode) -> GPU decode -> resize +
+        crop -> forward -> (idx, prob[, logits], status int32 [n]).  The whole body of Member::predict
+        from the file contents on."""
+        bufs = [np.frombuffer(b, dtype=np.uint8) if b else None for b in blobs]
+        n = len(bufs)
+        ptrs = (ctypes.c_void_p * max(n, 1))(*[None if b is None else b.ctypes.data for b in bufs])
+        lens = (ctypes.c_size_t * max(n, 1))(*[0 if b is None else b.size for b in bufs])
+        idx = np.empty((n, k), np.int32)
+        prob = np.empty((n, k), np.float32)
+        status = np.zeros(n, np.int32)
+        logits = np.empty((n, CLASSES), np.float32) if want_logits else None
+        first, count = devices if devices is not None else (0, 0)
+        check(_lib.lib().b2i_predict_jpeg(self._h, first, count, ptrs, lens, n, k, _ptr(idx), _ptr(prob), _ptr(logits),
+                                          _ptr(status)))
+        return (idx, prob, logits, status) if want_logits else (idx, prob, status)
 
     def submit_u8(self, images_u8, idx, prob, logits=None):
         """Asynchronous predict: enqueue and return a ticket. `images_u8` (ideally a PinnedBuffer

@@ -14,14 +14,19 @@ is absent here, see INTEGRATION.md for the cgo-style binding a maintainer would 
   Leader.run_job       reference src/services.rs:407-433   (batched: many ids per predict call)
   jobs_report          reference src/main.rs:281-309       (ms percentiles + accuracy)
 
-JPEG decode stays on the host (PIL), as SURVEY.md 8b prescribes: the ABI takes pixels, not paths.
+The ABI takes bytes, not paths.  Decode is off the calling thread:
+MemberState reads the files and hands the encoded streams to b2i_predict_jpeg (nvJPEG on the GPU); where
+nvJPEG is not installed, or for the few streams it refuses, a host thread pool decodes with PIL (which
+releases the GIL) and the pixels go through b2i_predict_raw_u8_status.
 """
 import math
 import os
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
+from . import _lib
 from .infer import ALEXNET_TCH, PREC_BF16, Context, Model
 
 IMAGE_ROOT = os.path.join("test_files", "imagenet_1k", "train")       # services.rs:476
@@ -48,6 +53,28 @@ def decode_image(path):
             return np.asarray(im.convert("RGB"))
     except Exception:
         return None
+
+
+def decode_bytes(blob):
+    """Host decode of one encoded image held in memory; None when it cannot be decoded."""
+    if not blob:
+        return None
+    try:
+        import io
+        from PIL import Image
+        with Image.open(io.BytesIO(blob)) as im:
+            return np.asarray(im.convert("RGB"))
+    except Exception:
+        return None
+
+
+class MissingDirectory(Exception):
+    """`read_dir(folder/id)` failed: the reference unwraps and the handler panics (services.rs:485)."""
+
+
+SKIPPED = "skipped"      # the id's directory is empty: the reference `continue`s (services.rs:490)
+UNDECODABLE = "undecodable"   # load_image_and_resize failed: the reference's RPC returns None (services.rs:492)
+MISSING = "missing"      # no such directory: the reference's handler panics (services.rs:485)
 
 
 def sample_predict(labels, ctx=None, weight_dir=WEIGHT_DIR,
@@ -84,10 +111,14 @@ def predict_image(model, image_path, label, labels, ctx=None):
 
 class MemberState:
     """The model half of the reference's `MemberState` (services.rs:450-457, 513-524): one ResNet-18
-    and one AlexNet resident on this member's GPUs, and the body of `Member::predict`."""
+    and one AlexNet resident on this member's GPUs, and the body of `Member::predict`.
+
+    decoder: "nvjpeg" = encoded streams go to the GPU decoder (b2i_predict_jpeg); "pil" = host thread
+    pool; "auto" (default) = nvjpeg when the library can be loaded on this box, else pil."""
 
     def __init__(self, ctx, labels, weight_dir=WEIGHT_DIR, image_root=IMAGE_ROOT, precision=PREC_BF16,
-                 max_batch=256, alexnet_geometry=ALEXNET_TCH, models=MODEL_NAMES):
+                 max_batch=256, alexnet_geometry=ALEXNET_TCH, models=MODEL_NAMES, decoder="auto",
+                 decode_threads=None):
         self.ctx = ctx
         self.labels = labels
         self.image_root = image_root
@@ -98,8 +129,19 @@ class MemberState:
                         max_batch=max_batch, alexnet_geometry=alexnet_geometry)
             for name in models
         }
+        if decoder == "auto":
+            try:
+                ctx.jpeg_backend()
+                decoder = "nvjpeg"
+            except _lib.B2IError:
+                decoder = "pil"
+        if decoder not in ("nvjpeg", "pil"):
+            raise ValueError("decoder must be auto, nvjpeg or pil")
+        self.decoder = decoder
+        self.pool = ThreadPoolExecutor(max_workers=decode_threads or min(32, os.cpu_count() or 1))
 
     def close(self):
+        self.pool.shutdown(wait=True)
         for m in self.models.values():
             m.close()
 
@@ -112,29 +154,81 @@ class MemberState:
             raise ValueError("Model not found: %r" % (model_name,))
         model.reload(os.path.join(weight_dir or self.weight_dir, model_name + ".ot"))
 
-    def predict(self, model_name, input_ids, k=1, devices=None):
-        """Option<Vec<(f64, String)>>: None for an unknown model (services.rs:480) or when any image
-        fails to decode (services.rs:492); ids whose directory is empty are skipped (services.rs:490);
-        a missing directory raises (the reference unwraps, services.rs:485).  With k > 1 each entry
-        is a list of k (prob, label) pairs instead of one pair."""
+    # ---- file side ---------------------------------------------------------------------------
+    def _read_one(self, input_id):
+        """First file of test_files/.../<id>/ (services.rs:485-490) as bytes; MISSING / SKIPPED markers."""
+        folder = os.path.join(self.image_root, input_id)
+        try:
+            entries = sorted(os.listdir(folder))
+        except OSError:
+            return MISSING
+        if not entries:
+            return SKIPPED
+        try:
+            with open(os.path.join(folder, entries[0]), "rb") as f:
+                return f.read()
+        except OSError:
+            return b""
+
+    def read_ids(self, input_ids):
+        """Encoded file contents for every id, read by the thread pool, aligned with input_ids."""
+        return list(self.pool.map(self._read_one, input_ids))
+
+    # ---- the handler -------------------------------------------------------------------------
+    def predict_each(self, model_name, input_ids, k=1, devices=None, blobs=None):
+        """One entry per input id, in order: (prob, label) -- or a list of k such pairs when k > 1 -- for
+        an id that was answered, else one of the markers SKIPPED / UNDECODABLE / MISSING.  This is what a
+        batched caller needs to keep the reference's per-query accounting: there, one id travels per RPC
+        (services.rs:421), so a bad file costs its own query and nothing else.  None for an unknown
+        model (services.rs:480).  `blobs` = the result of read_ids(input_ids) when the caller has
+        already fetched the files (run_job reads the next batch while this one is on the GPU)."""
         model = self.models.get(model_name)
         if model is None:
             return None
-        batch = []
-        for input_id in input_ids:
-            entries = sorted(os.listdir(os.path.join(self.image_root, input_id)))
-            if not entries:
-                continue
-            img = decode_image(os.path.join(self.image_root, input_id, entries[0]))
-            if img is None:
-                return None
-            batch.append(img)
-        if not batch:
-            return []
-        idx, prob = model.predict_raw(batch, k=k, devices=devices)   # resize + crop + forward + top-k on the GPU
-        if k == 1:
-            return [(float(p[0]), self.labels[int(i[0])][1]) for i, p in zip(idx, prob)]
-        return [[(float(pp), self.labels[int(ii)][1]) for ii, pp in zip(i, p)] for i, p in zip(idx, prob)]
+        if blobs is None:
+            blobs = self.read_ids(input_ids)
+        out = list(blobs)
+        live = [i for i, b in enumerate(blobs) if not isinstance(b, str)]
+        if not live:
+            return out
+        idx = prob = None
+        status = np.full(len(live), _lib.EDECODE, np.int32)
+        if self.decoder == "nvjpeg":
+            idx, prob, status = model.predict_jpeg([blobs[i] for i in live], k=k, devices=devices)
+        retry = [j for j in range(len(live)) if status[j] != _lib.OK]
+        if retry:
+            # host decode for what the GPU decoder did not take (all of it when nvJPEG is absent)
+            pixels = list(self.pool.map(decode_bytes, [blobs[live[j]] for j in retry]))
+            if any(p is not None for p in pixels):
+                ridx, rprob, rstatus = model.predict_raw_status(pixels, k=k, devices=devices)
+                if idx is None:
+                    idx = np.full((len(live), k), -1, np.int32)
+                    prob = np.zeros((len(live), k), np.float32)
+                for j, jj in enumerate(retry):
+                    idx[jj], prob[jj], status[jj] = ridx[j], rprob[j], rstatus[j]
+        for j, i in enumerate(live):
+            if status[j] != _lib.OK:
+                out[i] = UNDECODABLE
+            elif k == 1:
+                out[i] = (float(prob[j, 0]), self.labels[int(idx[j, 0])][1])
+            else:
+                out[i] = [(float(pp), self.labels[int(ii)][1]) for ii, pp in zip(idx[j], prob[j])]
+        return out
+
+    def predict(self, model_name, input_ids, k=1, devices=None):
+        """Option<Vec<(f64, String)>> exactly as the reference's handler returns it: None for an unknown
+        model (services.rs:480) or when any image fails to decode (services.rs:492); ids whose directory
+        is empty are skipped (services.rs:490); a missing directory raises (the reference unwraps,
+        services.rs:485).  With k > 1 each entry is a list of k (prob, label) pairs instead of one pair."""
+        each = self.predict_each(model_name, input_ids, k=k, devices=devices)
+        if each is None:
+            return None
+        if any(e == MISSING for e in each):
+            bad = input_ids[[e == MISSING for e in each].index(True)]
+            raise FileNotFoundError(os.path.join(self.image_root, bad))
+        if any(e == UNDECODABLE for e in each):
+            return None
+        return [e for e in each if e != SKIPPED]
 
 
 class Job:
@@ -178,27 +272,41 @@ class Leader:
         """Batched `run_job`: resumes at labels[finished_prediction_count..] (services.rs:410-411),
         sends `batch` ids per predict call to the job's assigned GPUs, skips the labels silently when
         nobody is assigned (services.rs:416), records one duration per query = the wall time of the
-        batch that carried it, and prints the reference's result lines (services.rs:425-429)."""
+        batch that carried it, and prints the reference's result lines (services.rs:425-429).  Every
+        answer is scored against ITS OWN label; an id that produced no answer (empty or missing
+        directory, undecodable file) is a lost query, as in the reference, and costs nothing else.
+        The files of batch i+1 are read while batch i is on the GPU."""
         start_at = job.finished_prediction_count
         todo = self.labels[start_at:] if limit is None else self.labels[start_at:start_at + limit]
-        for i in range(0, len(todo), batch):
-            chunk = todo[i:i + batch]
-            ids = list(job.assigned_member_ids)
-            if not ids:
-                continue
-            devices = (min(ids), max(ids) - min(ids) + 1)
-            t0 = time.perf_counter()
-            res = self.member.predict(job.model_name, [wnid for wnid, _ in chunk], devices=devices)
-            dt = time.perf_counter() - t0
-            if res is None:
-                continue
-            for (wnid, true_label), (prob, pred) in zip(chunk, res):
-                job.add_query_result(pred == true_label, dt)
-                if log:
-                    if pred == true_label:
-                        log("%s - %s: %s (%.2f%%)" % (job.model_name, wnid, pred, prob * 100.0))
-                    else:
-                        log("%s - %s: %s (%.2f%%) (should be %s)" % (job.model_name, wnid, pred, prob * 100.0, true_label))
+        chunks = [todo[i:i + batch] for i in range(0, len(todo), batch)]
+        ahead = ThreadPoolExecutor(max_workers=1)
+        fetch = lambda c: self.member.read_ids([wnid for wnid, _ in c])
+        nxt = ahead.submit(fetch, chunks[0]) if chunks else None
+        try:
+            for ci, chunk in enumerate(chunks):
+                blobs = nxt.result()
+                nxt = ahead.submit(fetch, chunks[ci + 1]) if ci + 1 < len(chunks) else None
+                ids = list(job.assigned_member_ids)
+                if not ids:
+                    continue
+                devices = (min(ids), max(ids) - min(ids) + 1)
+                t0 = time.perf_counter()
+                res = self.member.predict_each(job.model_name, [wnid for wnid, _ in chunk], devices=devices, blobs=blobs)
+                dt = time.perf_counter() - t0
+                if res is None:
+                    continue
+                for (wnid, true_label), r in zip(chunk, res):
+                    if isinstance(r, str):          # SKIPPED / UNDECODABLE / MISSING: no answer for this id
+                        continue
+                    prob, pred = r
+                    job.add_query_result(pred == true_label, dt)
+                    if log:
+                        if pred == true_label:
+                            log("%s - %s: %s (%.2f%%)" % (job.model_name, wnid, pred, prob * 100.0))
+                        else:
+                            log("%s - %s: %s (%.2f%%) (should be %s)" % (job.model_name, wnid, pred, prob * 100.0, true_label))
+        finally:
+            ahead.shutdown(wait=True)
 
     def predict(self, batch=32, limit=None, log=None):
         """`Leader::predict` (services.rs:146-151) joins both jobs; they run on disjoint GPU halves."""

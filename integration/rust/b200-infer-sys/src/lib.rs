@@ -23,6 +23,13 @@ pub struct b2i_model_config {
 }
 
 pub const B2I_OK: c_int = 0;
+pub const B2I_EINVAL: c_int = -1;
+pub const B2I_EIO: c_int = -2;
+pub const B2I_ECUDA: c_int = -3;
+pub const B2I_ENODEV: c_int = -4;
+pub const B2I_ENOMEM: c_int = -5;
+pub const B2I_EINTERNAL: c_int = -6;
+pub const B2I_EDECODE: c_int = -7;
 pub const B2I_PREC_BF16: c_int = 0;
 pub const B2I_PREC_FP32: c_int = 1;
 pub const B2I_PREC_FP16: c_int = 2;
@@ -48,6 +55,15 @@ extern "C" {
     pub fn b2i_predict_raw_u8(m: *mut b2i_model, first_dev: c_int, n_dev: c_int, images: *const *const u8,
                               heights: *const c_int, widths: *const c_int, n: c_int, k: c_int,
                               idx: *mut i32, prob: *mut c_float, logits: *mut c_float) -> c_int;
+    pub fn b2i_predict_raw_u8_status(m: *mut b2i_model, first_dev: c_int, n_dev: c_int, images: *const *const u8,
+                                     heights: *const c_int, widths: *const c_int, n: c_int, k: c_int,
+                                     idx: *mut i32, prob: *mut c_float, logits: *mut c_float,
+                                     status: *mut c_int) -> c_int;
+    pub fn b2i_predict_jpeg(m: *mut b2i_model, first_dev: c_int, n_dev: c_int, jpeg: *const *const u8,
+                            len: *const usize, n: c_int, k: c_int, idx: *mut i32, prob: *mut c_float,
+                            logits: *mut c_float, status: *mut c_int) -> c_int;
+    pub fn b2i_jpeg_decode_u8(ctx: *mut b2i_ctx, dev: c_int, jpeg: *const u8, len: usize, out: *mut u8,
+                              cap: usize, h: *mut c_int, w: *mut c_int) -> c_int;
     pub fn b2i_submit_u8(m: *mut b2i_model, images: *const u8, n: c_int, k: c_int, idx: *mut i32,
                          prob: *mut c_float, logits: *mut c_float, ticket: *mut c_longlong) -> c_int;
     pub fn b2i_wait(m: *mut b2i_model, ticket: c_longlong) -> c_int;

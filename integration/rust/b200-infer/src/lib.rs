@@ -68,6 +68,23 @@ impl Model {
         check(rc)?;
         Ok((0..n).map(|i| (0..k).map(|j| (prob[i * k + j] as f64, idx[i * k + j] as usize)).collect()).collect())
     }
+    /// The body of `Member::predict` from the file contents on (services.rs:484-495): encoded JPEG streams in,
+    /// one `Some(top-k)` per stream that decoded, `None` for one that did not (the caller maps any `None`
+    /// to the RPC-level `None` of `.ok()?` at :492, or keeps per-id accounting in a batched `run_job`).
+    pub fn predict_jpeg(&self, blobs: &[&[u8]], k: usize, devices: Option<(i32, i32)>) -> Result<Vec<Option<Vec<(f64, usize)>>>, Error> {
+        let n = blobs.len();
+        let ptrs: Vec<*const u8> = blobs.iter().map(|b| b.as_ptr()).collect();
+        let lens: Vec<usize> = blobs.iter().map(|b| b.len()).collect();
+        let (mut idx, mut prob, mut status) = (vec![0i32; n * k], vec![0f32; n * k], vec![0i32; n]);
+        let (f, c) = devices.unwrap_or((0, 0));
+        check(unsafe {
+            sys::b2i_predict_jpeg(self.0, f, c, ptrs.as_ptr(), lens.as_ptr(), n as i32, k as i32, idx.as_mut_ptr(),
+                                  prob.as_mut_ptr(), ptr::null_mut(), status.as_mut_ptr())
+        })?;
+        Ok((0..n).map(|i| if status[i] != sys::B2I_OK { None } else {
+            Some((0..k).map(|j| (prob[i * k + j] as f64, idx[i * k + j] as usize)).collect())
+        }).collect())
+    }
     /// After `train` has copied a new `<model>.ot` to this member (main.rs:231-256): swap the weights in.
     pub fn reload(&self, ot_path: &str) -> Result<(), Error> {
         let p = CString::new(ot_path).unwrap();

@@ -62,3 +62,51 @@ def test_product_never_imports_the_oracle():
             if fn.endswith((".py", ".cpp", ".cu", ".h", ".cuh")):
                 src = open(os.path.join(dirpath, fn)).read()
                 assert "oracle" not in src.lower(), (fn, "mentions the oracle")
+
+
+def _struct_fields(text, opener, field_re):
+    body = text[text.index(opener):]
+    body = body[:body.index("}")]
+    return re.findall(field_re, body)
+
+
+def test_model_config_layout_agrees_everywhere():
+    """b2i_model_config is passed by pointer and filled by b2i_default_config: a binding with fewer fields
+    gets written past its end.  The header, the ctypes table, the Rust -sys crate and the block a maintainer
+    would copy out of INTEGRATION.md must list the same fields in the same order."""
+    from importlib import import_module
+    header = open(os.path.join(ROOT, "include", "b200_infer.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    h_fields = _struct_fields(header, "typedef struct b2i_model_config", r"\bint\s+(\w+)\s*;")
+    assert len(h_fields) >= 12 and h_fields[0] == "precision"
+    py_fields = [n for n, _ in import_module("distributed-machine-learning-cluster_b200._lib").ModelConfig._fields_]
+    rust = open(os.path.join(ROOT, "integration", "rust", "b200-infer-sys", "src", "lib.rs")).read()
+    rs_fields = _struct_fields(rust, "pub struct b2i_model_config", r"pub\s+(\w+)\s*:\s*c_int")
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    md_fields = _struct_fields(doc, "pub struct b2i_model_config", r"pub\s+(\w+)\s*:\s*c_int")
+    assert py_fields == h_fields
+    assert rs_fields == h_fields
+    assert md_fields == h_fields
+
+
+def test_error_codes_agree(pkg):
+    from importlib import import_module
+    header = open(os.path.join(ROOT, "include", "b200_infer.h")).read()
+    codes = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define B2I_(E[A-Z]+) \((-\d+)\)", header)}
+    lib = import_module("distributed-machine-learning-cluster_b200._lib")
+    assert codes and all(getattr(lib, name) == val for name, val in codes.items()), codes
+    rust = open(os.path.join(ROOT, "integration", "rust", "b200-infer-sys", "src", "lib.rs")).read()
+    for name, val in codes.items():
+        assert re.search(r"B2I_%s: c_int = %d;" % (name, val), rust), name
+
+
+def test_every_entry_point_stops_exceptions():
+    """No C++ exception may cross the C boundary: every extern "C" function with a body of more than one
+    statement runs it inside guarded(...)."""
+    src = open(os.path.join(ROOT, "distributed-machine-learning-cluster_b200", "csrc", "capi.cpp")).read()
+    ext = src[src.index('extern "C" {'):]
+    heads = list(re.finditer(r"^(?:static )?(?:int|long long) (b2i_\w+|ctx_dev)\([^;{]*\{\s*$", ext, flags=re.M))
+    assert len(heads) >= 25
+    for h in heads:
+        nxt = ext[h.end():h.end() + 60]
+        assert "return guarded(" in nxt, h.group(1)

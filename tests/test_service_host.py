@@ -8,18 +8,30 @@ from conftest import GOLDEN
 
 
 class FakeMember:
-    """Answers like MemberState.predict: (prob, label) per id, the label being the true one for
-    ids whose wnid ends in an even digit."""
+    """Answers like MemberState.predict_each: one entry per id, (prob, label) with the true label for ids
+    whose wnid ends in an even digit, or a marker for the ids listed in `skipped` / `undecodable` /
+    `missing`."""
 
-    def __init__(self, labels):
+    def __init__(self, labels, skipped=(), undecodable=(), missing=()):
         self.by_wnid = dict(labels)
         self.calls = []
+        self.marks = {}
+        import importlib
+        svc = importlib.import_module("distributed-machine-learning-cluster_b200.service")
+        for ids, mark in ((skipped, svc.SKIPPED), (undecodable, svc.UNDECODABLE), (missing, svc.MISSING)):
+            for w in ids:
+                self.marks[w] = mark
 
-    def predict(self, model_name, input_ids, k=1, devices=None):
+    def read_ids(self, input_ids):
+        return [self.marks.get(w, b"jpeg bytes of " + w.encode()) for w in input_ids]
+
+    def predict_each(self, model_name, input_ids, k=1, devices=None, blobs=None):
         self.calls.append((model_name, list(input_ids), devices))
+        assert blobs is not None and len(blobs) == len(input_ids)      # run_job fetched the files itself
         if model_name not in ("resnet18", "alexnet"):
             return None
-        return [(0.5, self.by_wnid[w] if int(w[-1]) % 2 == 0 else "wrong") for w in input_ids]
+        return [b if isinstance(b, str) else (0.5, self.by_wnid[w] if int(w[-1]) % 2 == 0 else "wrong")
+                for w, b in zip(input_ids, blobs)]
 
 
 def test_load_labels_follows_reference_parsing(pkg):
@@ -95,3 +107,46 @@ def test_decode_failure_and_unknown_model(pkg, tmp_path):
     assert pkg.decode_image(str(bad)) is None
     with pytest.raises(ValueError):
         pkg.load_model("vgg16")
+
+
+def test_run_job_scores_every_answer_against_its_own_label(pkg):
+    """An empty directory, an undecodable file and a missing directory in the middle of a batch: each is a
+    lost query, as in the reference (one id per RPC, services.rs:421,485-492); the ids after them are still
+    compared with their own labels and the rest of the batch is counted."""
+    labels = pkg.load_labels(os.path.join(GOLDEN, "synset_words.txt"))[:32]
+    lost = [labels[3][0], labels[10][0], labels[17][0]]
+    member = FakeMember(labels, skipped=[lost[0]], undecodable=[lost[1]], missing=[lost[2]])
+    leader = pkg.Leader(member, labels)
+    pkg.assign_members([0, 1], leader.resnet18, leader.alexnet)
+    lines = []
+    leader.run_job(leader.alexnet, batch=32, log=lines.append)
+    assert leader.alexnet.finished_prediction_count == 29
+    answered = [(w, l) for w, l in labels if w not in lost]
+    assert leader.alexnet.correct_prediction_count == sum(1 for w, _ in answered if int(w[-1]) % 2 == 0)
+    # every printed line names the id it belongs to and, when wrong, that id's own label
+    by = dict(labels)
+    for ln in lines:
+        wnid = ln.split(" - ")[1].split(":")[0]
+        assert wnid not in lost
+        if "(should be " in ln:
+            assert ln.endswith("(should be %s)" % by[wnid])
+
+
+def test_member_file_side_markers(pkg, tmp_path):
+    """read_ids: first file of the id's directory as bytes; markers for an empty and a missing directory."""
+    import importlib
+    svc = importlib.import_module("distributed-machine-learning-cluster_b200.service")
+    (tmp_path / "a").mkdir()
+    (tmp_path / "a" / "2.JPEG").write_bytes(b"second")
+    (tmp_path / "a" / "1.JPEG").write_bytes(b"first")
+    (tmp_path / "b").mkdir()
+    m = svc.MemberState.__new__(svc.MemberState)          # file side only: no GPU, no models
+    m.image_root = str(tmp_path)
+    from concurrent.futures import ThreadPoolExecutor
+    m.pool = ThreadPoolExecutor(max_workers=2)
+    assert m.read_ids(["a", "b", "c"]) == [b"first", svc.SKIPPED, svc.MISSING]
+    assert svc.decode_bytes(b"junk") is None and svc.decode_bytes(b"") is None
+    img = svc.decode_bytes(open(os.path.join(GOLDEN, "imagenet_1k", "train", sorted(os.listdir(os.path.join(GOLDEN, "imagenet_1k", "train")))[0],
+                                             sorted(os.listdir(os.path.join(GOLDEN, "imagenet_1k", "train", sorted(os.listdir(os.path.join(GOLDEN, "imagenet_1k", "train")))[0])))[0]), "rb").read())
+    assert img.ndim == 3 and img.shape[2] == 3
+    m.pool.shutdown()
