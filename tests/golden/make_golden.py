@@ -3,7 +3,8 @@
     python tests/golden/make_golden.py
 
 The reference cannot be executed here (Rust + tch, no toolchain, weights are LFS pointers), so
-these vectors freeze the ORACLE's outputs on the committed fixture images with the seeded synthetic
+these vectors freeze the ORACLE's outputs on the committed fixture images (the subset
+select_fixtures.py picks from the reference's test_files/imagenet_1k) with the seeded synthetic
 weights: they pin the oracle, the synthetic-weight generator and the preprocessing restatement
 against drift, and give the GPU tests a fixed target.  Parity with the reference itself stays
 unpinned.
@@ -32,7 +33,9 @@ def fixture_paths():
 
 def main():
     paths = fixture_paths()
-    crops = np.stack([stb_resize.load_image_and_resize(p) for _, p in paths])
+    from concurrent.futures import ProcessPoolExecutor
+    with ProcessPoolExecutor() as ex:
+        crops = np.stack(list(ex.map(stb_resize.load_image_and_resize, [p for _, p in paths])))
     data = {
         "wnids": np.array([w for w, _ in paths]),
         "crop_sha256": np.array([hashlib.sha256(c.tobytes()).hexdigest() for c in crops]),
@@ -46,6 +49,8 @@ def main():
     _, _, data["alexnet_tch_logits"] = tch_oracle.predict_u8("alexnet", aw, crops, alexnet_geometry="tch")
     _, _, data["alexnet_torchvision_logits"] = tch_oracle.predict_u8("alexnet", aw, crops,
                                                                     alexnet_geometry="torchvision")
+    # the same ResNet-18 with logits of pretrained scale (std ~2.5): flat absolute tolerances are checked on it
+    _, _, data["resnet18_ps_logits"] = tch_oracle.predict_u8("resnet18", synth.weights("resnet18_ps"), crops)
     syn = synth.synthetic_images(4, seed=0)
     _, _, data["resnet18_logits_synthetic4"] = tch_oracle.predict_u8("resnet18", rw, syn)
     data["synthetic4_sha256"] = np.array(hashlib.sha256(syn.tobytes()).hexdigest())

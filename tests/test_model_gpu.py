@@ -1,46 +1,44 @@
 """Whole-network parity on the GPU through the C ABI (b2i_model_load / b2i_predict_u8) against the
 oracle and the committed golden vectors: logits, softmax probabilities and top-5 indices, for both
-models, both precisions, both AlexNet geometries, ragged / empty / single-image batches.
+models, three precisions, both AlexNet geometries, ragged / empty / single-image batches.
 
-Tolerances (BASELINE.json north_star): fp32 mode 1e-4 max-abs, bf16 mode 2e-2 max-abs on logits,
-stated for O(1) logits.  The seeded synthetic networks produce logits with std 9.0 (ResNet-18) and
-1.9 (AlexNet), so both bounds are applied in units of max(1, std of the oracle's logits).
+Fixture set: the 120 JPEGs tests/golden/select_fixtures.py picked from the reference's
+test_files/imagenet_1k (every grayscale, every side < 224, every 4:2:2, extreme aspect ratios ...), run at
+the batch sizes BASELINE.json names: ResNet-18 at batch 256 (the set cycled to fill it), AlexNet at batch 32.
+The whole 1000 go through the same checks in tools/parity_1000.py (record under profiles/).
 
-fp32 mode: against the fp32 oracle, 1e-4 units.
+Tolerances (BASELINE.json north_star): fp32 mode 1e-4 max-abs, bf16 mode 2e-2 max-abs on logits.  Both are
+ABSOLUTE figures meant for logits of pretrained scale (standard deviation 2-3).  Two weight sets:
+  * "ps" (oracle.synth resnet18_ps: logits of std 2.5, |max| 13) and AlexNet (std 2.1): the bounds are applied
+    FLAT.  fp32 mode and fp16 mode (PREC_FP16, the tensor-core kernels with IEEE-half storage) meet them;
+    bf16 mode does not and is not claimed to: its distance is printed and bounded by 3 % of the logit std.
+  * the default synthetic ResNet-18 (std 8.9, |max| 47): the bounds are applied in units of the logit std.
 bf16 mode, two separate statements:
   (1) kernel exactness: against the oracle evaluated WITH bf16 storage (oracle.tch_oracle.*_bf16:
-      same roundings, fp32 sums) the gap must be within 2e-2 units -- the BASELINE figure;
+      same roundings, fp32 sums) the gap must be within 2e-2 units;
   (2) cost of the dtype: against the fp32 oracle the kernel may be no further away than 1.25x the
-      distance of that bf16 evaluation itself (measured here 2.2-2.4 % of the logit std, the same
-      2-4 % SURVEY.md Appendix E found for torch's own bf16 CPU path).  A flat 2e-2 against the fp32
-      oracle is not reachable with bf16 activations at these logit scales; DESIGN.md says so.
-fp16 mode (PREC_FP16, the same tensor-core kernels with IEEE-half storage): against the FP32 oracle,
-2e-2 units, outright -- no dtype allowance (measured 0.24 % of the logit std).
-Top-5 indices must be identical wherever the oracle's margin between neighbouring ranks exceeds
-twice the logit tolerance."""
+      distance of that bf16 evaluation itself (measured 2.2-2.4 % of the logit std, the same
+      2-4 % SURVEY.md Appendix E found for torch's own bf16 CPU path).
+Top-5: on every image whose top-1 / top-2 margin exceeds twice the tolerance the top-1 index is identical;
+where the 5th / 6th margin does too, the top-5 SET is identical; where every neighbouring pair among the first
+six is that far apart, the order is identical.  The counts of images passing each filter are printed."""
 import os
 
 import numpy as np
 import pytest
 import torch
 
-from conftest import GOLDEN
+from conftest import GOLDEN, fixture_crops, fixture_paths
 
 pytestmark = pytest.mark.gpu
 
 BF16, FP32, FP16 = 0, 1, 2
 GV = np.load(os.path.join(GOLDEN, "golden_vectors.npz"))
+NFIX = len(GV["wnids"])
 
 
-def fixture_crops():
-    from oracle import stb_resize
-    root = os.path.join(GOLDEN, "imagenet_1k", "train")
-    return np.stack([stb_resize.load_image_and_resize(os.path.join(root, w, sorted(os.listdir(os.path.join(root, w)))[0]))
-                     for w in GV["wnids"]])
-
-
-def tol_for(precision, ref_logits):
-    unit = max(1.0, float(np.std(ref_logits)))
+def tol_for(precision, ref_logits, flat=False):
+    unit = 1.0 if flat else max(1.0, float(np.std(ref_logits)))
     return (1e-4 if precision == FP32 else 2e-2) * unit
 
 
@@ -50,20 +48,46 @@ def bf16_budget(ref_logits):
     return 3e-2 * max(1.0, float(np.std(ref_logits)))
 
 
-def check_against(ref_logits, idx, prob, logits, precision, what, emu_logits=None):
-    tol = tol_for(precision, ref_logits)
+def check_topk(ref_logits, idx, tol, what):
+    """The margin-filtered top-k comparison of the module docstring; returns the filter counts."""
+    order = np.argsort(-ref_logits, axis=1, kind="stable")
+    srt = np.take_along_axis(ref_logits, order, 1)
+    k = idx.shape[1]
+    n1 = nset = nord = 0
+    for r in range(ref_logits.shape[0]):
+        margins = srt[r, :k] - srt[r, 1:k + 1]
+        if margins[0] > 2 * tol:
+            n1 += 1
+            assert idx[r, 0] == order[r, 0], (what, "top-1", r, idx[r], order[r, :k])
+        if margins[k - 1] > 2 * tol:
+            nset += 1
+            assert set(idx[r].tolist()) == set(order[r, :k].tolist()), (what, "top-%d set" % k, r, idx[r], order[r, :k])
+        if (margins > 2 * tol).all():
+            nord += 1
+            assert np.array_equal(idx[r], order[r, :k]), (what, "order", r, idx[r], order[r, :k])
+    print("%s: of %d images, top-1 compared on %d, top-%d set on %d, full order on %d (margin > %.3e): all identical" %
+          (what, ref_logits.shape[0], n1, k, nset, nord, 2 * tol))
+    return n1, nset, nord
+
+
+def check_against(ref_logits, idx, prob, logits, precision, what, emu_logits=None, flat=False):
+    tol = tol_for(precision, ref_logits, flat)
     gap = float(np.abs(logits - ref_logits).max())
-    print("%s: logits max-abs gap vs fp32 oracle %.3e (2e-2/1e-4 unit bound %.3e, oracle logit std %.3f, absmax %.3f)" %
-          (what, gap, tol, np.std(ref_logits), np.abs(ref_logits).max()))
+    std = float(np.std(ref_logits))
+    print("%s: logits max-abs gap vs fp32 oracle %.3e absolute = %.3f %% of the logit std %.3f (|max| %.2f); bound %.3e %s" %
+          (what, gap, 100.0 * gap / std, std, np.abs(ref_logits).max(), tol, "FLAT" if flat else "in units of max(1, std)"))
     if precision == FP32 or precision == FP16:
         # fp16 storage (11-bit significands) meets the 2e-2 bar against the fp32 oracle OUTRIGHT, no dtype allowance
         assert gap <= tol, what
     else:
+        tol = tol_for(precision, ref_logits, False)       # bf16 storage: never claimed flat
         gap_emu = float(np.abs(logits - emu_logits).max())
         emu_vs_fp32 = float(np.abs(emu_logits - ref_logits).max())
-        print("%s: vs bf16-evaluated oracle %.3e (bound %.3e); that oracle vs fp32 oracle %.3e" % (what, gap_emu, tol, emu_vs_fp32))
+        print("%s: vs bf16-evaluated oracle %.3e (bound %.3e); that oracle vs fp32 oracle %.3e; flat 2e-2 vs fp32 oracle: %s" %
+              (what, gap_emu, tol, emu_vs_fp32, "met" if gap <= 2e-2 else "NOT met (bf16 storage)"))
         assert gap_emu <= tol, what                       # (1) kernel exactness
         assert gap <= 1.25 * emu_vs_fp32 + 1e-3, what    # (2) no worse than bf16 storage itself
+        assert gap <= bf16_budget(ref_logits), what
         tol = max(tol, 1.25 * emu_vs_fp32)                # rank comparisons below use the dtype's real budget
     # softmax + top-5 of the kernel's own logits must be what torch computes from them
     t = torch.from_numpy(logits)
@@ -71,41 +95,70 @@ def check_against(ref_logits, idx, prob, logits, precision, what, emu_logits=Non
     pv, pi = torch.topk(p, idx.shape[1], -1)
     assert np.abs(prob - pv.numpy()).max() <= 1e-5
     # top-k indices vs the ORACLE's logits wherever ranks are separated by more than the tolerance
-    order = np.argsort(-ref_logits, axis=1)
-    srt = np.take_along_axis(ref_logits, order, 1)
-    k = idx.shape[1]
-    for r in range(ref_logits.shape[0]):
-        margins = srt[r, :k] - srt[r, 1:k + 1]
-        if (margins > 2 * tol).all():
-            assert np.array_equal(idx[r], order[r, :k]), (what, r, idx[r], order[r, :k])
+    n1, nset, nord = check_topk(ref_logits, idx, tol, what)
+    assert n1 >= ref_logits.shape[0] // 2, (what, "the margin filter left too little to compare", n1)
+
+
+def resnet18_batch256(crops):
+    """BASELINE.json configs[1]: ResNet-18 at batch 256 -- the fixture set cycled to fill the batch."""
+    rep = np.resize(np.arange(len(crops)), 256)
+    return crops[rep], rep
 
 
 @pytest.mark.parametrize("precision", [BF16, FP32, FP16], ids=["bf16", "fp32", "fp16"])
 def test_resnet18_fixture_images_match_golden(pkg, ctx, resnet18_ot, precision):
     crops = fixture_crops()
-    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=precision, max_batch=8) as m:
-        idx, prob, logits = m.predict_u8(crops, k=5, want_logits=True)
+    batch, rep = resnet18_batch256(crops)
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=precision, max_batch=256) as m:
+        idx, prob, logits = m.predict_u8(batch, k=5, want_logits=True)
+    # a repeated image gets the same answer wherever it sits in the batch
+    assert np.array_equal(logits[NFIX:], logits[rep[NFIX:]])
+    idx, prob, logits = idx[:NFIX], prob[:NFIX], logits[:NFIX]
     emu = None
     if precision == BF16:
         from oracle import synth, tch_oracle
         with torch.no_grad():
             emu = tch_oracle.resnet18_forward_bf16(synth.resnet18_weights(), crops).numpy()
-    check_against(GV["resnet18_logits"], idx, prob, logits, precision, "resnet18 fixtures", emu)
+    check_against(GV["resnet18_logits"], idx, prob, logits, precision, "resnet18 fixtures bs256", emu)
+
+
+@pytest.mark.parametrize("precision", [BF16, FP32, FP16], ids=["bf16", "fp32", "fp16"])
+def test_resnet18_pretrained_scale_logits_flat_bounds(pkg, ctx, resnet18_ps_ot, precision):
+    """The north-star tolerances as written -- max-abs 2e-2 (16-bit modes) / 1e-4 (fp32 mode), no scaling --
+    on the weight set whose logits have pretrained scale.  fp32 and fp16 modes must meet them; for bf16 the
+    absolute gap is printed and held to 3 % of the logit std (it does not meet a flat 2e-2: 8 mantissa bits)."""
+    crops = fixture_crops()
+    batch, rep = resnet18_batch256(crops)
+    with pkg.Model(ctx, "resnet18", resnet18_ps_ot, precision=precision, max_batch=256) as m:
+        idx, prob, logits = m.predict_u8(batch, k=5, want_logits=True)
+    idx, prob, logits = idx[:NFIX], prob[:NFIX], logits[:NFIX]
+    emu = None
+    if precision == BF16:
+        from oracle import synth, tch_oracle
+        with torch.no_grad():
+            emu = tch_oracle.resnet18_forward_bf16(synth.weights("resnet18_ps"), crops).numpy()
+    check_against(GV["resnet18_ps_logits"], idx, prob, logits, precision, "resnet18 (pretrained-scale logits) bs256", emu,
+                  flat=True)
 
 
 @pytest.mark.parametrize("geometry", [0, 1], ids=["tch", "torchvision"])
 @pytest.mark.parametrize("precision", [BF16, FP32, FP16], ids=["bf16", "fp32", "fp16"])
 def test_alexnet_fixture_images_match_golden(pkg, ctx, alexnet_ot, precision, geometry):
+    """BASELINE.json configs[0]: AlexNet at batch 32 (three full batches and one of 24); AlexNet's synthetic
+    logits have std 2.1, so the bounds are the flat ones."""
     crops = fixture_crops()
-    with pkg.Model(ctx, "alexnet", alexnet_ot, precision=precision, max_batch=8, alexnet_geometry=geometry) as m:
-        idx, prob, logits = m.predict_u8(crops, k=5, want_logits=True)
+    outs = []
+    with pkg.Model(ctx, "alexnet", alexnet_ot, precision=precision, max_batch=32, alexnet_geometry=geometry) as m:
+        for lo in range(0, NFIX, 32):
+            outs.append(m.predict_u8(crops[lo:lo + 32], k=5, want_logits=True))
+    idx, prob, logits = (np.concatenate([o[j] for o in outs]) for j in range(3))
     ref = GV["alexnet_tch_logits" if geometry == 0 else "alexnet_torchvision_logits"]
     emu = None
     if precision == BF16:
         from oracle import synth, tch_oracle
         with torch.no_grad():
             emu = tch_oracle.alexnet_forward_bf16(synth.alexnet_weights(), crops, "tch" if geometry == 0 else "torchvision").numpy()
-    check_against(ref, idx, prob, logits, precision, "alexnet fixtures geometry %d" % geometry, emu)
+    check_against(ref, idx, prob, logits, precision, "alexnet fixtures bs32 geometry %d" % geometry, emu, flat=True)
 
 
 @pytest.mark.parametrize("conv_mode", [0, 1], ids=["gather", "im2col"])
@@ -290,12 +343,13 @@ def test_predict_raw_equals_resize_then_predict(pkg, ctx, resnet18_ot):
     """b2i_predict_raw_u8 (decoded images of any size in, top-k out) is bit-identical to
     b2i_resize_crop_u8 per image followed by b2i_predict_u8, on fixture JPEGs and synthetic sizes."""
     from oracle import stb_resize
-    root = os.path.join(GOLDEN, "imagenet_1k", "train")
-    imgs = [stb_resize.decode_image(os.path.join(root, w, sorted(os.listdir(os.path.join(root, w)))[0])) for w in GV["wnids"]]
+    imgs = [stb_resize.decode_image(p) for _, p in fixture_paths()]
     rng = np.random.default_rng(5)
     imgs += [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in ((224, 224), (90, 301), (640, 480))]
-    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=16, micro_batch=4) as m:
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=128, micro_batch=32) as m:
         crops = np.stack([ctx.resize_crop(im) for im in imgs])
+        # the GPU resize + crop of every fixture is the oracle's, bit for bit
+        assert np.array_equal(crops[:NFIX], fixture_crops())
         want = m.predict_u8(crops, k=5, want_logits=True)
         got = m.predict_raw(imgs, k=5, want_logits=True)
         for a, b in zip(got, want):
@@ -351,12 +405,12 @@ def test_member_predict_mirrors_reference_semantics(pkg, ctx, resnet18_ot, alexn
     os.symlink(resnet18_ot, wd / "resnet18.ot")
     os.symlink(alexnet_ot, wd / "alexnet.ot")
     root = os.path.join(GOLDEN, "imagenet_1k", "train")
-    member = pkg.MemberState(ctx, labels, weight_dir=str(wd), image_root=root, max_batch=8)
+    member = pkg.MemberState(ctx, labels, weight_dir=str(wd), image_root=root, max_batch=128, decoder="pil")
     try:
         assert member.predict("vgg16", ["n01491361"]) is None
         ids = list(GV["wnids"])
         res = member.predict("resnet18", ids)
-        assert len(res) == 8 and all(0.0 < p <= 1.0 and isinstance(lbl, str) for p, lbl in res)
+        assert len(res) == NFIX and all(0.0 < p <= 1.0 and isinstance(lbl, str) for p, lbl in res)
         top1 = np.argmax(GV["resnet18_logits"], 1)
         srt = np.sort(GV["resnet18_logits"], 1)
         for i, (p, lbl) in enumerate(res):
@@ -383,9 +437,123 @@ def test_member_predict_mirrors_reference_semantics(pkg, ctx, resnet18_ot, alexn
         assert leader.resnet18.assigned_member_ids == [] and leader.alexnet.assigned_member_ids == [0]
         leader.run_job(leader.resnet18, batch=4)                 # nobody assigned: labels skipped, nothing counted
         assert leader.resnet18.finished_prediction_count == 0
-        leader.run_job(leader.alexnet, batch=3)
-        assert leader.alexnet.finished_prediction_count == 8 and len(leader.alexnet.query_durations) == 8
+        leader.run_job(leader.alexnet, batch=32)
+        assert leader.alexnet.finished_prediction_count == NFIX and len(leader.alexnet.query_durations) == NFIX
         rep = pkg.jobs_report(leader.alexnet)
-        assert rep["total"] == 8 and rep["p99_ms"] >= rep["median_ms"]
+        assert rep["total"] == NFIX and rep["p99_ms"] >= rep["median_ms"]
     finally:
         member.close()
+
+
+def test_one_bad_image_costs_one_answer_not_the_batch(pkg, ctx, resnet18_ot, tmp_path):
+    """b2i_predict_raw_u8_status: a batch of 8 with one undecoded image (NULL) gives 7 answers, bit-identical
+    to the same 7 images alone, and one B2I_EDECODE status.  Above the ABI, MemberState.predict_each keeps the
+    ids aligned when an empty directory, an undecodable file and a missing directory sit in the middle of a
+    batch, and Leader.run_job scores the survivors against their own labels (reference: one id per RPC,
+    services.rs:421,485-492)."""
+    import importlib
+    import shutil
+    from oracle import stb_resize
+    svc = importlib.import_module("distributed-machine-learning-cluster_b200.service")
+    paths = fixture_paths()[:8]
+    imgs = [stb_resize.decode_image(p) for _, p in paths]
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=8) as m:
+        holed = list(imgs)
+        holed[3] = None
+        idx, prob, logits, status = m.predict_raw_status(holed, k=5, want_logits=True)
+        assert status.tolist() == [0, 0, 0, pkg._lib.EDECODE, 0, 0, 0, 0]
+        assert (idx[3] == -1).all() and (prob[3] == 0).all()
+        alone = m.predict_raw(imgs[:3] + imgs[4:], k=5, want_logits=True)
+        keep = [0, 1, 2, 4, 5, 6, 7]
+        assert np.array_equal(idx[keep], alone[0]) and np.array_equal(logits[keep], alone[2])
+        i2, p2, st2 = m.predict_raw_status([None, None], k=1)
+        assert st2.tolist() == [pkg._lib.EDECODE] * 2 and (i2 == -1).all()
+    labels = pkg.load_labels(os.path.join(GOLDEN, "synset_words.txt"))
+    by = dict(labels)
+    root = tmp_path / "train"
+    ids = []
+    for j, (wnid, path) in enumerate(paths):
+        (root / wnid).mkdir(parents=True)
+        shutil.copy(path, root / wnid / os.path.basename(path))
+        ids.append(wnid)
+    (root / "n_empty").mkdir()
+    (root / "n_bad").mkdir()
+    (root / "n_bad" / "x.JPEG").write_bytes(b"\xff\xd8 not really a jpeg")
+    ids = ids[:2] + ["n_empty"] + ids[2:4] + ["n_bad"] + ids[4:6] + ["n_gone"] + ids[6:]
+    wd = tmp_path / "pretrained_models"
+    wd.mkdir()
+    os.symlink(resnet18_ot, wd / "resnet18.ot")
+    for decoder in ("pil", "auto"):
+        member = pkg.MemberState(ctx, labels, weight_dir=str(wd), image_root=str(root), max_batch=16, models=("resnet18",),
+                                 decoder=decoder)
+        try:
+            each = member.predict_each("resnet18", ids)
+            assert [e if isinstance(e, str) else "ok" for e in each] == \
+                ["ok", "ok", svc.SKIPPED, "ok", "ok", svc.UNDECODABLE, "ok", "ok", svc.MISSING, "ok", "ok"], (decoder, each)
+            clean = member.predict_each("resnet18", [w for w, _ in paths])
+            if member.decoder == "pil":       # same decoder, same pixels: the answers do not depend on the neighbours
+                assert [e for e in each if not isinstance(e, str)] == clean
+            assert member.predict("resnet18", ids[:5]) == [e for e in each[:5] if not isinstance(e, str)]
+            assert member.predict("resnet18", ids[:6]) is None          # reference semantics of the plain handler
+            leader = pkg.Leader(member, [(w, by.get(w, "?")) for w in ids])
+            pkg.assign_members([0, 0], leader.resnet18, leader.alexnet)
+            leader.alexnet.assigned_member_ids = []
+            leader.resnet18.assigned_member_ids = [0]
+            lines = []
+            leader.run_job(leader.resnet18, batch=11, log=lines.append)
+            assert leader.resnet18.finished_prediction_count == 8
+            want_correct = sum(1 for (w, _), e in zip(paths, clean) if e[1] == by[w])
+            if member.decoder == "pil":
+                assert leader.resnet18.correct_prediction_count == want_correct
+            assert all(ln.split(" - ")[1].split(":")[0] in by for ln in lines)
+        finally:
+            member.close()
+
+
+def test_predict_jpeg_decodes_on_the_gpu(pkg, ctx, resnet18_ot):
+    """b2i_predict_jpeg: encoded streams in, top-k out.  Decoders differ by a few LSB, so
+    the pixels the GPU decoder produced are read back (b2i_jpeg_decode_u8) and THOSE go through the oracle's
+    resize and through b2i_predict_u8: the JPEG path must equal that bit for bit, and sit within the bf16
+    budget of the fp32 oracle on the same pixels.  A damaged stream costs its own answer only."""
+    from oracle import stb_resize, synth, tch_oracle
+    try:
+        backend = ctx.jpeg_backend()
+    except pkg.B2IError as e:
+        if e.code == pkg._lib.ENODEV and "not installed" in str(e):
+            pytest.skip("nvJPEG is not installed on this box")
+        raise
+    print("nvJPEG backends:", backend)
+    rows = [ln.rstrip("\n").split("\t") for ln in open(os.path.join(GOLDEN, "fixtures_manifest.tsv"))][1:]
+    kind = {r[0]: r[7] for r in rows}
+    paths = fixture_paths()
+    pick = []
+    for want in ("grayscale", "side < 224", "4:2:2", "4:2:0", "widest", "tallest", "square", "ordinary"):
+        pick += [p for p in paths if kind[p[0]].startswith(want)][:3]
+    blobs = [open(p, "rb").read() for _, p in pick]
+    pix = [ctx.jpeg_decode(b) for b in blobs]
+    ref = [stb_resize.decode_image(p) for _, p in pick]
+    worst = 0
+    for a, b, (w, _) in zip(pix, ref, pick):
+        assert a.shape == b.shape, (w, a.shape, b.shape)
+        d = np.abs(a.astype(int) - b.astype(int))
+        worst = max(worst, int(d.max()))
+        assert d.mean() < 1.5, (w, kind[w], float(d.mean()))          # same picture, decoder-level differences only
+    print("GPU decoder vs libjpeg (PIL) on %d fixtures: max |diff| %d LSB" % (len(pick), worst))
+    crops = np.stack([stb_resize.resize_crop_224(p) for p in pix])
+    with pkg.Model(ctx, "resnet18", resnet18_ot, precision=BF16, max_batch=32) as m:
+        want = m.predict_u8(crops, k=5, want_logits=True)
+        idx, prob, logits, status = m.predict_jpeg(blobs, k=5, want_logits=True)
+        assert (status == 0).all()
+        assert np.array_equal(logits, want[2]) and np.array_equal(idx, want[0]) and np.array_equal(prob, want[1])
+        _, _, oracle_logits = tch_oracle.predict_u8("resnet18", synth.resnet18_weights(), crops)
+        assert np.abs(logits - oracle_logits).max() <= bf16_budget(oracle_logits)
+        # damaged / missing streams in the middle of a batch
+        broken = list(blobs[:6])
+        broken[1] = b"\xff\xd8\xff\xe0 this is not a jpeg stream"
+        broken[4] = b""
+        i2, p2, l2, st2 = m.predict_jpeg(broken, k=5, want_logits=True)
+        assert st2.tolist() == [0, pkg._lib.EDECODE, 0, 0, pkg._lib.EDECODE, 0]
+        keep = [0, 2, 3, 5]
+        assert np.array_equal(l2[keep], logits[keep]) and (i2[[1, 4]] == -1).all()
+        assert m.predict_jpeg([], k=5)[0].shape == (0, 5)
+

@@ -8,16 +8,10 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import GOLDEN
+from conftest import GOLDEN, fixture_crops
 from oracle import stb_resize, synth, tch_oracle
 
 GV = np.load(os.path.join(GOLDEN, "golden_vectors.npz"))
-
-
-def fixture_crops():
-    root = os.path.join(GOLDEN, "imagenet_1k", "train")
-    return np.stack([stb_resize.load_image_and_resize(os.path.join(root, w, sorted(os.listdir(os.path.join(root, w)))[0]))
-                     for w in GV["wnids"]])
 
 
 def test_resnet18_graph_matches_torchvision():
@@ -130,10 +124,47 @@ def test_golden_vectors_still_reproduce():
     assert [hashlib.sha256(c.tobytes()).hexdigest() for c in crops] == list(GV["crop_sha256"])
     i = list(GV["wnids"]).index("n03825788")
     assert np.array_equal(crops[i], GV["crop_n03825788"])
-    _, _, lg = tch_oracle.predict_u8("resnet18", synth.resnet18_weights(), crops)
-    assert np.allclose(lg, GV["resnet18_logits"], rtol=0, atol=2e-4 * np.abs(lg).max())
+    sel = list(range(0, len(crops), 9))                      # a spread of the set keeps the CPU suite short
+    _, _, lg = tch_oracle.predict_u8("resnet18", synth.resnet18_weights(), crops[sel])
+    assert np.allclose(lg, GV["resnet18_logits"][sel], rtol=0, atol=2e-4 * np.abs(lg).max())
+    _, _, lp = tch_oracle.predict_u8("resnet18", synth.weights("resnet18_ps"), crops[sel])
+    assert np.allclose(lp, GV["resnet18_ps_logits"][sel], rtol=0, atol=2e-4 * np.abs(lp).max())
+    assert 2.0 < float(GV["resnet18_ps_logits"].std()) < 3.0    # "pretrained scale": what flat tolerances assume
     _, _, la = tch_oracle.predict_u8("alexnet", synth.alexnet_weights(), crops[:3], alexnet_geometry="tch")
     assert np.allclose(la, GV["alexnet_tch_logits"][:3], rtol=0, atol=2e-4 * np.abs(la).max())
+
+
+def test_fixture_set_covers_the_input_classes_of_the_reference_set():
+    """The committed subset holds every kind of file SURVEY.md section 4 found among the reference's 1000:
+    grayscale, sides under 224 (up-sampling), 4:2:2 and 4:2:0 chroma, extreme aspect ratios, squares."""
+    rows = [ln.rstrip("\n").split("\t") for ln in open(os.path.join(GOLDEN, "fixtures_manifest.tsv"))][1:]
+    assert len(rows) == len(GV["wnids"]) >= 100
+    w = np.array([int(r[2]) for r in rows]); h = np.array([int(r[3]) for r in rows])
+    gray = np.array([int(r[4]) for r in rows]); samp = np.array([int(r[5]) for r in rows])
+    assert gray.sum() >= 19 and (np.minimum(w, h) < 224).sum() >= 18
+    assert (samp == 1).sum() >= 9 and (samp == 2).sum() >= 10
+    assert w.max() == 2304 and h.max() == 2877 and (w == h).sum() >= 6
+    assert (w / h).max() > 2.5 and (h / w).max() > 2.0
+
+
+def test_real_weight_hook_authenticates_by_size_and_sha256(tmp_path):
+    """oracle.synth.real_weights: only a file with the LFS pointer's size and sha256 is taken (reference
+    pretrained_models/*.ot:2-3); pointers, truncated files and other weights are ignored."""
+    assert synth.LFS["resnet18"] == ("f349134076ce5f2dc50f1003b798fe068c7ab0695c757450723d259441b20ebb", 46831783)
+    assert synth.LFS["alexnet"] == ("8fb43520a45c164aba438753cdc5fd4b6f5c5dd5436db6d69efdf1e5532ff0e8", 244408272)
+    (tmp_path / "resnet18.ot").write_text("version https://git-lfs.github.com/spec/v1\noid sha256:f349\nsize 46831783\n")
+    assert synth.real_weights("resnet18", [str(tmp_path)]) is None
+    blob = b"x" * 1000
+    import hashlib
+    saved = dict(synth.LFS)
+    try:
+        synth.LFS["resnet18"] = (hashlib.sha256(blob).hexdigest(), len(blob))
+        (tmp_path / "resnet18.ot").write_bytes(blob)
+        assert synth.real_weights("resnet18", [str(tmp_path)]) == str(tmp_path / "resnet18.ot")
+        (tmp_path / "resnet18.ot").write_bytes(b"y" * 1000)          # right size, wrong content
+        assert synth.real_weights("resnet18", [str(tmp_path)]) is None
+    finally:
+        synth.LFS.update(saved)
 
 
 def test_unknown_model_is_an_error():

@@ -43,3 +43,24 @@ def test_static_scratch_refuses_images_beyond_its_limit(pkg, ctx):
     # the entry point is still usable afterwards
     ok = np.full((300, 300, 3), 9, np.uint8)
     assert np.array_equal(run_static(ctx, ok), ctx.resize_crop(ok))
+
+
+def test_static_scratch_refuses_a_capturing_stream(pkg, ctx):
+    """The resampling plans are per image and are uploaded from host memory that does not outlive the call,
+    so the entry point declines to be recorded into a CUDA graph (B2I_EINVAL) and keeps working afterwards."""
+    img = np.full((300, 260, 3), 200, np.uint8)
+    d_in = torch.from_numpy(img).cuda()
+    d_out = torch.zeros((224, 224, 3), dtype=torch.uint8, device="cuda")
+    run_static(ctx, img)                       # the address look-up of the first call happens outside any capture
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    refused = None
+    with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
+        try:
+            ctx.resize_crop_static(d_in.data_ptr(), 300, 260, d_out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        except pkg.B2IError as e:
+            refused = e
+        d_out.add_(0)                          # the capture itself stays valid
+    assert refused is not None and refused.code == -1 and "captur" in str(refused)
+    torch.cuda.synchronize()
+    assert np.array_equal(run_static(ctx, img), ctx.resize_crop(img))
