@@ -7,6 +7,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <map>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -66,6 +69,67 @@ Api* api() {
   return &a;
 }
 
+// nvJPEG sizes its work buffers per batch and, left to itself, gets them from cudaMalloc / cudaFree -- both
+// synchronise the device, once or more per call.  These two allocators keep every block they were ever
+// asked for on a free list (per process, never shrinking: a decoder's working set is a few hundred MB
+// at most) and hand back the smallest block that fits.
+struct BlockPool {
+  std::mutex mu;
+  std::multimap<size_t, void*> free_blocks;
+  std::map<void*, size_t> live;
+  bool pinned = false;
+  int get(void** p, size_t bytes) {
+    if (bytes == 0) bytes = 256;
+    {
+      std::lock_guard<std::mutex> lock(mu);
+      auto it = free_blocks.lower_bound(bytes);
+      if (it != free_blocks.end() && it->first <= 2 * bytes + (1u << 20)) {
+        *p = it->second;
+        live[*p] = it->first;
+        free_blocks.erase(it);
+        return 0;
+      }
+    }
+    const size_t cap = (bytes + (bytes >> 2) + 65535) & ~static_cast<size_t>(65535);   // room to grow without a new block
+    cudaError_t e = pinned ? cudaHostAlloc(p, cap, cudaHostAllocDefault) : cudaMalloc(p, cap);
+    if (e != cudaSuccess) { cudaGetLastError(); *p = nullptr; return static_cast<int>(e); }
+    std::lock_guard<std::mutex> lock(mu);
+    live[*p] = cap;
+    return 0;
+  }
+  int put(void* p) {
+    if (!p) return 0;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = live.find(p);
+    if (it == live.end()) return 0;
+    free_blocks.emplace(it->second, p);
+    live.erase(it);
+    return 0;
+  }
+};
+BlockPool* dev_pool(int device) {   // one free list per GPU
+  static BlockPool pools[64];
+  return &pools[device & 63];
+}
+BlockPool* pin_pool() {
+  static BlockPool p;
+  p.pinned = true;
+  return &p;
+}
+int pool_dev_malloc(void** p, size_t n) {
+  int d = 0;
+  cudaGetDevice(&d);
+  return dev_pool(d)->get(p, n);
+}
+int pool_dev_free(void* p) {
+  if (!p) return 0;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return dev_pool(a.device)->put(p);   // back onto the list of the GPU that owns the block
+}
+int pool_pin_malloc(void** p, size_t n, unsigned int) { return pin_pool()->get(p, n); }
+int pool_pin_free(void* p) { return pin_pool()->put(p); }
+
 struct Engine {
   nvjpegHandle_t handle = nullptr;
   nvjpegJpegState_t state = nullptr;
@@ -73,7 +137,10 @@ struct Engine {
 };
 
 bool engine_open(Api* a, nvjpegBackend_t backend, Engine* e) {
-  if (a->nvjpegCreateEx(backend, nullptr, nullptr, 0, &e->handle) != NVJPEG_STATUS_SUCCESS) {
+  static nvjpegDevAllocator_t dev_alloc = {pool_dev_malloc, pool_dev_free};
+  static nvjpegPinnedAllocator_t pin_alloc = {pool_pin_malloc, pool_pin_free};
+  static const bool pooled = [] { const char* v = std::getenv("B2I_JPEG_NO_POOL"); return !(v && v[0] == '1'); }();
+  if (a->nvjpegCreateEx(backend, pooled ? &dev_alloc : nullptr, pooled ? &pin_alloc : nullptr, 0, &e->handle) != NVJPEG_STATUS_SUCCESS) {
     e->handle = nullptr;
     cudaGetLastError();
     return false;
@@ -120,11 +187,11 @@ JpegDecoder* jpeg_decoder_create(std::string* err) {
   if (w.empty() || w == "gpu") engine_open(a, NVJPEG_BACKEND_GPU_HYBRID, &d->gpu);
   if (a->nvjpegJpegStreamCreate(d->cpu.handle, &d->parsed) != NVJPEG_STATUS_SUCCESS) d->parsed = nullptr;
   cudaGetDevice(&d->device);
-  // helper engines for the images no batched engine takes: B2I_JPEG_THREADS (default: half the host's
-  // hardware threads, at most 16; all of that work when neither batched engine opened)
+  // helper engines for the images no batched engine takes: B2I_JPEG_THREADS (default: the host's hardware
+  // threads, at most 32)
   const char* te = std::getenv("B2I_JPEG_THREADS");
-  int threads = te ? std::atoi(te) : static_cast<int>(std::thread::hardware_concurrency() / 2);
-  threads = threads < 1 ? 1 : (threads > 16 ? 16 : threads);
+  int threads = te ? std::atoi(te) : static_cast<int>(std::thread::hardware_concurrency());
+  threads = threads < 1 ? 1 : (threads > 32 ? 32 : threads);
   for (int t = 1; t < threads; ++t) {
     Engine e;
     if (!engine_open(a, NVJPEG_BACKEND_HYBRID, &e)) break;
@@ -170,6 +237,8 @@ bool jpeg_decode_batch(JpegDecoder* d, const uint8_t* const* data, const size_t*
                        uint8_t* const* d_out, const int* h, const int* w, int* status, cudaStream_t st,
                        std::string* err) {
   Api* a = api();
+  static const bool trace = [] { const char* e = std::getenv("B2I_TRACE"); return e && e[0] == '1'; }();
+  const auto t0 = std::chrono::steady_clock::now();
   // route every image to the first engine that accepts its coding
   std::vector<int> to_hw, to_gpu, to_cpu;
   for (int i = 0; i < n; ++i) {
@@ -210,8 +279,11 @@ bool jpeg_decode_batch(JpegDecoder* d, const uint8_t* const* data, const size_t*
       to_cpu.insert(to_cpu.end(), set.begin(), set.end());
     }
   };
+  const auto t1 = std::chrono::steady_clock::now();
+  const size_t n_hw = to_hw.size(), n_gpu = to_gpu.size(), n_cpu0 = to_cpu.size();
   batched(d->hw, to_hw);
   batched(d->gpu, to_gpu);
+  const auto t2 = std::chrono::steady_clock::now();
   auto one_by_one = [&](Engine& e, size_t first, size_t step) {
     for (size_t j = first; j < to_cpu.size(); j += step) {
       const int i = to_cpu[j];
@@ -234,6 +306,14 @@ bool jpeg_decode_batch(JpegDecoder* d, const uint8_t* const* data, const size_t*
       th.emplace_back([&, t, dev] { cudaSetDevice(dev); one_by_one(d->pool[t], t + 1, helpers + 1); });
     one_by_one(d->cpu, 0, helpers + 1);
     for (auto& x : th) x.join();
+  }
+  if (trace) {
+    const auto t3 = std::chrono::steady_clock::now();
+    auto ms = [](std::chrono::steady_clock::time_point x, std::chrono::steady_clock::time_point y) {
+      return std::chrono::duration<double, std::milli>(y - x).count();
+    };
+    std::fprintf(stderr, "[b2i trace] jpeg decode of %d: routing %.2f ms; batched (%zu hardware, %zu gpu) %.2f ms; per image (%zu, of which %zu fell back) %.2f ms on %zu thread(s)\n",
+                 n, ms(t0, t1), n_hw, n_gpu, ms(t1, t2), to_cpu.size(), to_cpu.size() - n_cpu0, ms(t2, t3), helpers + 1);
   }
   (void)err;
   (void)h;

@@ -2,6 +2,9 @@
 #include "predict.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -280,6 +283,19 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
     return true;
   };
   if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
+  // B2I_TRACE=1: wall time of every host-side stage of this call on stderr (where does a batch from files go?)
+  static const bool trace = [] { const char* e = getenv("B2I_TRACE"); return e && e[0] == '1'; }();
+  using clk = std::chrono::steady_clock;
+  auto t_last = clk::now();
+  std::string tr;
+  auto stamp = [&](const char* what) {
+    if (!trace) return;
+    const auto now = clk::now();
+    char b[64];
+    snprintf(b, sizeof b, " %s %.2f ms;", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+    tr += b;
+    t_last = now;
+  };
   Lane& L = s.lane[0];
   RawScratch& R = s.raw;
   std::vector<int> hbuf, wbuf, stbuf;
@@ -295,17 +311,31 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
     jpeg_probe(s.jpeg, jpeg, jpeg_len, n, hbuf.data(), wbuf.data(), status);
     hs = hbuf.data();
     ws = wbuf.data();
+    stamp("header probe");
   }
   auto usable = [&](int i) { return jpeg ? status[i] == B2I_OK : true; };
   std::vector<AxisPlan> px(n), py(n);
   std::vector<size_t> img_off(n), tab_off(n);
   size_t img_bytes = 0, tab_bytes = 0, tmp_elems = 0;
+  for (int i = 0; i < n; ++i)
+    if (usable(i) && !jpeg && (!images[i] || hs[i] < 1 || ws[i] < 1)) { out->rc = B2I_EINVAL; out->err = "image " + std::to_string(i) + " is empty"; return; }
+  {
+    // the resampling plans are independent per image: a few helper threads for a large batch
+    const int nt = n >= 32 ? std::min<int>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    auto plan_range = [&](int t) {
+      for (int i = t; i < n; i += nt)
+        if (usable(i)) plan_image(hs[i], ws[i], &px[i], &py[i]);
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(plan_range, t);
+    plan_range(0);
+    for (auto& x : th) x.join();
+  }
+  stamp("resampling plans");
   for (int i = 0; i < n; ++i) {
     img_off[i] = img_bytes;
     tab_off[i] = tab_bytes;
     if (!usable(i)) continue;
-    if (!jpeg && (!images[i] || hs[i] < 1 || ws[i] < 1)) { out->rc = B2I_EINVAL; out->err = "image " + std::to_string(i) + " is empty"; return; }
-    plan_image(hs[i], ws[i], &px[i], &py[i]);
     img_off[i] = img_bytes;
     img_bytes += (static_cast<size_t>(hs[i]) * ws[i] * 3 + 255) & ~static_cast<size_t>(255);
     tab_off[i] = tab_bytes;
@@ -343,13 +373,16 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
   if (jpeg) {
     std::vector<uint8_t*> dst(n);
     for (int i = 0; i < n; ++i) dst[i] = R.d_jimg + img_off[i];
+    stamp("tables");
     if (!jpeg_decode_batch(s.jpeg, jpeg, jpeg_len, n, dst.data(), hs, ws, status, s.comp_st, &out->err)) { out->rc = B2I_ECUDA; return; }
+    stamp("decode (host side)");
   } else if (cu(cudaMemcpyAsync(R.d_img, R.h_img, img_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D raw images")) {
     return;
   }
   if (cu(cudaMemcpyAsync(R.d_tab, R.h_tab, tab_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D resize tables")) return;
   for (int i = 0; i < n; ++i)
     if (usable(i) && cu(launch_resize_job(jobs[i], s.comp_st), "resize kernels")) return;
+  stamp("resize launches");
   const int classes = s.dm->classes();
   if (logits && !L.d_logits) {
     const size_t cap = static_cast<size_t>(s.dm->max_batch());
@@ -369,7 +402,10 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
   if (cu(cudaMemcpyAsync(L.h_idx, L.d_idx, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H idx")) return;
   if (cu(cudaMemcpyAsync(L.h_prob, L.d_prob, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H prob")) return;
   if (logits && cu(cudaMemcpyAsync(L.h_logits, L.d_logits, static_cast<size_t>(n) * classes * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H logits")) return;
+  stamp("forward launches");
   if (cu(cudaStreamSynchronize(s.comp_st), "cudaStreamSynchronize")) return;
+  stamp("wait for the GPU");
+  if (trace) fprintf(stderr, "[b2i trace] %s shard of %d on GPU %d:%s\n", jpeg ? "jpeg" : "raw", n, s.dm->device(), tr.c_str());
   std::memcpy(idx, L.h_idx, nk * 4);
   std::memcpy(prob, L.h_prob, nk * 4);
   if (logits) std::memcpy(logits, L.h_logits, static_cast<size_t>(n) * classes * 4);

@@ -17,16 +17,20 @@ __device__ __forceinline__ void tma4d(uint32_t dst, const CUtensorMap* tm, uint3
 }
 
 // mode 0/1: im2col (tm), 2/3: pixel rows (tm, rows_per_tile loads of row_px pixels), 4: 2-D weights
-__global__ void __launch_bounds__(32, 1) rate_kernel(const __grid_constant__ CUtensorMap tm, int mode, int iters, int H, int W, int OH, int OW,
-                                                      int stride, int cslices, int nimg, int rows_per_tile, int px, long long* cycles) {
+// nst_force > 0: ring depth per issuing warp (several warps per CTA, or two CTAs per SM, share the shared memory)
+__global__ void __launch_bounds__(64, 1) rate_kernel(const __grid_constant__ CUtensorMap tm, int mode, int iters, int H, int W, int OH, int OW,
+                                                      int stride, int cslices, int nimg, int rows_per_tile, int px, long long* cycles,
+                                                      int nst_force) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[8];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int lane = threadIdx.x;
+  __shared__ __align__(8) uint64_t bars_all[16];
+  const int wid = threadIdx.x >> 5;
+  uint64_t* bars = bars_all + 8 * wid;
+  const int lane = threadIdx.x & 31;
   if (lane == 0) { for (int s = 0; s < 8; ++s) mbar_init(smem_u32(&bars[s]), 1); mbar_fence_init(); }
-  __syncwarp();
+  __syncthreads();
   const uint32_t stage_bytes = px > 128 ? px * 128 + 4096 : 20 * 1024;
-  const int nst = px > 128 ? (px > 256 ? 2 : 4) : 8;
+  const int nst = nst_force > 0 ? nst_force : (px > 128 ? (px > 256 ? 2 : 4) : 8);
+  const uint32_t base = ((smem_u32(smem_raw) + 1023u) & ~1023u) + wid * nst * stage_bytes;
   long long t0 = clock64();
   uint32_t bytes_per = 0;
   for (int it = 0; it < iters; ++it) {
@@ -34,7 +38,7 @@ __global__ void __launch_bounds__(32, 1) rate_kernel(const __grid_constant__ CUt
     if (it >= nst) mbar_wait(smem_u32(&bars[s]), ((it / nst) - 1) & 1);
     const uint32_t dst = base + s * stage_bytes + 2048;
     const uint32_t bar = smem_u32(&bars[s]);
-    const int tile = (blockIdx.x * 131 + it / 9) % ((nimg * OH * OW) / 128);
+    const int tile = ((blockIdx.x * 2 + wid) * 131 + it / 9) % ((nimg * OH * OW) / 128);
     const int tap = it % 9, r = tap / 3, sx = tap % 3, cb = (it / 9) % cslices;
     const int m0 = tile * 128;
     if (mode <= 1) {
@@ -63,7 +67,7 @@ __global__ void __launch_bounds__(32, 1) rate_kernel(const __grid_constant__ CUt
     mbar_wait(smem_u32(&bars[s]), (it_last / nst) & 1);
   }
   long long t1 = clock64();
-  if (blockIdx.x == 0 && lane == 0) { cycles[0] = t1 - t0; cycles[1] = (long long)bytes_per * iters; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { cycles[0] = t1 - t0; cycles[1] = (long long)bytes_per * iters; }
 }
 
 int main() {
@@ -105,10 +109,26 @@ int main() {
     }
     const int iters = 4000;
     for (int rep = 0; rep < 2; ++rep) {
-      rate_kernel<<<148, 32, 200 * 1024>>>(tm, c.mode, iters, c.H, c.W, OH, OW, c.stride, c.C / 64, nimg, rows, c.px ? c.px : 128, d_c);
+      rate_kernel<<<148, 32, 200 * 1024>>>(tm, c.mode, iters, c.H, c.W, OH, OW, c.stride, c.C / 64, nimg, rows, c.px ? c.px : 128, d_c, 0);
       cudaError_t e = cudaDeviceSynchronize();
       long long h[2]; cudaMemcpy(h, d_c, 16, cudaMemcpyDeviceToHost);
       if (rep) printf("%s: %6.1f B/clk/SM (%lld cycles per load of %lld B) [%s]\n", c.name, (double)h[1] / h[0], h[0] / iters, h[1] / iters, cudaGetErrorString(e));
+    }
+    // Do im2col requests from DIFFERENT issuers overlap?  (a) two issuing warps in one CTA, each with its own ring;
+    // (b) two CTAs per SM.  Rates are per issuer: if requests serialise in the SM's TMA unit, cycles per load doubles.
+    if (c.mode <= 1 && (c.px == 0 || c.px == 128 || c.px == 256)) {
+      const int px = c.px ? c.px : 128;
+      for (int variant = 0; variant < 2; ++variant) {
+        for (int rep = 0; rep < 2; ++rep) {
+          if (variant == 0) rate_kernel<<<148, 64, 200 * 1024>>>(tm, c.mode, iters, c.H, c.W, OH, OW, c.stride, c.C / 64, nimg, rows, px, d_c, px > 128 ? 2 : 4);
+          else rate_kernel<<<296, 32, 100 * 1024>>>(tm, c.mode, iters, c.H, c.W, OH, OW, c.stride, c.C / 64, nimg, rows, px, d_c, px > 128 ? 2 : 4);
+          cudaError_t e = cudaDeviceSynchronize();
+          long long h[2]; cudaMemcpy(h, d_c, 16, cudaMemcpyDeviceToHost);
+          if (rep) printf("    %s: %6.1f B/clk per issuer, %lld cycles per load per issuer -> %.1f B/clk/SM [%s]\n",
+                          variant == 0 ? "two issuing warps in one CTA" : "two CTAs per SM            ", (double)h[1] / h[0], h[0] / iters,
+                          2.0 * h[1] / h[0], cudaGetErrorString(e));
+        }
+      }
     }
     cudaFree(d_x);
   }
