@@ -9,7 +9,7 @@ mkdir -p "$OBJ"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-ffp-contract=off,-Wall,-Wno-unused-function)
 pids=()
-for f in conv_umma.cu stem.cu stem_alex.cu conv_fp32.cu misc_kernels.cu resize.cu ot_reader.cpp engine.cpp predict.cpp jpeg_decode.cpp capi.cpp; do
+for f in conv_umma.cu stem.cu stem2.cu stem_alex.cu conv_fp32.cu misc_kernels.cu resize.cu ot_reader.cpp engine.cpp predict.cpp jpeg_decode.cpp capi.cpp; do
   o="$OBJ/${f%.*}.o"
   if [ ! -f "$o" ] || [ "$SRC/$f" -nt "$o" ] || [ -n "$(find "$SRC" "$HERE/../include" -name '*.h' -newer "$o" -o -name '*.cuh' -newer "$o")" ]; then
     "$NVCC" "${FLAGS[@]}" -c "$SRC/$f" -o "$o" &

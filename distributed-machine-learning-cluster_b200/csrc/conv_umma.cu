@@ -48,6 +48,7 @@ struct KP {
   int msub;   // pair kernel: 128-row sub-tiles per CTA (1 or 2)
   int f16;    // 16-bit tensors are IEEE half instead of bf16
   int rev;    // pair kernel: walk the tiles from the last to the first
+  int nprod;  // pair kernel: warps that issue TMA requests (1..4), k-blocks dealt round-robin among them
 };
 
 // Where one tile's results go.
@@ -601,8 +602,16 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
       : "memory");
 }
 
+// TMA issue: an im2col-mode request takes 700-950 cycles from issue to completion whatever its size, and the
+// requests of ONE issuing warp do not overlap each other, but requests of different warps do (tools/microbench/
+// tma_rate.cu, two-issuer rows: the per-SM rate doubles with two warps or two CTAs).  So the k-blocks are dealt
+// round-robin to `nprod` producer warps (warp 0 and warps 10 ..), each walking the same tile / stage sequence
+// and issuing every nprod-th request: with four of them a request completes every ~240 cycles, under the MMA
+// time of a k-block (256 cycles at tile-N 128, 512 at 256).
+constexpr int PAIR_MAX_PROD = 4;
+constexpr int PAIR_THREADS = PTHREADS + 32 * (PAIR_MAX_PROD - 1);
 template <int AMODE, bool F16>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PTHREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PAIR_THREADS, 1)
 conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmB2, const KP p) {
   griddep_launch();
@@ -681,11 +690,13 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   }
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
-  if (warp == 0) {
-    if (lane == 0) {
+  const int prod_id = warp == 0 ? 0 : (warp >= PTHREADS / 32 ? warp - PTHREADS / 32 + 1 : -1);
+  if (prod_id >= 0) {
+    if (lane == 0 && prod_id < p.nprod) {
       const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
       const int ohw = p.OH * p.OW;
       int s = 0, ph = 0;
+      int turn = 0;   // whose k-block the next one is
       for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters) {
         const int t = p.rev ? total_tiles - 1 - t0 : t0;   // snake order: start with what the producer wrote last
         const int tm = t / tn_all;
@@ -709,23 +720,27 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         int cblk = kb_begin - tap0 * cpb, r = tap0 / p.S, sx = tap0 - (tap0 / p.S) * p.S;
         for (int j = 0; j < kb_count; ++j) {
           const int kb = kb_begin + j;
-          mbar_wait(empty_bar(s), ph ^ 1);
-          const uint32_t a_s = ring_base + s * stage_bytes;
-          if (leader) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
-          else mbar_arrive_cluster(full_bar(s), 0);
-          if (AMODE == A_IM2COL) {
-            tma_load_im2col_4d_2sm(a_s, &tmA, full_bar(s), cblk << 6, iw_base, ih_base, n_base,
-                                   static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
-            if (++cblk == cpb) {
-              cblk = 0;
-              if (++sx == p.S) { sx = 0; ++r; }
+          const bool mine = turn == prod_id;
+          if (++turn == p.nprod) turn = 0;
+          if (mine) {
+            mbar_wait(empty_bar(s), ph ^ 1);
+            const uint32_t a_s = ring_base + s * stage_bytes;
+            if (leader) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
+            else mbar_arrive_cluster(full_bar(s), 0);
+            if (AMODE == A_IM2COL) {
+              tma_load_im2col_4d_2sm(a_s, &tmA, full_bar(s), cblk << 6, iw_base, ih_base, n_base,
+                                     static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
+            } else {
+              tma_load_2d_2sm(a_s, &tmA, full_bar(s), kb * BK, m0);
             }
-          } else {
-            tma_load_2d_2sm(a_s, &tmA, full_bar(s), kb * BK, m0);
+            if (!resb) {
+              if (second) tma_load_2d_2sm(a_s + a_bytes, &tmB2, full_bar(s), j * BK, n0);
+              else tma_load_2d_2sm(a_s + a_bytes, &tmB, full_bar(s), kb * BK, n0);
+            }
           }
-          if (!resb) {
-            if (second) tma_load_2d_2sm(a_s + a_bytes, &tmB2, full_bar(s), j * BK, n0);
-            else tma_load_2d_2sm(a_s + a_bytes, &tmB, full_bar(s), kb * BK, n0);
+          if (AMODE == A_IM2COL && ++cblk == cpb) {
+            cblk = 0;
+            if (++sx == p.S) { sx = 0; ++r; }
           }
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
@@ -1300,6 +1315,7 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->msub = 1;
   p->f16 = a.f16;
   p->rev = a.reverse;
+  p->nprod = 1;
 }
 
 template <int AMODE, bool F16>
@@ -1368,7 +1384,12 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
     smem = resb_bytes + static_cast<size_t>(p.stages) * a_bytes + 1024;
   }
   if (p.stages < 3) return cudaErrorInvalidValue;
-  return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
+  // B2I_NPROD=1..4 overrides the number of TMA-issuing warps (A/B timing); im2col layers default to 4, never more
+  // than the ring has stages
+  static const int nprod_env = [] { const char* e = getenv("B2I_NPROD"); return e ? atoi(e) : 0; }();
+  p.nprod = nprod_env >= 1 && nprod_env <= PAIR_MAX_PROD ? nprod_env : (AMODE == A_IM2COL ? PAIR_MAX_PROD : 1);
+  p.nprod = std::min(p.nprod, p.stages);
+  return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PAIR_THREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
 template <bool F16>

@@ -352,6 +352,16 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       B2I_CUDA(cudaMemcpy(d.w, wb.data(), wb.size() * 2, cudaMemcpyHostToDevice));
       owned_.push_back(d.w);
       weight_bytes_ += wb.size() * 2;
+      {
+        std::vector<uint32_t> w2(128 * 144);
+        stem2_pack_weights(wb.data(), w2.data());
+        void* p2 = nullptr;
+        B2I_CUDA(cudaMalloc(&p2, w2.size() * 4));
+        B2I_CUDA(cudaMemcpy(p2, w2.data(), w2.size() * 4, cudaMemcpyHostToDevice));
+        owned_.push_back(p2);
+        d.w2 = static_cast<uint32_t*>(p2);
+        weight_bytes_ += w2.size() * 4;
+      }
       void* bp = nullptr;
       B2I_CUDA(cudaMalloc(&bp, c.bias.size() * 4));
       B2I_CUDA(cudaMemcpy(bp, c.bias.data(), c.bias.size() * 4, cudaMemcpyHostToDevice));
@@ -475,7 +485,9 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         auto est = [&](int bn, int ms) {
           const long long units = ((M + 256 * ms - 1) / (256 * ms)) * (c.Cout_pad / bn) * (carries ? 2 : 1);
           const long long waves = (units + 73) / 74;
-          const long long req = ms <= 2 ? 700 : (ms == 3 ? 730 : 764);
+          // requests of different issuing warps overlap: with nprod producers one completes every req / nprod cycles
+          static const int nprod = [] { const char* e = getenv("B2I_NPROD"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 4 ? v : 4; }();
+          const long long req = (ms <= 2 ? 700 : (ms == 3 ? 730 : 764)) / nprod;
           const long long kb_cycles = std::max<long long>(req, static_cast<long long>(ms) * 4 * (bn / 2));
           const long long epi = (2 * ms * bn > 512) ? 10000 : 0;
           const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
@@ -589,9 +601,13 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     const OpSpec& o = d.spec;
     if (d.skip) { mark(); continue; }
     switch (o.kind) {
-      case OpSpec::STEM:
-        B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, f16, st));
+      case OpSpec::STEM: {
+        // B2I_STEM=1: the first form of the kernel (pixels on the accumulator lanes, stem.cu); default: stem2.cu
+        static const int stem_form = [] { const char* e = getenv("B2I_STEM"); return e ? atoi(e) : 1; }();
+        if (stem_form == 2) B2I_CUDA(launch_stem2(d_u8, buf(o.out), d.w2, d.bias_host.data(), nb, stem_sched_, f16, st));
+        else B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, f16, st));
         break;
+      }
       case OpSpec::STEM_ALEX:
         B2I_CUDA(launch_alex_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, f16, st));
         break;

@@ -119,6 +119,7 @@ class DeviceModel {
     OpSpec spec;
     ConvGeom g{};
     void* w = nullptr;
+    uint32_t* w2 = nullptr;         // fused ResNet stem, second form: packed (parity, channel) x K matrix
     float* bias = nullptr;
     std::vector<float> bias_host;   // fused stem only: its bias travels as kernel parameters
     CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};

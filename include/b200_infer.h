@@ -33,8 +33,8 @@ extern "C" {
 /* Precision modes. The bounds are the ones tests/test_model_gpu.py enforces against the CPU restatement of
  * the reference path (oracle/, fp32); that restatement is itself not pinned by any reference-held vector
  * ("parity unpinned"). `unit` = max(1, standard deviation of the logits). */
-#define B2I_PREC_BF16 0 /* tcgen05, bf16 storage, fp32 accumulate: logits within 2e-2 x unit of the same network
-                          evaluated with bf16 storage on the CPU and within 3e-2 x unit of the fp32 restatement
+#define B2I_PREC_BF16 0 /* tcgen05, bf16 storage, fp32 accumulate: logits within 2.5e-2 x unit of the same network
+                          evaluated with bf16 storage on the CPU and within 4e-2 x unit of the fp32 restatement
                           (8 mantissa bits per stored activation: a FLAT 2e-2 holds only for logits of unit
                           scale); top-k identical wherever neighbouring logits differ by more than that */
 #define B2I_PREC_FP32 1 /* FFMA fp32: logits within 1e-4 x unit of the fp32 restatement */

@@ -11,13 +11,13 @@ Tolerances (BASELINE.json north_star): fp32 mode 1e-4 max-abs, bf16 mode 2e-2 ma
 ABSOLUTE figures meant for logits of pretrained scale (standard deviation 2-3).  Two weight sets:
   * "ps" (oracle.synth resnet18_ps: logits of std 2.5, |max| 13) and AlexNet (std 2.1): the bounds are applied
     FLAT.  fp32 mode and fp16 mode (PREC_FP16, the tensor-core kernels with IEEE-half storage) meet them;
-    bf16 mode does not and is not claimed to: its distance is printed and bounded by 3 % of the logit std.
+    bf16 mode does not and is not claimed to: its distance is printed and bounded by 4 % of the logit std.
   * the default synthetic ResNet-18 (std 8.9, |max| 47): the bounds are applied in units of the logit std.
 bf16 mode, two separate statements:
   (1) kernel exactness: against the oracle evaluated WITH bf16 storage (oracle.tch_oracle.*_bf16:
       same roundings, fp32 sums) the gap must be within 2.5e-2 units;
   (2) cost of the dtype: against the fp32 oracle the kernel may be no further away than 1.25x the
-      distance of that bf16 evaluation itself (measured 2.2-2.4 % of the logit std, the same
+      distance of that bf16 evaluation itself (measured 2.4-3.5 % of the logit std, the same
       2-4 % SURVEY.md Appendix E found for torch's own bf16 CPU path).
 Top-5: on every image whose top-1 / top-2 margin exceeds twice the tolerance the top-1 index is identical;
 where the 5th / 6th margin does too, the top-5 SET is identical; where every neighbouring pair among the first
@@ -43,9 +43,10 @@ def tol_for(precision, ref_logits, flat=False):
 
 
 def bf16_budget(ref_logits):
-    """Distance a bf16 evaluation may have from the fp32 oracle: 3 % of the logit std (measured
-    2.2-2.4 %; see the module docstring)."""
-    return 3e-2 * max(1.0, float(np.std(ref_logits)))
+    """Distance a bf16 evaluation may have from the fp32 oracle: 4 % of the logit std (measured over the 120
+    fixtures: 2.4 % ResNet-18, 3.3-3.5 % AlexNet; over all 1000 reference images 2.7 % / 3.5 %,
+    profiles/r03_parity_1000.json; see the module docstring)."""
+    return 4e-2 * max(1.0, float(np.std(ref_logits)))
 
 
 def check_topk(ref_logits, idx, tol, what):
@@ -129,7 +130,7 @@ def test_resnet18_fixture_images_match_golden(pkg, ctx, resnet18_ot, precision):
 def test_resnet18_pretrained_scale_logits_flat_bounds(pkg, ctx, resnet18_ps_ot, precision):
     """The north-star tolerances as written -- max-abs 2e-2 (16-bit modes) / 1e-4 (fp32 mode), no scaling --
     on the weight set whose logits have pretrained scale.  fp32 and fp16 modes must meet them; for bf16 the
-    absolute gap is printed and held to 3 % of the logit std (it does not meet a flat 2e-2: 8 mantissa bits)."""
+    absolute gap is printed and held to 4 % of the logit std (it does not meet a flat 2e-2: 8 mantissa bits)."""
     crops = fixture_crops()
     batch, rep = resnet18_batch256(crops)
     with pkg.Model(ctx, "resnet18", resnet18_ps_ot, precision=precision, max_batch=256) as m:
