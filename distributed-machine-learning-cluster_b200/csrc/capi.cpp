@@ -334,7 +334,6 @@ int b2i_predict_raw_u8(b2i_model* m, int first_dev, int n_dev, const uint8_t* co
     if (!m) return fail(B2I_EINVAL, "null model");
     if (n == 0) return B2I_OK;
     if (n_dev <= 0) { first_dev = 0; n_dev = static_cast<int>(m->slots.size()); }
-    std::lock_guard<std::mutex> lock(m->mu);
     std::string err;
     const int rc = predict_raw(m, first_dev, n_dev, images, heights, widths, n, k, idx, prob, logits, &err);
     if (rc != B2I_OK) return fail(rc, err);
@@ -348,7 +347,6 @@ int b2i_predict_raw_u8_status(b2i_model* m, int first_dev, int n_dev, const uint
     if (!m) return fail(B2I_EINVAL, "null model");
     if (n == 0) return B2I_OK;
     if (n_dev <= 0) { first_dev = 0; n_dev = static_cast<int>(m->slots.size()); }
-    std::lock_guard<std::mutex> lock(m->mu);
     std::string err;
     const int rc = predict_raw_status(m, first_dev, n_dev, images, heights, widths, n, k, idx, prob, logits, status, &err);
     if (rc != B2I_OK) return fail(rc, err);
@@ -362,7 +360,6 @@ int b2i_predict_jpeg(b2i_model* m, int first_dev, int n_dev, const uint8_t* cons
     if (!m) return fail(B2I_EINVAL, "null model");
     if (n == 0) return B2I_OK;
     if (n_dev <= 0) { first_dev = 0; n_dev = static_cast<int>(m->slots.size()); }
-    std::lock_guard<std::mutex> lock(m->mu);
     std::string err;
     const int rc = predict_jpeg(m, first_dev, n_dev, jpeg, len, n, k, idx, prob, logits, status, &err);
     if (rc != B2I_OK) return fail(rc, err);

@@ -485,9 +485,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         auto est = [&](int bn, int ms) {
           const long long units = ((M + 256 * ms - 1) / (256 * ms)) * (c.Cout_pad / bn) * (carries ? 2 : 1);
           const long long waves = (units + 73) / 74;
-          // requests of different issuing warps overlap: with nprod producers one completes every req / nprod cycles
-          static const int nprod = [] { const char* e = getenv("B2I_NPROD"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 4 ? v : 4; }();
-          const long long req = (ms <= 2 ? 700 : (ms == 3 ? 730 : 764)) / nprod;
+          const long long req = ms <= 2 ? 700 : (ms == 3 ? 730 : 764);
           const long long kb_cycles = std::max<long long>(req, static_cast<long long>(ms) * 4 * (bn / 2));
           const long long epi = (2 * ms * bn > 512) ? 10000 : 0;
           const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;

@@ -181,15 +181,26 @@ void slot_free(DevSlot* s) {
     for (auto ev : L.copied) if (ev) cudaEventDestroy(ev);
     L = Lane();
   }
-  if (s->raw.d_img) cudaFree(s->raw.d_img);
-  if (s->raw.h_img) cudaFreeHost(s->raw.h_img);
-  if (s->raw.d_tab) cudaFree(s->raw.d_tab);
-  if (s->raw.h_tab) cudaFreeHost(s->raw.h_tab);
-  if (s->raw.d_tmp) cudaFree(s->raw.d_tmp);
-  if (s->raw.d_jimg) cudaFree(s->raw.d_jimg);
-  s->raw = RawScratch();
-  if (s->jpeg) jpeg_decoder_destroy(s->jpeg);
-  s->jpeg = nullptr;
+  for (RawLane& R : s->rawlane) {
+    if (R.raw.d_img) cudaFree(R.raw.d_img);
+    if (R.raw.h_img) cudaFreeHost(R.raw.h_img);
+    if (R.raw.d_tab) cudaFree(R.raw.d_tab);
+    if (R.raw.h_tab) cudaFreeHost(R.raw.h_tab);
+    if (R.raw.d_tmp) cudaFree(R.raw.d_tmp);
+    if (R.raw.d_jimg) cudaFree(R.raw.d_jimg);
+    if (R.jpeg) jpeg_decoder_destroy(R.jpeg);
+    if (R.d_in) cudaFree(R.d_in);
+    if (R.d_idx) cudaFree(R.d_idx);
+    if (R.d_prob) cudaFree(R.d_prob);
+    if (R.d_logits) cudaFree(R.d_logits);
+    if (R.h_idx) cudaFreeHost(R.h_idx);
+    if (R.h_prob) cudaFreeHost(R.h_prob);
+    if (R.h_logits) cudaFreeHost(R.h_logits);
+    if (R.staged) cudaEventDestroy(R.staged);
+    if (R.st) cudaStreamDestroy(R.st);
+    R.raw = RawScratch(); R.jpeg = nullptr; R.d_in = nullptr; R.d_idx = nullptr; R.d_prob = nullptr; R.d_logits = nullptr;
+    R.h_idx = nullptr; R.h_prob = nullptr; R.h_logits = nullptr; R.staged = nullptr; R.st = nullptr; R.busy = false;
+  }
   for (auto& kv : s->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   s->graphs.clear();
   if (s->copy_st) cudaStreamDestroy(s->copy_st);
@@ -267,53 +278,122 @@ bool grow(void** dev, void** host, size_t* cap, size_t need, std::string* err) {
   return true;
 }
 
-// One GPU's share: plan every image on the host, ship images + tables in two copies, run the two
-// resize passes per image into lane 0's device batch, then the usual chunked forward.
-//   images != null: decoded pixels in host memory, sizes in hs / ws
-//   jpeg   != null: encoded streams; decoded on this GPU (jpeg_decode.h) straight into the packed image
+// The raw-image / JPEG path runs in two phases so that the host-heavy part of one call overlaps the GPU part of
+// another (a member serves several `predict` RPCs at once, reference src/main.rs:74-79):
+//   stage   (no model lock; exclusive use of one of the slot's two RawLanes)  header probe, resampling plans,
+//           entropy decoding / the copy of the pixels, all GPU work on the LANE's stream
+//   finish  (under the model lock, like every other forward)  resize + crop into the lane's device batch, the
+//           network, the copy of the answers, on the slot's compute stream
+// With two callers, caller B decodes its batch while caller A's batch is on the GPU.
+struct StagedShard {
+  DevSlot* slot = nullptr;
+  RawLane* lane = nullptr;
+  int n = 0, k = 0;
+  bool from_jpeg = false;
+  int32_t* idx = nullptr;
+  float* prob = nullptr;
+  float* logits = nullptr;
+  int* status = nullptr;               // per image, caller's array (JPEG path) or null
+  std::vector<int> own_status;
+  std::vector<ResizeJob> jobs;
+  std::vector<char> usable;
+  std::string trace;
+  Shard result;
+};
+
+RawLane* lane_acquire(DevSlot& s) {
+  std::unique_lock<std::mutex> lock(s.raw_mu);
+  for (;;) {
+    for (RawLane& L : s.rawlane)
+      if (!L.busy) { L.busy = true; return &L; }
+    s.raw_cv.wait(lock);
+  }
+}
+void lane_release(DevSlot& s, RawLane* L) {
+  {
+    std::lock_guard<std::mutex> lock(s.raw_mu);
+    L->busy = false;
+  }
+  s.raw_cv.notify_one();
+}
+
+bool lane_setup(DevSlot& s, RawLane& L, int max_batch, bool want_logits, std::string* err) {
+  cudaError_t e = cudaSuccess;
+  auto chk = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+  if (!L.st) {
+    const size_t nk = static_cast<size_t>(max_batch) * 8;
+    chk(cudaStreamCreateWithFlags(&L.st, cudaStreamNonBlocking));
+    chk(cudaEventCreateWithFlags(&L.staged, cudaEventDisableTiming));
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_in), static_cast<size_t>(max_batch) * B2I_IMAGE_BYTES));
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_idx), nk * 4));
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_prob), nk * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_idx), nk * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_prob), nk * 4));
+  }
+  if (want_logits && !L.d_logits) {
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_logits), static_cast<size_t>(max_batch) * B2I_CLASSES * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_logits), static_cast<size_t>(max_batch) * B2I_CLASSES * 4));
+  }
+  if (e != cudaSuccess) { *err = std::string("raw-path staging: ") + cudaGetErrorString(e); return false; }
+  (void)s;
+  return true;
+}
+
+// Phase 1 for one GPU's share.
+//   images != null: decoded pixels in host memory, sizes in hs_in / ws_in
+//   jpeg   != null: encoded streams; decoded on this GPU (jpeg_decode.h) straight into the lane's packed image
 //                   buffer, sizes from the header probe, one status per image
-void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* jpeg, const size_t* jpeg_len,
-               const int* hs_in, const int* ws_in, int n, int k, int32_t* idx, float* prob, float* logits,
-               int* status, Shard* out) {
+void raw_stage(DevSlot& s, int device, int max_batch, const uint8_t* const* images, const uint8_t* const* jpeg,
+               const size_t* jpeg_len, const int* hs_in, const int* ws_in, int n, int k, int32_t* idx, float* prob,
+               float* logits, int* status, StagedShard* sh) {
+  sh->slot = &s; sh->n = n; sh->k = k; sh->from_jpeg = jpeg != nullptr;
+  sh->idx = idx; sh->prob = prob; sh->logits = logits; sh->status = status;
   if (n == 0) return;
+  Shard* out = &sh->result;
   auto cu = [&](cudaError_t e, const char* what) {
     if (e == cudaSuccess) return false;
     out->rc = B2I_ECUDA;
     out->err = std::string(what) + ": " + cudaGetErrorString(e);
     return true;
   };
-  if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
+  if (cu(cudaSetDevice(device), "cudaSetDevice")) return;
   // B2I_TRACE=1: wall time of every host-side stage of this call on stderr (where does a batch from files go?)
   static const bool trace = [] { const char* e = getenv("B2I_TRACE"); return e && e[0] == '1'; }();
   using clk = std::chrono::steady_clock;
   auto t_last = clk::now();
-  std::string tr;
   auto stamp = [&](const char* what) {
     if (!trace) return;
     const auto now = clk::now();
     char b[64];
     snprintf(b, sizeof b, " %s %.2f ms;", what, std::chrono::duration<double, std::milli>(now - t_last).count());
-    tr += b;
+    sh->trace += b;
     t_last = now;
   };
-  Lane& L = s.lane[0];
-  RawScratch& R = s.raw;
-  std::vector<int> hbuf, wbuf, stbuf;
+  RawLane* Lp = lane_acquire(s);
+  sh->lane = Lp;
+  RawLane& L = *Lp;
+  stamp("lane");
+  if (!lane_setup(s, L, max_batch, logits != nullptr, &out->err)) { out->rc = B2I_ENOMEM; return; }
+  RawScratch& R = L.raw;
+  std::vector<int> hbuf, wbuf;
   const int* hs = hs_in;
   const int* ws = ws_in;
   if (jpeg) {
-    if (!s.jpeg) {
-      s.jpeg = jpeg_decoder_create(&out->err);
-      if (!s.jpeg) { out->rc = B2I_ENODEV; return; }
+    if (!L.jpeg) {
+      L.jpeg = jpeg_decoder_create(&out->err);
+      if (!L.jpeg) { out->rc = B2I_ENODEV; return; }
     }
     hbuf.resize(n); wbuf.resize(n);
-    if (!status) { stbuf.resize(n); status = stbuf.data(); }
-    jpeg_probe(s.jpeg, jpeg, jpeg_len, n, hbuf.data(), wbuf.data(), status);
+    if (!status) { sh->own_status.resize(n); status = sh->own_status.data(); sh->status = status; }
+    jpeg_probe(L.jpeg, jpeg, jpeg_len, n, hbuf.data(), wbuf.data(), status);
     hs = hbuf.data();
     ws = wbuf.data();
     stamp("header probe");
   }
-  auto usable = [&](int i) { return jpeg ? status[i] == B2I_OK : true; };
+  sh->usable.assign(n, 1);
+  if (jpeg)
+    for (int i = 0; i < n; ++i) sh->usable[i] = status[i] == B2I_OK;
+  auto usable = [&](int i) { return sh->usable[i] != 0; };
   std::vector<AxisPlan> px(n), py(n);
   std::vector<size_t> img_off(n), tab_off(n);
   size_t img_bytes = 0, tab_bytes = 0, tmp_elems = 0;
@@ -336,9 +416,7 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
     img_off[i] = img_bytes;
     tab_off[i] = tab_bytes;
     if (!usable(i)) continue;
-    img_off[i] = img_bytes;
     img_bytes += (static_cast<size_t>(hs[i]) * ws[i] * 3 + 255) & ~static_cast<size_t>(255);
-    tab_off[i] = tab_bytes;
     tab_bytes += ((4 * 224 * 4 + (px[i].idx.size() + py[i].idx.size()) * 8) + 255) & ~static_cast<size_t>(255);
     tmp_elems = std::max(tmp_elems, static_cast<size_t>(hs[i]) * 224 * 3);
   }
@@ -349,7 +427,7 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
     out->rc = B2I_ENOMEM;
     return;
   }
-  std::vector<ResizeJob> jobs(n);
+  sh->jobs.assign(n, ResizeJob());
   for (int i = 0; i < n; ++i) {
     if (!usable(i)) continue;
     if (!jpeg) std::memcpy(R.h_img + img_off[i], images[i], static_cast<size_t>(hs[i]) * ws[i] * 3);
@@ -357,7 +435,7 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
     uint8_t* dt = R.d_tab + tab_off[i];
     size_t o = 0;
     auto put = [&](const void* src, size_t bytes) { std::memcpy(ht + o, src, bytes); const size_t at = o; o += bytes; return at; };
-    ResizeJob& j = jobs[i];
+    ResizeJob& j = sh->jobs[i];
     j.d_img = (jpeg ? R.d_jimg : R.d_img) + img_off[i]; j.h = hs[i]; j.w = ws[i];
     j.xf = reinterpret_cast<const int*>(dt + put(px[i].first.data(), 224 * 4));
     j.xc = reinterpret_cast<const int*>(dt + put(px[i].count.data(), 224 * 4));
@@ -370,30 +448,46 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
     j.d_tmp = R.d_tmp;
     j.d_out = L.d_in + static_cast<size_t>(i) * B2I_IMAGE_BYTES;
   }
+  stamp("tables");
+  if (cu(cudaMemcpyAsync(R.d_tab, R.h_tab, tab_bytes, cudaMemcpyHostToDevice, L.st), "H2D resize tables")) return;
   if (jpeg) {
     std::vector<uint8_t*> dst(n);
     for (int i = 0; i < n; ++i) dst[i] = R.d_jimg + img_off[i];
-    stamp("tables");
-    if (!jpeg_decode_batch(s.jpeg, jpeg, jpeg_len, n, dst.data(), hs, ws, status, s.comp_st, &out->err)) { out->rc = B2I_ECUDA; return; }
+    if (!jpeg_decode_batch(L.jpeg, jpeg, jpeg_len, n, dst.data(), hs, ws, status, L.st, &out->err)) { out->rc = B2I_ECUDA; return; }
+    for (int i = 0; i < n; ++i) sh->usable[i] = status[i] == B2I_OK;   // streams that turned out to be damaged
     stamp("decode (host side)");
-  } else if (cu(cudaMemcpyAsync(R.d_img, R.h_img, img_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D raw images")) {
+  } else if (cu(cudaMemcpyAsync(R.d_img, R.h_img, img_bytes, cudaMemcpyHostToDevice, L.st), "H2D raw images")) {
     return;
   }
-  if (cu(cudaMemcpyAsync(R.d_tab, R.h_tab, tab_bytes, cudaMemcpyHostToDevice, s.comp_st), "H2D resize tables")) return;
+  cu(cudaEventRecord(L.staged, L.st), "cudaEventRecord(staged)");
+}
+
+// Phase 2 for one GPU's share; the caller holds the model lock.
+void raw_finish(StagedShard* sh) {
+  Shard* out = &sh->result;
+  if (sh->n == 0 || out->rc != B2I_OK || !sh->lane) return;
+  DevSlot& s = *sh->slot;
+  RawLane& L = *sh->lane;
+  const int n = sh->n, k = sh->k;
+  auto cu = [&](cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return false;
+    out->rc = B2I_ECUDA;
+    out->err = std::string(what) + ": " + cudaGetErrorString(e);
+    return true;
+  };
+  static const bool trace = [] { const char* e = getenv("B2I_TRACE"); return e && e[0] == '1'; }();
+  const auto t0 = std::chrono::steady_clock::now();
+  if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
+  if (n > s.dm->max_batch()) { out->rc = B2I_EINVAL; out->err = "shard exceeds max_batch"; return; }
+  if (cu(cudaStreamWaitEvent(s.comp_st, L.staged, 0), "cudaStreamWaitEvent(staged)")) return;
   for (int i = 0; i < n; ++i)
-    if (usable(i) && cu(launch_resize_job(jobs[i], s.comp_st), "resize kernels")) return;
-  stamp("resize launches");
+    if (sh->usable[i] && cu(launch_resize_job(sh->jobs[i], s.comp_st), "resize kernels")) return;
   const int classes = s.dm->classes();
-  if (logits && !L.d_logits) {
-    const size_t cap = static_cast<size_t>(s.dm->max_batch());
-    if (cu(cudaMalloc(reinterpret_cast<void**>(&L.d_logits), cap * classes * 4), "cudaMalloc(logits)")) return;
-    if (cu(cudaMallocHost(reinterpret_cast<void**>(&L.h_logits), cap * classes * 4), "cudaMallocHost(logits)")) return;
-  }
   for (int off = 0; off < n; off += s.chunk) {
     const int nb = std::min(s.chunk, n - off);
     if (!s.dm->forward(L.d_in + static_cast<size_t>(off) * B2I_IMAGE_BYTES, nb, k, L.d_idx + static_cast<size_t>(off) * k,
                        L.d_prob + static_cast<size_t>(off) * k,
-                       logits ? L.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, &out->err)) {
+                       sh->logits ? L.d_logits + static_cast<size_t>(off) * classes : nullptr, s.comp_st, &out->err)) {
       out->rc = B2I_ECUDA;
       return;
     }
@@ -401,20 +495,68 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
   const size_t nk = static_cast<size_t>(n) * k;
   if (cu(cudaMemcpyAsync(L.h_idx, L.d_idx, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H idx")) return;
   if (cu(cudaMemcpyAsync(L.h_prob, L.d_prob, nk * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H prob")) return;
-  if (logits && cu(cudaMemcpyAsync(L.h_logits, L.d_logits, static_cast<size_t>(n) * classes * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H logits")) return;
-  stamp("forward launches");
+  if (sh->logits && cu(cudaMemcpyAsync(L.h_logits, L.d_logits, static_cast<size_t>(n) * classes * 4, cudaMemcpyDeviceToHost, s.comp_st), "D2H logits")) return;
+  const auto t1 = std::chrono::steady_clock::now();
   if (cu(cudaStreamSynchronize(s.comp_st), "cudaStreamSynchronize")) return;
-  stamp("wait for the GPU");
-  if (trace) fprintf(stderr, "[b2i trace] %s shard of %d on GPU %d:%s\n", jpeg ? "jpeg" : "raw", n, s.dm->device(), tr.c_str());
-  std::memcpy(idx, L.h_idx, nk * 4);
-  std::memcpy(prob, L.h_prob, nk * 4);
-  if (logits) std::memcpy(logits, L.h_logits, static_cast<size_t>(n) * classes * 4);
-  if (jpeg)
-    for (int i = 0; i < n; ++i)
-      if (status[i] != B2I_OK) {   // its slot of the device batch held no image: blank the answer
-        for (int j = 0; j < k; ++j) { idx[static_cast<size_t>(i) * k + j] = -1; prob[static_cast<size_t>(i) * k + j] = 0.f; }
-        if (logits) std::fill(logits + static_cast<size_t>(i) * classes, logits + static_cast<size_t>(i + 1) * classes, 0.f);
+  if (trace) {
+    const auto t2 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[b2i trace] %s shard of %d on GPU %d:%s launches %.2f ms; wait for the GPU %.2f ms\n", sh->from_jpeg ? "jpeg" : "raw", n,
+            s.dm->device(), sh->trace.c_str(), std::chrono::duration<double, std::milli>(t1 - t0).count(),
+            std::chrono::duration<double, std::milli>(t2 - t1).count());
+  }
+  std::memcpy(sh->idx, L.h_idx, nk * 4);
+  std::memcpy(sh->prob, L.h_prob, nk * 4);
+  if (sh->logits) std::memcpy(sh->logits, L.h_logits, static_cast<size_t>(n) * classes * 4);
+  for (int i = 0; i < n; ++i)
+    if (!sh->usable[i]) {   // its slot of the device batch held no image: blank the answer
+      for (int j = 0; j < k; ++j) { sh->idx[static_cast<size_t>(i) * k + j] = -1; sh->prob[static_cast<size_t>(i) * k + j] = 0.f; }
+      if (sh->logits) std::fill(sh->logits + static_cast<size_t>(i) * classes, sh->logits + static_cast<size_t>(i + 1) * classes, 0.f);
+    }
+}
+
+// Both phases over the GPUs [first_dev, first_dev + n_dev): staging without the model lock, the forwards under it.
+int raw_run(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const uint8_t* const* jpeg, const size_t* len,
+            const int* heights, const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, int* status,
+            std::string* err) {
+  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
+  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size())) { *err = "device range outside the model's context"; return B2I_EINVAL; }
+  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch) { *err = "batch exceeds GPUs x max_batch"; return B2I_EINVAL; }
+  const int per = (n + n_dev - 1) / n_dev;
+  std::vector<StagedShard> sh(n_dev);
+  auto each = [&](auto&& fn) {
+    if (n_dev == 1) { fn(0); return; }
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_dev; ++g) th.emplace_back(fn, g);
+    for (auto& x : th) x.join();
+  };
+  each([&](int g) {
+    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
+    raw_stage(m->slots[first_dev + g], m->ctx->devices[first_dev + g], m->max_batch, images ? images + lo : nullptr,
+              jpeg ? jpeg + lo : nullptr, jpeg ? len + lo : nullptr, heights ? heights + lo : nullptr, widths ? widths + lo : nullptr,
+              hi - lo, k, idx + static_cast<size_t>(lo) * k, prob + static_cast<size_t>(lo) * k,
+              logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, status ? status + lo : nullptr, &sh[g]);
+  });
+  int rc = B2I_OK;
+  {
+    std::lock_guard<std::mutex> lock(m->mu);   // forwards of one model are serialised, whatever path they come from
+    if (m->pending[0].active || m->pending[1].active) {
+      *err = "an asynchronous request is still in flight; b2i_wait for it first";
+      rc = B2I_EINVAL;
+    } else {
+      each([&](int g) { raw_finish(&sh[g]); });
+    }
+  }
+  for (int g = 0; g < n_dev; ++g) {
+    if (sh[g].lane) {
+      if (rc != B2I_OK || sh[g].result.rc != B2I_OK) {   // nothing may still be writing into the lane when it is handed on
+        cudaSetDevice(m->ctx->devices[first_dev + g]);
+        cudaStreamSynchronize(sh[g].lane->st);
       }
+      lane_release(m->slots[first_dev + g], sh[g].lane);
+    }
+    if (rc == B2I_OK && sh[g].result.rc != B2I_OK) { *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].result.err; rc = sh[g].result.rc; }
+  }
+  return rc;
 }
 
 }  // namespace
@@ -422,51 +564,13 @@ void raw_shard(DevSlot& s, const uint8_t* const* images, const uint8_t* const* j
 int predict_jpeg(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* jpeg, const size_t* len, int n, int k,
                  int32_t* idx, float* prob, float* logits, int* status, std::string* err) {
   if (n < 0 || (n > 0 && (!jpeg || !len || !idx || !prob || !status))) { *err = "null buffer"; return B2I_EINVAL; }
-  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
-  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size())) { *err = "device range outside the model's context"; return B2I_EINVAL; }
-  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch) { *err = "batch exceeds GPUs x max_batch"; return B2I_EINVAL; }
-  if (m->pending[0].active || m->pending[1].active) { *err = "an asynchronous request is still in flight; b2i_wait for it first"; return B2I_EINVAL; }
-  const int per = (n + n_dev - 1) / n_dev;
-  std::vector<Shard> sh(n_dev);
-  auto work = [&](int g) {
-    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
-    raw_shard(m->slots[first_dev + g], nullptr, jpeg + lo, len + lo, nullptr, nullptr, hi - lo, k, idx + static_cast<size_t>(lo) * k,
-              prob + static_cast<size_t>(lo) * k, logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, status + lo, &sh[g]);
-  };
-  if (n_dev == 1) work(0);
-  else {
-    std::vector<std::thread> th;
-    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
-    for (auto& x : th) x.join();
-  }
-  for (int g = 0; g < n_dev; ++g)
-    if (sh[g].rc != B2I_OK) { *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].err; return sh[g].rc; }
-  return B2I_OK;
+  return raw_run(m, first_dev, n_dev, nullptr, jpeg, len, nullptr, nullptr, n, k, idx, prob, logits, status, err);
 }
 
 int predict_raw(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,
                 const int* widths, int n, int k, int32_t* idx, float* prob, float* logits, std::string* err) {
   if (n < 0 || (n > 0 && (!images || !heights || !widths || !idx || !prob))) { *err = "null buffer"; return B2I_EINVAL; }
-  if (k < 1 || k > 8) { *err = "k must be in 1..8"; return B2I_EINVAL; }
-  if (first_dev < 0 || n_dev < 1 || first_dev + n_dev > static_cast<int>(m->slots.size())) { *err = "device range outside the model's context"; return B2I_EINVAL; }
-  if (static_cast<long long>(n) > static_cast<long long>(n_dev) * m->max_batch) { *err = "batch exceeds GPUs x max_batch"; return B2I_EINVAL; }
-  if (m->pending[0].active || m->pending[1].active) { *err = "an asynchronous request is still in flight; b2i_wait for it first"; return B2I_EINVAL; }
-  const int per = (n + n_dev - 1) / n_dev;
-  std::vector<Shard> sh(n_dev);
-  auto work = [&](int g) {
-    const int lo = std::min(n, g * per), hi = std::min(n, (g + 1) * per);
-    raw_shard(m->slots[first_dev + g], images + lo, nullptr, nullptr, heights + lo, widths + lo, hi - lo, k, idx + static_cast<size_t>(lo) * k,
-              prob + static_cast<size_t>(lo) * k, logits ? logits + static_cast<size_t>(lo) * B2I_CLASSES : nullptr, nullptr, &sh[g]);
-  };
-  if (n_dev == 1) work(0);
-  else {
-    std::vector<std::thread> th;
-    for (int g = 0; g < n_dev; ++g) th.emplace_back(work, g);
-    for (auto& x : th) x.join();
-  }
-  for (int g = 0; g < n_dev; ++g)
-    if (sh[g].rc != B2I_OK) { *err = "GPU " + std::to_string(first_dev + g) + ": " + sh[g].err; return sh[g].rc; }
-  return B2I_OK;
+  return raw_run(m, first_dev, n_dev, images, nullptr, nullptr, heights, widths, n, k, idx, prob, logits, nullptr, err);
 }
 
 int predict_raw_status(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* images, const int* heights,

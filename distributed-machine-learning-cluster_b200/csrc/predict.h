@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <condition_variable>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -62,10 +63,30 @@ struct RawScratch {
 
 struct JpegDecoder;
 
-struct DevSlot {
-  std::unique_ptr<DeviceModel> dm;
+// Everything one raw-image / JPEG request needs on one GPU before its forward: decoder, packed source images,
+// resampling tables, the device batch the resize writes and the forward reads, result staging.  A slot has two,
+// so that one request is being decoded while the other's forward runs (predict.cpp, raw_stage / raw_finish).
+struct RawLane {
   RawScratch raw;
-  JpegDecoder* jpeg = nullptr;                 // created by the first b2i_predict_jpeg on this GPU
+  JpegDecoder* jpeg = nullptr;                 // created by the lane's first JPEG request
+  cudaStream_t st = nullptr;                   // decode kernels / pixel and table copies
+  cudaEvent_t staged = nullptr;                // recorded on st when the lane's inputs are on the GPU
+  uint8_t* d_in = nullptr;                     // max_batch cropped images
+  int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
+  int32_t* h_idx = nullptr; float* h_prob = nullptr; float* h_logits = nullptr;   // pinned
+  bool busy = false;                           // guarded by DevSlot::raw_mu
+};
+
+struct DevSlot {
+  DevSlot() = default;
+  DevSlot(DevSlot&& o) noexcept : dm(std::move(o.dm)), copy_st(o.copy_st), comp_st(o.comp_st), chunk(o.chunk),
+                                  graph_max_batch(o.graph_max_batch), graphs(std::move(o.graphs)) {
+    for (int i = 0; i < 2; ++i) { lane[i] = o.lane[i]; rawlane[i] = o.rawlane[i]; }
+  }
+  std::unique_ptr<DeviceModel> dm;
+  RawLane rawlane[2];
+  std::mutex raw_mu;
+  std::condition_variable raw_cv;
   cudaStream_t copy_st = nullptr, comp_st = nullptr;
   Lane lane[2];
   int chunk = 0;

@@ -22,11 +22,13 @@
 //     3-tap max, and the vertical max of the two same-parity rows, are register operations on raw accumulators
 //     (+bias, ReLU and the rounding are monotone, so they commute with max and are applied once per POOLED value).
 //     Only the pooled values cross threads: 2 x 6 KB per tile through shared memory instead of 32 KB + 56 KB.
-// One CTA per SM (all 512 TMEM columns: two accumulator sets of 128 + 144 of weights), 17 warps:
-//   warps 0-7   epilogue: two sets (pooled rows 0-3 / 4-6) of four warps, one per TMEM lane quarter
-//   warp  8     MMA issue
-//   warps 9-16  two loader groups of four warps; tiles alternate between the groups so that the global-memory
-//               latency of one tile's pixels hides behind the other group's tile
+// One CTA per SM (all 512 TMEM columns: two accumulator sets of 128 + 144 of weights), 25 warps; tiles alternate
+// between two loader groups and two epilogue groups (even / odd tile of the CTA's sequence = patch buffer =
+// accumulator set), because both are latency chains (global loads; TMEM loads feeding dependent max chains)
+// that take longer than the MMAs of a tile:
+//   warps 0-15  two epilogue groups of eight warps: two sets (pooled rows 0-3 / 4-6) x four TMEM lane quarters
+//   warp  16    MMA issue
+//   warps 17-24 two loader groups of four warps
 #include "conv.h"
 #include "ops.h"
 #include "ptx.cuh"
@@ -34,7 +36,7 @@
 namespace b2i {
 namespace {
 
-constexpr int S2_DRAIN = 256;
+constexpr int S2_DRAIN = 512;
 constexpr int S2_GROUP = 128;                          // threads of one loader group
 constexpr int S2_THREADS = S2_DRAIN + 32 + 2 * S2_GROUP;
 constexpr int PATCH_H = 37, PATCH_W = 40;              // pixels of 8 bytes (r, g, b, 0 in the 16-bit storage format)
@@ -127,7 +129,8 @@ stem2_kernel(const Stem2Params p) {
     }
     mbar_fence_init();
   }
-  if (warp == 8) tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
+  constexpr int MMA_WARP = S2_DRAIN / 32;
+  if (warp == MMA_WARP) tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -150,7 +153,7 @@ stem2_kernel(const Stem2Params p) {
   tc_fence_after();
   griddep_wait();   // the pooled map written below may still be read by the previous forward's kernels
 
-  if (warp == 8) {
+  if (warp == MMA_WARP) {
     // ------------------------------------------------------------------ MMA issue
     const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
     bool done[2] = {false, false};
@@ -182,9 +185,9 @@ stem2_kernel(const Stem2Params p) {
       umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
       umma_commit_elect(acc_full(b));
     }
-  } else if (warp > 8) {
+  } else if (warp > MMA_WARP) {
     // ------------------------------------------------------------------ patch loaders: group g fills buffer g
-    const int g = (warp - 9) >> 2;
+    const int g = (warp - MMA_WARP - 1) >> 2;
     const int lt = tid - (S2_DRAIN + 32) - g * S2_GROUP;
     uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));
     __shared__ int next_tile[2];
@@ -262,24 +265,20 @@ stem2_kernel(const Stem2Params p) {
     }
   } else {
     // ------------------------------------------------------------------ epilogue: pool in registers, +bias, ReLU, store
-    const int set = warp >> 2;                 // 0: pooled rows 0-3, 1: pooled rows 4-6
+    const int b = warp >> 3;                   // epilogue group = accumulator set = tiles 2k + b of the CTA's sequence
+    const int set = (warp >> 2) & 1;           // 0: pooled rows 0-3, 1: pooled rows 4-6
     const int q = warp & 3;                    // TMEM lane quarter
     const int par = q >> 1;                    // 0: even conv rows of the tile (slots 2i), 1: odd rows (slots 2i + 1)
     const int ch = (q & 1) * 32 + lane;
     const float bias = p.bias[ch];
     const int py0 = set * 4, npy = set == 0 ? 4 : 3;
-    const int st = tid & 127;                  // index inside the set (its two named barriers: 4 + set, 6 + set)
+    const int st = tid & 127;                  // index inside the set
     uint8_t* const x_gen = smem_raw + (x0 - smem_u32(smem_raw));
-    bool done[2] = {false, false};
-    for (int i = 0;; ++i) {
-      const int b = i & 1;
-      if (done[b]) {
-        if (done[b ^ 1]) break;
-        continue;
-      }
-      mbar_wait(acc_full(b), static_cast<uint32_t>((i >> 1) & 1));
+    for (int k = 0;; ++k) {
+      const int i = 2 * k + b;
+      mbar_wait(acc_full(b), static_cast<uint32_t>(k & 1));
       const int t = *reinterpret_cast<volatile int*>(&tile_ring[i & 7]);
-      if (t < 0) { done[b] = true; continue; }
+      if (t < 0) break;
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
       tc_fence_after();
@@ -333,8 +332,7 @@ stem2_kernel(const Stem2Params p) {
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(b));   // this warp has read what it needs of accumulator set b
-      if (set == 0) asm volatile("bar.sync 4, %0;" ::"n"(128) : "memory");
-      else asm volatile("bar.sync 5, %0;" ::"n"(128) : "memory");
+      asm volatile("bar.sync %0, %1;" ::"r"(4 + 2 * b + set), "n"(128) : "memory");   // the set's 128 threads
       // the set's pooled rows: max of the two parities' candidates, 16 bytes (8 channels) per task
       const uint8_t* xe = x_gen + b * X_BYTES;
       const int ntask = npy * 7 * 8;
@@ -350,8 +348,8 @@ stem2_kernel(const Stem2Params p) {
         const int ph = pty * 7 + py, pw = ptx * 7 + px;
         *reinterpret_cast<uint4*>(p.out + ((static_cast<size_t>(n) * 56 + ph) * 56 + pw) * 64 + c8 * 8) = m;
       }
-      // the candidates buffer of parity b is rewritten two tiles from now; the set's next barrier (after it has
-      // written the OTHER buffer) orders these reads before those writes
+      // this group's candidates buffer is rewritten by its next tile: order these reads before those writes
+      asm volatile("bar.sync %0, %1;" ::"r"(4 + 2 * b + set), "n"(128) : "memory");
     }
   }
 
@@ -365,7 +363,7 @@ stem2_kernel(const Stem2Params p) {
       __threadfence();
     }
   }
-  if (warp == 8) {
+  if (warp == MMA_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
