@@ -59,6 +59,11 @@ struct ConvArgs {
   const CUtensorMap* tmO = nullptr;
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)
   int flat = 0;                   // 3x3/s1/p1, one N tile: flattened-row CTA-pair kernel (tmA = make_tmap_flat, tmB with BN/2 box rows)
+  // split-K (persistent kernel, A_TILED = FC layers): `splits` CTAs per output tile over disjoint k-block ranges;
+  // ws: fp32 [splits][rows padded to 128][ldw] scratch; ctr: one int per output tile, all zero between launches
+  int splits = 1, ldw = 0;
+  float* ws = nullptr;
+  int* ctr = nullptr;
 };
 
 // Flattened-row CTA-pair kernel (ResNet layer2 convolutions).

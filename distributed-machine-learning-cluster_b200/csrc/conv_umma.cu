@@ -49,6 +49,13 @@ struct KP {
   int f16;    // 16-bit tensors are IEEE half instead of bf16
   int rev;    // pair kernel: walk the tiles from the last to the first
   int nprod;  // pair kernel: warps that issue TMA requests (1..4), k-blocks dealt round-robin among them
+  // persistent kernel, split-K (FC layers with few rows: all SMs stream a share of the weights): `splits` CTAs
+  // compute one output tile over disjoint k-block ranges, each stores its accumulators in its own slice of `ws`
+  // (fp32 [splits][tiles_m * 128][ldw]) and the one that arrives last on `ctr[tile]` (all zero between launches)
+  // sums the slices in split order, runs the epilogue and re-zeroes the counter.
+  int splits, ldw;
+  float* ws;
+  int* ctr;
 };
 
 // Where one tile's results go.
@@ -391,19 +398,22 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 4];
   __shared__ uint32_t tmem_slot;
+  __shared__ int split_last;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t b_tile_bytes = static_cast<uint32_t>(p.BN) * 128u;
   const uint32_t stage_bytes = A_TILE_BYTES + b_tile_bytes;
+  const int splits = p.splits;                                   // 1 unless the launcher chose split-K
+  const int kb_per = (p.num_kb + splits - 1) / splits;           // k-blocks of one split (the last may be shorter, never empty)
   const uint32_t bar0 = smem_u32(bars);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (MAX_STAGES + s); };
   auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + b); };
   auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * MAX_STAGES + 2 + b); };
   const int tn_all = p.tiles_n + p.tiles_n2;
-  const int total_tiles = p.tiles_m * tn_all;
+  const int total_tiles = p.tiles_m * tn_all * splits;           // work items: (output tile, split), splits of a tile adjacent
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -433,14 +443,15 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       const int ohw = p.OH * p.OW;
       const uint32_t tx = b_tile_bytes + A_TILE_BYTES;
       int s = 0, ph = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int w = blockIdx.x; w < total_tiles; w += gridDim.x) {
+        const int t = w / splits, sp = w - t * splits;
         const int tm = t / tn_all;
         const int nn = t - tm * tn_all;
         const bool second = nn >= p.tiles_n;
         const int m0 = tm * BM;
         const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
-        const int kb_begin = second ? p.kb_first2 : 0;
-        const int kb_count = second ? p.num_kb2 : p.num_kb;
+        const int kb_begin = second ? p.kb_first2 : sp * kb_per;
+        const int kb_count = second ? p.num_kb2 : min(kb_per, p.num_kb - sp * kb_per);
         int iw_base = 0, ih_base = 0, n_base = 0;
         if (AMODE == A_IM2COL) {
           n_base = m0 / ohw;
@@ -476,12 +487,13 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   } else if (warp == 1) {
     const uint32_t idesc = umma_idesc_bf16(BM, p.BN, F16 ? 1 : 0);
     int s = 0, ph = 0, i = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+    for (int w = blockIdx.x; w < total_tiles; w += gridDim.x, ++i) {
+      const int t = w / splits, sp = w - t * splits;
       const int buf = i & 1;
       mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
-      const int kb_count = (t % tn_all) >= p.tiles_n ? p.num_kb2 : p.num_kb;
+      const int kb_count = (t % tn_all) >= p.tiles_n ? p.num_kb2 : min(kb_per, p.num_kb - sp * kb_per);
       for (int kb = 0; kb < kb_count; ++kb) {
         mbar_wait(full_bar(s), ph);
         tc_fence_after();
@@ -502,7 +514,8 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int n_chunks = p.BN >> 5;
     int i = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+    for (int w = blockIdx.x; w < total_tiles; w += gridDim.x, ++i) {
+      const int t = w / splits;
       const int buf = i & 1;
       const int tm = t / tn_all;
       const int nn = t - tm * tn_all;
@@ -519,6 +532,10 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
       const int last_c = ((n_chunks - 1 - half) & ~1) + half;
       if (last_c < 0) {                          // BN = 32: the second warp of the quarter has nothing to drain
         if (lane == 0) mbar_arrive(acc_empty_bar(buf));
+        if (splits > 1) {                        // still part of the split-K hand-shake below
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
         continue;
       }
       for (int c = half; c < n_chunks; c += 2) {
@@ -531,7 +548,50 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
           __syncwarp();
           if (lane == 0) mbar_arrive(acc_empty_bar(buf));
         }
-        if (row_ok) epilogue_chunk<F16>(epi, m, n0 + c * 32, v);
+        if (splits == 1) {
+          if (row_ok) epilogue_chunk<F16>(epi, m, n0 + c * 32, v);
+        } else if (row_ok) {
+          // this split's partial sums, in its own slice of the workspace (plain stores: the final sum below runs over
+          // the slices in a fixed order, so the result does not depend on which CTA finishes when)
+          float4* wsp = reinterpret_cast<float4*>(p.ws + (static_cast<size_t>(w - t * splits) * (p.tiles_m * BM) + m) * p.ldw + n0 + c * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            __stcg(wsp + j, make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                        __uint_as_float(v[4 * j + 3])));
+        }
+      }
+      if (splits > 1) {
+        // the split that arrives last on the tile's counter owns the epilogue: it adds the slices up (read past L1,
+        // split 0 first), writes the layer's output and puts the counter back to zero for the next launch
+        __threadfence();
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (threadIdx.x == 64) {
+          const int arrived = atomicAdd(p.ctr + t, 1);
+          split_last = arrived == splits - 1;
+          if (arrived == splits - 1) p.ctr[t] = 0;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (*reinterpret_cast<volatile int*>(&split_last)) {
+          __threadfence();
+          for (int c = half; c < n_chunks; c += 2) {
+            if (!row_ok) continue;
+            float acc[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+            for (int sp = 0; sp < splits; ++sp) {
+              const float4* wsp = reinterpret_cast<const float4*>(p.ws + (static_cast<size_t>(sp) * (p.tiles_m * BM) + m) * p.ldw + n0 + c * 32);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 f = __ldcg(wsp + j);
+                acc[4 * j] += f.x; acc[4 * j + 1] += f.y; acc[4 * j + 2] += f.z; acc[4 * j + 3] += f.w;
+              }
+            }
+            uint32_t v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
+            epilogue_chunk<F16>(epi, m, n0 + c * 32, v);
+          }
+        }
       }
     }
   }
@@ -1316,6 +1376,10 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->f16 = a.f16;
   p->rev = a.reverse;
   p->nprod = 1;
+  p->splits = 1;
+  p->ldw = 0;
+  p->ws = nullptr;
+  p->ctr = nullptr;
 }
 
 template <int AMODE, bool F16>
@@ -1343,7 +1407,16 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
   const int total = p.tiles_m * p.tiles_n;
   const int grid = total < sm_count[dev] ? total : sm_count[dev];
   const size_t smem = conv_umma_smem_bytes(a.BN, p.stages);
-  const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2);
+  if (a.splits > 1 && a.ws && a.ctr && p.tiles_n2 == 0 && AMODE == A_TILED) {
+    // keep every split non-empty: kb_per = ceil(num_kb / splits) and (splits - 1) * kb_per < num_kb
+    int sp = std::min(a.splits, p.num_kb);
+    while (sp > 1 && (sp - 1) * ((p.num_kb + sp - 1) / sp) >= p.num_kb) --sp;
+    p.splits = sp;
+    p.ws = a.ws;
+    p.ctr = a.ctr;
+    p.ldw = a.ldw;
+  }
+  const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2) * p.splits;
   const int grid2 = total2 < sm_count[dev] ? total2 : sm_count[dev];
   (void)grid;
   return launch_pdl(kern, dim3(static_cast<unsigned>(grid2)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);

@@ -3,8 +3,9 @@
 // decodes one image at a time on the calling thread.  The decoder is NVIDIA's nvJPEG, loaded with
 // dlopen at first use: libb200infer.so itself keeps linking nothing but the static CUDA runtime, and
 // every entry point that needs the decoder reports B2I_ENODEV-style errors when the library is absent.
-// Backends are tried in this order: the NVJPG hardware engines (baseline JPEG, batched), GPU-assisted
-// Huffman decode (batched), the hybrid CPU-Huffman decoder (per image).
+// Backends: the NVJPG hardware engines where the device exposes them (baseline JPEG, batched), else the hybrid
+// decoder (entropy decoding on a pool of host threads, one nvJPEG state each; IDCT and colour conversion on the
+// GPU); GPU-assisted Huffman decode on request (B2I_JPEG_BACKEND=gpu; slower than the host threads here).
 //
 // Decoders differ by +-1-2 LSB per pixel (stb in the reference, libjpeg-turbo under PIL, nvJPEG here;
 // SURVEY.md 8c R2), so parity of this stage is defined from the decoded pixels on: the tests read them

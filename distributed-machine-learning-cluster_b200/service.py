@@ -268,45 +268,53 @@ class Leader:
     def jobs(self):
         return [self.resnet18, self.alexnet]
 
-    def run_job(self, job, batch=32, limit=None, log=None):
+    def run_job(self, job, batch=32, limit=None, log=None, in_flight=2):
         """Batched `run_job`: resumes at labels[finished_prediction_count..] (services.rs:410-411),
         sends `batch` ids per predict call to the job's assigned GPUs, skips the labels silently when
         nobody is assigned (services.rs:416), records one duration per query = the wall time of the
         batch that carried it, and prints the reference's result lines (services.rs:425-429).  Every
         answer is scored against ITS OWN label; an id that produced no answer (empty or missing
         directory, undecodable file) is a lost query, as in the reference, and costs nothing else.
-        The files of batch i+1 are read while batch i is on the GPU."""
+        `in_flight` batches are in progress at once (the reference spawns one task per query and never
+        waits for the previous one, services.rs:418): while one batch is on the GPU the next one's files
+        are read and decoded.  Results are accounted in label order."""
         start_at = job.finished_prediction_count
         todo = self.labels[start_at:] if limit is None else self.labels[start_at:start_at + limit]
         chunks = [todo[i:i + batch] for i in range(0, len(todo), batch)]
-        ahead = ThreadPoolExecutor(max_workers=1)
-        fetch = lambda c: self.member.read_ids([wnid for wnid, _ in c])
-        nxt = ahead.submit(fetch, chunks[0]) if chunks else None
+
+        def one(chunk):
+            ids = list(job.assigned_member_ids)
+            if not ids:
+                return None, 0.0
+            devices = (min(ids), max(ids) - min(ids) + 1)
+            t0 = time.perf_counter()
+            wn = [wnid for wnid, _ in chunk]
+            res = self.member.predict_each(job.model_name, wn, devices=devices, blobs=self.member.read_ids(wn))
+            return res, time.perf_counter() - t0
+
+        workers = ThreadPoolExecutor(max_workers=max(1, in_flight))
         try:
-            for ci, chunk in enumerate(chunks):
-                blobs = nxt.result()
-                nxt = ahead.submit(fetch, chunks[ci + 1]) if ci + 1 < len(chunks) else None
-                ids = list(job.assigned_member_ids)
-                if not ids:
-                    continue
-                devices = (min(ids), max(ids) - min(ids) + 1)
-                t0 = time.perf_counter()
-                res = self.member.predict_each(job.model_name, [wnid for wnid, _ in chunk], devices=devices, blobs=blobs)
-                dt = time.perf_counter() - t0
-                if res is None:
-                    continue
-                for (wnid, true_label), r in zip(chunk, res):
-                    if isinstance(r, str):          # SKIPPED / UNDECODABLE / MISSING: no answer for this id
+            pending = []
+            for ci in range(len(chunks) + in_flight):
+                if ci < len(chunks):
+                    pending.append((chunks[ci], workers.submit(one, chunks[ci])))
+                if ci >= in_flight - 1 and pending:
+                    chunk, fut = pending.pop(0)
+                    res, dt = fut.result()
+                    if res is None:
                         continue
-                    prob, pred = r
-                    job.add_query_result(pred == true_label, dt)
-                    if log:
-                        if pred == true_label:
-                            log("%s - %s: %s (%.2f%%)" % (job.model_name, wnid, pred, prob * 100.0))
-                        else:
-                            log("%s - %s: %s (%.2f%%) (should be %s)" % (job.model_name, wnid, pred, prob * 100.0, true_label))
+                    for (wnid, true_label), r in zip(chunk, res):
+                        if isinstance(r, str):          # SKIPPED / UNDECODABLE / MISSING: no answer for this id
+                            continue
+                        prob, pred = r
+                        job.add_query_result(pred == true_label, dt)
+                        if log:
+                            if pred == true_label:
+                                log("%s - %s: %s (%.2f%%)" % (job.model_name, wnid, pred, prob * 100.0))
+                            else:
+                                log("%s - %s: %s (%.2f%%) (should be %s)" % (job.model_name, wnid, pred, prob * 100.0, true_label))
         finally:
-            ahead.shutdown(wait=True)
+            workers.shutdown(wait=True)
 
     def predict(self, batch=32, limit=None, log=None):
         """`Leader::predict` (services.rs:146-151) joins both jobs; they run on disjoint GPU halves."""

@@ -151,13 +151,15 @@ int b2i_predict_raw_u8_status(b2i_model* m, int first_dev, int n_dev, const uint
 /* `Member::predict` from the FILE CONTENTS on: the reference decodes each JPEG on the handler's thread
  * (stb, inside load_image_and_resize, services.rs:492); here jpeg[i] / len[i] is one encoded stream in
  * host memory and the whole batch is decoded on the GPU (nvJPEG, loaded with dlopen when this is first
- * called: NVJPG hardware engines where the device has them, else GPU-assisted or multi-threaded hybrid
- * decode), resized + cropped by the b2i_resize_crop_u8 kernels straight into the device batch and run
+ * called: NVJPG hardware engines where the device exposes them, else entropy decoding on a pool of host
+ * threads with the IDCT on the GPU), resized + cropped by the b2i_resize_crop_u8 kernels straight into the device batch and run
  * through the network. status[i]: B2I_OK, B2I_EDECODE (not a decodable JPEG; that image gets idx -1 /
  * prob 0, the others are answered) or B2I_EINVAL (a side longer than 16384). Fails with B2I_ENODEV when
  * libnvjpeg.so.12 is not installed; callers then decode on the host (the thread pool in service.py) and
  * use b2i_predict_raw_u8_status. Decoders differ by a few LSB per pixel (stb, libjpeg,
- * nvJPEG), so results are compared with the CPU restatement on the pixels b2i_jpeg_decode_u8 returns. */
+ * nvJPEG), so results are compared with the CPU restatement on the pixels b2i_jpeg_decode_u8 returns.
+ * Unlike the other predict calls this one (and b2i_predict_raw_u8[_status]) holds the model's lock only for
+ * its GPU part: two threads calling it on one model overlap one batch's decode with the other's forward. */
 int b2i_predict_jpeg(b2i_model* m, int first_dev, int n_dev, const uint8_t* const* jpeg, const size_t* len,
                      int n, int k, int32_t* idx, float* prob, float* logits, int* status);
 /* The decode stage alone: *h, *w always; when out != NULL also the RGB pixels u8 [h][w][3] (cap >= h*w*3). */
