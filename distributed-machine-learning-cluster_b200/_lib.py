@@ -80,6 +80,7 @@ SIGNATURES = {
     "b2i_model_tensor_shape": (_i, [_vp, _i, _ip, _ip, _ip]),
     "b2i_op_conv2d": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "b2i_op_linear": (_i, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _i, _i, _vp]),
+    "b2i_op_linear_splitk": (_i, [_vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _i, _i, _vp]),
     "b2i_op_maxpool": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "b2i_op_adaptive_avgpool": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "b2i_op_normalize": (_i, [_vp, _i, _i, _vp, _i, _vp]),

@@ -654,8 +654,8 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
   });
 }
 
-int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float* x, int M, int K,
-                  const float* w, const float* bias, int Cout, int relu, float* out) {
+static int op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, int splits, const float* x, int M, int K,
+                     const float* w, const float* bias, int Cout, int relu, float* out) {
   return guarded([&]() -> int {
     if (int rc = ctx_dev(ctx, dev)) return rc;
     if (!x || !w || !out || M < 1 || K < 1 || Cout < 1) return fail(B2I_EINVAL, "b2i_op_linear: bad argument");
@@ -682,6 +682,14 @@ int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float*
     bnv = std::min(bnv, 256) / 32 * 32;
     while (bnv > 32 && cs.Cout_pad % bnv) bnv -= 32;
     a.BN = bnv; a.stages = conv_umma_pick_stages(bnv); a.amode = A_TILED; a.b_tma = 1;
+    DevBuf dws, dctr;
+    if (splits > 1 && precision != B2I_PREC_FP32) {
+      const size_t rows = static_cast<size_t>((M + 127) / 128) * 128;
+      CAPI_CUDA(dws.alloc(static_cast<size_t>(splits) * rows * cs.Cout_pad * 4));
+      CAPI_CUDA(dctr.alloc(4096 * 4));
+      CAPI_CUDA(cudaMemset(dctr.p, 0, 4096 * 4));
+      a.splits = splits; a.ws = static_cast<float*>(dws.p); a.ctr = static_cast<int*>(dctr.p); a.ldw = cs.Cout_pad;
+    }
     if (precision == B2I_PREC_FP32) {
       CAPI_CUDA(launch_conv_fp32(a, nullptr));
     } else {
@@ -694,6 +702,19 @@ int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float*
     CAPI_CUDA(cudaDeviceSynchronize());
     CAPI_CUDA(cudaMemcpy(out, dout.p, nout * 4, cudaMemcpyDeviceToHost));
     return B2I_OK;
+  });
+}
+
+int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float* x, int M, int K,
+                  const float* w, const float* bias, int Cout, int relu, float* out) {
+  return guarded([&]() -> int { return op_linear(ctx, dev, precision, tile_n, 1, x, M, K, w, bias, Cout, relu, out); });
+}
+
+int b2i_op_linear_splitk(b2i_ctx* ctx, int dev, int precision, int tile_n, int splits, const float* x, int M, int K,
+                         const float* w, const float* bias, int Cout, int relu, float* out) {
+  return guarded([&]() -> int {
+    if (splits < 1 || splits > 64) return fail(B2I_EINVAL, "b2i_op_linear_splitk: splits must be in 1..64");
+    return op_linear(ctx, dev, precision, tile_n, splits, x, M, K, w, bias, Cout, relu, out);
   });
 }
 

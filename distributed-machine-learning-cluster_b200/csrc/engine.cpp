@@ -563,6 +563,29 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
     }
   }
   op_names_.push_back("softmax_topk");
+  // Split-K scratch for the FC layers of the 16-bit path (few rows, many weights: the k-blocks of one output tile
+  // are spread over several CTAs so that every SM streams a share of the weight matrix).  B2I_NO_SPLITK=1: off.
+  static const bool splitk_on = [] { const char* e = getenv("B2I_NO_SPLITK"); return !(e && e[0] == '1'); }();
+  if (cfg_.precision != PREC_FP32 && splitk_on) {
+    size_t need = 0;
+    for (const DevOp& d : ops_)
+      if (d.spec.kind == OpSpec::CONV && d.spec.fc && !d.pair) {
+        const size_t tiles_m = (static_cast<size_t>(mb_) + 127) / 128;
+        need = std::max(need, static_cast<size_t>(16) * tiles_m * 128 * d.g.Cout_pad * 4 / std::max<size_t>(1, tiles_m));
+      }
+    if (need) {
+      void* w = nullptr;
+      void* c = nullptr;
+      B2I_CUDA(cudaMalloc(&w, need));
+      B2I_CUDA(cudaMalloc(&c, 4096 * 4));
+      B2I_CUDA(cudaMemset(c, 0, 4096 * 4));
+      owned_.push_back(w);
+      owned_.push_back(c);
+      splitk_ws_ = static_cast<float*>(w);
+      splitk_ctr_ = static_cast<int*>(c);
+      splitk_ws_bytes_ = need;
+    }
+  }
   // A 1x1 / stride-s / pad-0 conv followed by a 3x3 / stride-s / pad-1 conv on the same input (the
   // ResNet downsample and the block's first conv) read the same pixels: the 1x1 conv's input is the
   // centre tap of the 3x3 window.  Compute the former as extra N-tiles of the latter's kernel.
@@ -654,6 +677,20 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         static const bool snake = [] { const char* e = getenv("B2I_NO_SNAKE"); return !(e && e[0] == '1'); }();
         a.reverse = (snake && (d.patch || d.flat || d.pair) && !o.fc) ? (patch_seq++ & 1) ^ 1 : 0;
         a.f16 = f16;
+        if (o.fc && !d.pair && splitk_ws_ && d.amode == A_TILED) {
+          // enough (tile, split) work items for two per SM, at least four k-blocks each, within the scratch
+          const int tiles_mn = ((nb + 127) / 128) * (d.g.Cout_pad / d.BN);
+          int sp = std::min(16, std::max(1, 296 / std::max(1, tiles_mn)));
+          sp = std::min(sp, std::max(1, (d.g.K / 64) / 4));
+          const size_t per_split = static_cast<size_t>((nb + 127) / 128) * 128 * d.g.Cout_pad * 4;
+          sp = static_cast<int>(std::min<size_t>(sp, splitk_ws_bytes_ / per_split));
+          if (sp > 1 && tiles_mn <= 4096) {
+            a.splits = sp;
+            a.ws = splitk_ws_;
+            a.ctr = splitk_ctr_;
+            a.ldw = d.g.Cout_pad;
+          }
+        }
         if (d.fused_second >= 0) {
           const DevOp& s2 = ops_[d.fused_second];
           const int cpb = d.g.C >> 6;

@@ -144,6 +144,9 @@ class DeviceModel {
   std::vector<size_t> buf_bytes_;
   std::vector<void*> owned_;         // weight allocations
   unsigned int* stem_sched_ = nullptr;
+  float* splitk_ws_ = nullptr;       // FC split-K: per-split partial sums (fp32), see conv_umma.cu
+  int* splitk_ctr_ = nullptr;        // one arrival counter per output tile, zero between launches
+  size_t splitk_ws_bytes_ = 0;
   int logits_tensor_ = -1;
   size_t weight_bytes_ = 0, act_bytes_ = 0;
 };

@@ -194,7 +194,7 @@ stem2_kernel(const Stem2Params p) {
     constexpr int GROUPS = PATCH_W / 4;                                       // 10 four-pixel tasks per patch row
     constexpr int TASKS = PATCH_H * GROUPS;                                   // 370
     constexpr int ROUNDS = (TASKS + S2_GROUP - 1) / S2_GROUP;                 // 3
-    // (u/255 - mean)/std as one FMA per byte (bit-identical after rounding to 16 bits: tests/test_oracle.py)
+    // (u/255 - mean)/std as one FMA per byte (bit-identical after rounding to 16 bits: checked exhaustively by the CPU tests)
     const float na[3] = {0x1.18926cp-6f, 0x1.1ed5b2p-6f, 0x1.1d8f56p-6f};
     const float nb[3] = {-0x1.0f177ap+1f, -0x1.04924ap+1f, -0x1.cdf012p+0f};
     int t = 2 * blockIdx.x + g;              // first tile of this group; the rest come from the global counter

@@ -61,14 +61,19 @@ class Context:
                                        _ptr(out)))
         return out
 
-    def linear(self, x, w, bias=None, relu=False, precision=PREC_BF16, tile_n=0, dev=0):
+    def linear(self, x, w, bias=None, relu=False, precision=PREC_BF16, tile_n=0, dev=0, splits=1):
+        """x [M,K] fp32, w [Cout,K] fp32 -> [M,Cout] fp32; splits > 1: split-K over that many CTAs per output tile."""
         x, w = _f32(x), _f32(w)
         M, K = x.shape
         Cout = w.shape[0]
         out = np.empty((M, Cout), np.float32)
         b = _f32(bias) if bias is not None else None
-        check(_lib.lib().b2i_op_linear(self._h, dev, precision, tile_n, _ptr(x), M, K, _ptr(w), _ptr(b), Cout,
-                                       int(relu), _ptr(out)))
+        if splits > 1:
+            check(_lib.lib().b2i_op_linear_splitk(self._h, dev, precision, tile_n, splits, _ptr(x), M, K, _ptr(w), _ptr(b),
+                                                  Cout, int(relu), _ptr(out)))
+        else:
+            check(_lib.lib().b2i_op_linear(self._h, dev, precision, tile_n, _ptr(x), M, K, _ptr(w), _ptr(b), Cout,
+                                           int(relu), _ptr(out)))
         return out
 
     def maxpool(self, x, k, stride, pad, precision=PREC_BF16, dev=0):

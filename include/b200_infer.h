@@ -255,6 +255,11 @@ int b2i_op_conv2d(b2i_ctx* ctx, int dev, int precision, int conv_mode, int weigh
 /* linear (+bias, ReLU): x [M][K], w [Cout][K], out [M][Cout]. */
 int b2i_op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, const float* x, int M, int K,
                   const float* w, const float* bias, int Cout, int relu, float* out);
+/* The same with the K dimension of every output tile split over `splits` CTAs (the FC layers of a small batch:
+ * few rows, a large weight matrix that all SMs should stream); partial sums are added in split order, so the
+ * result is reproducible run to run. 16-bit precisions only; splits = 1 is b2i_op_linear. */
+int b2i_op_linear_splitk(b2i_ctx* ctx, int dev, int precision, int tile_n, int splits, const float* x, int M,
+                         int K, const float* w, const float* bias, int Cout, int relu, float* out);
 int b2i_op_maxpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, int H, int W, int C,
                    int k, int stride, int pad, float* out);
 int b2i_op_adaptive_avgpool(b2i_ctx* ctx, int dev, int precision, const float* x, int N, int H,
