@@ -666,9 +666,9 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
 // requests of ONE issuing warp do not overlap each other, but requests of different warps do (tools/microbench/
 // tma_rate.cu, two-issuer rows: the per-SM rate doubles with two warps or two CTAs).  So the k-blocks are dealt
 // round-robin to `nprod` producer warps (warp 0 and warps 10 ..), each walking the same tile / stage sequence
-// and issuing every nprod-th request: with four of them a request completes every ~240 cycles, under the MMA
+// and issuing every nprod-th request: with three of them a request completes every ~300 cycles, around the MMA
 // time of a k-block (256 cycles at tile-N 128, 512 at 256).
-constexpr int PAIR_MAX_PROD = 4;
+constexpr int PAIR_MAX_PROD = 3;   // 384 threads: one more warp would push the epilogue warps under the registers they need (spills)
 constexpr int PAIR_THREADS = PTHREADS + 32 * (PAIR_MAX_PROD - 1);
 template <int AMODE, bool F16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PAIR_THREADS, 1)

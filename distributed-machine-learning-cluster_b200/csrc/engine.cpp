@@ -469,8 +469,8 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       // feeds msub times the MMAs per request.  It also divides the number of tiles, and when msub * BN exceeds 256
       // TMEM columns only one accumulator set fits (the epilogue no longer overlaps the next tile).  Pick tile-N and
       // msub by an estimate of the launch time at the full micro-batch: waves x (k-blocks x max(request, MMAs) +
-      // exposed epilogue).  At batch 256 it keeps (256, 1) for layer3, takes (128, 2) for layer2.0.conv1 and
-      // (256, 2) for the 3x3 convs of layer4.  msub is 1, 2 or 4: a 384-pixel request faults on B200 (measured).
+      // exposed epilogue + per-tile set-up).  At batch 256 it keeps (256, 1) for layer3 and layer4 and takes (128, 2)
+      // for layer2.0.conv1, which is what an A/B over (msub, producers) measured (profiles/r03_msub_nprod_matrix.txt).  msub is 1, 2 or 4: a 384-pixel request faults on B200 (measured).
       // B2I_MSUB=1 / 2 / 4 forces msub (tile-N unchanged).
       d.msub = 1;
       if (d.pair && !d.flat && !o.fc && d.amode == A_IM2COL && g.R > 1) {
@@ -485,11 +485,13 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         auto est = [&](int bn, int ms) {
           const long long units = ((M + 256 * ms - 1) / (256 * ms)) * (c.Cout_pad / bn) * (carries ? 2 : 1);
           const long long waves = (units + 73) / 74;
-          const long long req = ms <= 2 ? 700 : (ms == 3 ? 730 : 764);
+          // requests of different issuing warps overlap (tools/microbench/tma_rate.cu, two-issuer rows): with the pair
+          // kernel's three producer warps one completes every req / 3 cycles
+          const long long req = (ms <= 2 ? 700 : (ms == 3 ? 730 : 764)) / 3;
           const long long kb_cycles = std::max<long long>(req, static_cast<long long>(ms) * 4 * (bn / 2));
           const long long epi = (2 * ms * bn > 512) ? 10000 : 0;
           const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
-          return waves * (kb_avg * kb_cycles + epi);
+          return waves * (kb_avg * kb_cycles + epi + 600);   // + per-tile set-up (barrier turn-around, bias / residual fetch)
         };
         if (msub_env == 1 || msub_env == 2 || msub_env == 4) {
           if (fits(d.BN, msub_env)) d.msub = msub_env;

@@ -22,13 +22,13 @@
 //     3-tap max, and the vertical max of the two same-parity rows, are register operations on raw accumulators
 //     (+bias, ReLU and the rounding are monotone, so they commute with max and are applied once per POOLED value).
 //     Only the pooled values cross threads: 2 x 6 KB per tile through shared memory instead of 32 KB + 56 KB.
-// One CTA per SM (all 512 TMEM columns: two accumulator sets of 128 + 144 of weights), 25 warps; tiles alternate
+// One CTA per SM (all 512 TMEM columns: two accumulator sets of 128 + 144 of weights), 26 warps; tiles alternate
 // between two loader groups and two epilogue groups (even / odd tile of the CTA's sequence = patch buffer =
 // accumulator set), because both are latency chains (global loads; TMEM loads feeding dependent max chains)
 // that take longer than the MMAs of a tile:
 //   warps 0-15  two epilogue groups of eight warps: two sets (pooled rows 0-3 / 4-6) x four TMEM lane quarters
-//   warp  16    MMA issue
-//   warps 17-24 two loader groups of four warps
+//   warps 16-17 MMA issue, one per half of the tile's columns
+//   warps 18-25 two loader groups of four warps
 #include "conv.h"
 #include "ops.h"
 #include "ptx.cuh"
@@ -38,7 +38,8 @@ namespace {
 
 constexpr int S2_DRAIN = 512;
 constexpr int S2_GROUP = 128;                          // threads of one loader group
-constexpr int S2_THREADS = S2_DRAIN + 32 + 2 * S2_GROUP;
+constexpr int S2_MMA_WARPS = 2;                         // one per half of the tile's columns: see the kernel
+constexpr int S2_THREADS = S2_DRAIN + 32 * S2_MMA_WARPS + 2 * S2_GROUP;
 constexpr int PATCH_H = 37, PATCH_W = 40;              // pixels of 8 bytes (r, g, b, 0 in the 16-bit storage format)
 constexpr uint32_t PATCH_ROW_BYTES = PATCH_W * 8;      // 320
 constexpr uint32_t PATCH_BYTES = ((PATCH_H * PATCH_W * 8 + 127) / 128) * 128;
@@ -123,8 +124,8 @@ stem2_kernel(const Stem2Params p) {
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
       mbar_init(patch_full(b), S2_GROUP);
-      mbar_init(patch_empty(b), 1);
-      mbar_init(acc_full(b), 1);
+      mbar_init(patch_empty(b), S2_MMA_WARPS);   // one commit per MMA-issuing warp
+      mbar_init(acc_full(b), S2_MMA_WARPS);
       mbar_init(acc_empty(b), 8);
     }
     mbar_fence_init();
@@ -153,8 +154,14 @@ stem2_kernel(const Stem2Params p) {
   tc_fence_after();
   griddep_wait();   // the pooled map written below may still be read by the previous forward's kernels
 
-  if (warp == MMA_WARP) {
+  if (warp >= MMA_WARP && warp < MMA_WARP + S2_MMA_WARPS) {
     // ------------------------------------------------------------------ MMA issue
+    // Two issuing warps, one per half of the tile's conv columns (its own 64 accumulator columns, the same
+    // weights): an MMA of this size occupies the tensor pipe for 32 cycles, but the instructions that bring its
+    // operands into uniform registers take a warp about 50 (ncu: the single issuing warp was busy 60 % of the
+    // time with the pipe 44 % active).  tcgen05.commit tracks the MMAs of the committing thread, so both warps
+    // commit and the barriers count two arrivals.
+    const int hx = warp - MMA_WARP;
     const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
     bool done[2] = {false, false};
     for (int i = 0;; ++i) {
@@ -173,8 +180,7 @@ stem2_kernel(const Stem2Params p) {
       }
       tc_fence_after();
       const uint32_t pbase = patch0 + b * PATCH_BYTES;
-#pragma unroll
-      for (int hx = 0; hx < 2; ++hx) {          // conv columns 0-7 / 8-15 of the tile
+      {                                         // conv columns 8 * hx .. 8 * hx + 7 of the tile
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + hx * 64);
 #pragma unroll
         for (int t = 0; t < KCHUNKS; ++t) {      // input row rho = t / 2 under the pair's even conv row, taps 4 * (t & 1) .. + 3
@@ -185,10 +191,10 @@ stem2_kernel(const Stem2Params p) {
       umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
       umma_commit_elect(acc_full(b));
     }
-  } else if (warp > MMA_WARP) {
+  } else if (warp >= MMA_WARP + S2_MMA_WARPS) {
     // ------------------------------------------------------------------ patch loaders: group g fills buffer g
-    const int g = (warp - MMA_WARP - 1) >> 2;
-    const int lt = tid - (S2_DRAIN + 32) - g * S2_GROUP;
+    const int g = (warp - MMA_WARP - S2_MMA_WARPS) >> 2;
+    const int lt = tid - (S2_DRAIN + 32 * S2_MMA_WARPS) - g * S2_GROUP;
     uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));
     __shared__ int next_tile[2];
     constexpr int GROUPS = PATCH_W / 4;                                       // 10 four-pixel tasks per patch row
