@@ -689,6 +689,7 @@ static int op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, int split
       CAPI_CUDA(dctr.alloc(4096 * 4));
       CAPI_CUDA(cudaMemset(dctr.p, 0, 4096 * 4));
       a.splits = splits; a.ws = static_cast<float*>(dws.p); a.ctr = static_cast<int*>(dctr.p); a.ldw = cs.Cout_pad;
+      if (M <= 120) a.a_rows = std::max(8, (M + 7) / 8 * 8);   // the A box no taller than the batch, as the engine builds it
     }
     if (precision == B2I_PREC_FP32) {
       CAPI_CUDA(launch_conv_fp32(a, nullptr));
@@ -696,7 +697,7 @@ static int op_linear(b2i_ctx* ctx, int dev, int precision, int tile_n, int split
       CUtensorMap tmA, tmB;
       const char* terr = "";
       if (make_tmap_weights(&tmB, dw.p, cs.Cout_pad, cs.K, a.BN, &terr)) return fail(B2I_ECUDA, terr);
-      if (make_tmap_rows(&tmA, dx.p, M, cs.K, 128, &terr)) return fail(B2I_ECUDA, terr);
+      if (make_tmap_rows(&tmA, dx.p, M, cs.K, a.a_rows, &terr)) return fail(B2I_ECUDA, terr);
       CAPI_CUDA(launch_conv_umma(a, &tmA, &tmB, nullptr));
     }
     CAPI_CUDA(cudaDeviceSynchronize());

@@ -64,6 +64,7 @@ struct ConvArgs {
   int splits = 1, ldw = 0;
   float* ws = nullptr;
   int* ctr = nullptr;
+  int a_rows = 128;               // A_TILED, persistent kernel: box rows of tmA (a multiple of 8 below 128 when the layer has one M tile)
 };
 
 // Flattened-row CTA-pair kernel (ResNet layer2 convolutions).

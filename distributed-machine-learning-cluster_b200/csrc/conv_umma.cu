@@ -56,6 +56,7 @@ struct KP {
   int splits, ldw;
   float* ws;
   int* ctr;
+  int a_rows;   // persistent kernel, A_TILED: rows of the A box (the tensor map's), 128 unless the layer has fewer rows
 };
 
 // Where one tile's results go.
@@ -441,7 +442,10 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
     if (lane == 0) {
       const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
       const int ohw = p.OH * p.OW;
-      const uint32_t tx = b_tile_bytes + A_TILE_BYTES;
+      // A_TILED with fewer than 128 rows in the layer: the map's box holds only those rows (the TMA unit spends about
+      // 3.5 cycles per 128-byte row it moves, zero-filled or not, and that, not HBM, is what limits an FC layer
+      // on a small batch); the MMA still reads 128 rows, the rest are whatever the ring held and are never stored
+      const uint32_t tx = b_tile_bytes + (AMODE == A_TILED ? static_cast<uint32_t>(p.a_rows) * 128u : static_cast<uint32_t>(A_TILE_BYTES));
       int s = 0, ph = 0;
       for (int w = blockIdx.x; w < total_tiles; w += gridDim.x) {
         const int t = w / splits, sp = w - t * splits;
@@ -1376,6 +1380,7 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->f16 = a.f16;
   p->rev = a.reverse;
   p->nprod = 1;
+  p->a_rows = BM;
   p->splits = 1;
   p->ldw = 0;
   p->ws = nullptr;
@@ -1416,6 +1421,7 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
     p.ctr = a.ctr;
     p.ldw = a.ldw;
   }
+  if (AMODE == A_TILED && a.a_rows >= 8 && a.a_rows < BM && (a.a_rows & 7) == 0 && p.tiles_m == 1) p.a_rows = a.a_rows;
   const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2) * p.splits;
   const int grid2 = total2 < sm_count[dev] ? total2 : sm_count[dev];
   (void)grid;

@@ -434,6 +434,34 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         else if (tiles256 < 148) bn = std::min(bn, 64);
       }
       while (bn > 32 && c.Cout_pad % bn) bn -= 32;
+      // FC layers of the 16-bit path: tile width, split-K factor and A-box rows from a model of what limits them.
+      // Measured (AlexNet classifier, batch 32 and 256): the kernel is bound by the TMA unit, which spends about 62
+      // cycles per request plus 3.5 per 128-byte row it moves, so a k-block costs 124 + 3.5 x (A rows + tile width)
+      // cycles whatever the MMAs need; an FC layer is fast when few rows carry many weight bytes (wide tiles, an A
+      // box no taller than the batch) and every SM has a share (split-K).  The factor is fixed per layer at load
+      // time, so an image's logits do not depend on the size of the batch it arrives in.  B2I_NO_SPLITK=1: off.
+      static const bool fc_plan_on = [] { const char* e = getenv("B2I_NO_SPLITK"); return !(e && e[0] == '1'); }();
+      bool fc_planned = false;
+      if (o.fc && fc_bn < 32 && cfg_.precision != PREC_FP32 && fc_plan_on) {
+        const int tiles_m = (mb_ + 127) / 128;
+        const int a_rows = tiles_m == 1 ? std::max(8, (mb_ + 7) / 8 * 8) : 128;
+        const int kb = c.K / 64;
+        double best = 1e30;
+        for (int cand : {64, 128, 256}) {
+          if (cand > std::min(cfg_.bn_max, 256) || c.Cout_pad % cand) continue;
+          for (int sp : {1, 2, 3, 4, 6, 8, 12, 16}) {
+            const int kb_per = (kb + sp - 1) / sp;
+            if (sp > 1 && (kb_per < 4 || (sp - 1) * kb_per >= kb)) continue;
+            const double items = static_cast<double>(tiles_m) * (c.Cout_pad / cand) * sp;
+            const double waves = std::ceil(items / 148.0);
+            const double ws_cycles = sp > 1 ? static_cast<double>(sp) * mb_ * c.Cout_pad * 8.0 / (148.0 * 40.0) : 0.0;
+            const double cost = waves * (kb_per * (124.0 + 3.5 * (a_rows + cand)) + 2500.0 + (sp > 1 ? 1500.0 : 0.0)) + ws_cycles;
+            if (cost < best) { best = cost; bn = cand; d.splits = sp; }
+          }
+        }
+        d.a_rows = a_rows;
+        fc_planned = best < 1e30;
+      }
       d.BN = bn;
       d.stages = conv_umma_pick_stages(bn);
       d.b_tma = cfg_.b_tma;
@@ -444,7 +472,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       d.patch = (cfg_.patch_conv && cfg_.precision != PREC_FP32 && !o.fc && d.amode == A_IM2COL && conv_patch_applicable(g))
                     ? 1 : 0;
       if (d.patch) d.BN = 64;
-      d.pair = (cfg_.pair_mma && cfg_.precision != PREC_FP32 && !d.patch && d.BN >= cfg_.pair_mma &&
+      d.pair = (cfg_.pair_mma && cfg_.precision != PREC_FP32 && !d.patch && d.BN >= cfg_.pair_mma && !fc_planned &&
                 (d.amode == A_IM2COL || d.amode == A_TILED)) ? 1 : 0;
       // One N-tile whose weights fit in shared memory next to four A stages (ResNet layer2): CTA pairs with
       // resident weights, whatever pair_mma says about the tile width.  B2I_NO_RESB=1 turns this off.
@@ -510,7 +538,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         }
       }
 
-      if (getenv("B2I_PLAN_DEBUG")) fprintf(stderr, "[plan] %s BN %d pair %d msub %d resb %d flat %d patch %d\n", c.name.c_str(), d.BN, d.pair, d.msub, d.resident_b, d.flat, d.patch);
+      if (getenv("B2I_PLAN_DEBUG")) fprintf(stderr, "[plan] %s BN %d pair %d msub %d resb %d flat %d patch %d splits %d a_rows %d\n", c.name.c_str(), d.BN, d.pair, d.msub, d.resident_b, d.flat, d.patch, d.splits, d.a_rows);
       const size_t wn = c.w.size();
       if (cfg_.precision == PREC_FP32) {
         B2I_CUDA(cudaMalloc(&d.w, wn * 4));
@@ -549,7 +577,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           if (make_tmap_im2col_px(&d.tmA, xin, g, mb_, 128 * d.msub, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_TILED) {
-          if (make_tmap_rows(&d.tmA, xin, mb_, c.K, 128, &terr)) { *err = c.name + ": " + terr; return false; }
+          if (make_tmap_rows(&d.tmA, xin, mb_, c.K, d.pair ? 128 : d.a_rows, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         }
       }
@@ -567,14 +595,12 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
   op_names_.push_back("softmax_topk");
   // Split-K scratch for the FC layers of the 16-bit path (few rows, many weights: the k-blocks of one output tile
   // are spread over several CTAs so that every SM streams a share of the weight matrix).  B2I_NO_SPLITK=1: off.
-  static const bool splitk_on = [] { const char* e = getenv("B2I_NO_SPLITK"); return !(e && e[0] == '1'); }();
-  if (cfg_.precision != PREC_FP32 && splitk_on) {
+  // Split-K scratch for the FC layers (per-split partial sums + one arrival counter per output tile).
+  {
     size_t need = 0;
     for (const DevOp& d : ops_)
-      if (d.spec.kind == OpSpec::CONV && d.spec.fc && !d.pair) {
-        const size_t tiles_m = (static_cast<size_t>(mb_) + 127) / 128;
-        need = std::max(need, static_cast<size_t>(16) * tiles_m * 128 * d.g.Cout_pad * 4 / std::max<size_t>(1, tiles_m));
-      }
+      if (d.spec.kind == OpSpec::CONV && d.spec.fc && d.splits > 1)
+        need = std::max(need, static_cast<size_t>(d.splits) * ((static_cast<size_t>(mb_) + 127) / 128) * 128 * d.g.Cout_pad * 4);
     if (need) {
       void* w = nullptr;
       void* c = nullptr;
@@ -626,8 +652,8 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
     switch (o.kind) {
       case OpSpec::STEM: {
         // B2I_STEM=1: the first form of the kernel (pixels on the accumulator lanes, stem.cu); default: stem2.cu
-        static const int stem_form = [] { const char* e = getenv("B2I_STEM"); return e ? atoi(e) : 1; }();
-        if (stem_form == 2) B2I_CUDA(launch_stem2(d_u8, buf(o.out), d.w2, d.bias_host.data(), nb, stem_sched_, f16, st));
+        static const int stem_form = [] { const char* e = getenv("B2I_STEM"); return e ? atoi(e) : 2; }();
+        if (stem_form != 1) B2I_CUDA(launch_stem2(d_u8, buf(o.out), d.w2, d.bias_host.data(), nb, stem_sched_, f16, st));
         else B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, f16, st));
         break;
       }
@@ -679,15 +705,10 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         static const bool snake = [] { const char* e = getenv("B2I_NO_SNAKE"); return !(e && e[0] == '1'); }();
         a.reverse = (snake && (d.patch || d.flat || d.pair) && !o.fc) ? (patch_seq++ & 1) ^ 1 : 0;
         a.f16 = f16;
-        if (o.fc && !d.pair && splitk_ws_ && d.amode == A_TILED) {
-          // enough (tile, split) work items for two per SM, at least four k-blocks each, within the scratch
-          const int tiles_mn = ((nb + 127) / 128) * (d.g.Cout_pad / d.BN);
-          int sp = std::min(16, std::max(1, 296 / std::max(1, tiles_mn)));
-          sp = std::min(sp, std::max(1, (d.g.K / 64) / 4));
-          const size_t per_split = static_cast<size_t>((nb + 127) / 128) * 128 * d.g.Cout_pad * 4;
-          sp = static_cast<int>(std::min<size_t>(sp, splitk_ws_bytes_ / per_split));
-          if (sp > 1 && tiles_mn <= 4096) {
-            a.splits = sp;
+        if (o.fc && !d.pair && d.amode == A_TILED) {
+          a.a_rows = d.a_rows;
+          if (d.splits > 1 && splitk_ws_) {
+            a.splits = d.splits;
             a.ws = splitk_ws_;
             a.ctr = splitk_ctr_;
             a.ldw = d.g.Cout_pad;

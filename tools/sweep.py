@@ -1,8 +1,9 @@
 """Batch-size sweep (BASELINE.json configs[4]) and the dual-job fair share (configs[3]) on the GPUs
 visible to this process.  Writes JSON lines to the file given as argv[1] (default stdout).
 
-  sweep : for each model and batch size 1..1024, blocking b2i_predict_u8 latency (p50 / p99 over the
-          repetitions, host buffers pinned, preprocessing = normalise on the GPU) and images/s
+  sweep : for each model, batch size 1..4096 and GPU count (1 and all visible), blocking b2i_predict_u8 latency
+          (p50 / p99 over the repetitions, host buffers pinned, preprocessing = normalise on the GPU) and images/s;
+          plus, per model, b2i_predict_raw_u8 on 500x375 decoded images (resize + crop + normalise on the GPU)
   dual  : ResNet-18 (bs 256) and AlexNet (bs 256) at the same time on disjoint halves of the GPUs
           (reference src/services.rs:199-211) against each job alone on the same half
 """
@@ -47,20 +48,36 @@ def timed(model, imgs, reps, devices=None):
 
 
 def sweep():
-    ctx = b2.Context((0,))
-    for name in ("resnet18", "alexnet"):
-        ot = synth.ensure_ot(name, os.path.join(ROOT, "tests", "_cache", name + ".ot"))
-        model = b2.Model(ctx, name, ot, max_batch=1024, micro_batch=256)
-        pin, imgs = pinned_images(1024, seed=1)
-        for bs in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024):
-            reps = 50 if bs <= 64 else 20
-            ms = timed(model, imgs[:bs], reps)
-            emit({"kind": "sweep", "model": name, "batch": bs, "gpus": 1, "reps": reps,
-                  "p50_ms": ms[len(ms) // 2], "p99_ms": ms[min(len(ms) - 1, int(0.99 * len(ms)))],
-                  "images_per_s": bs / (sum(ms) / len(ms) / 1000.0), "api": "b2i_predict_u8 (blocking, pinned host buffers)"})
-        model.close()
-        pin.close()
-    ctx.close()
+    for g in sorted({1, n_gpus}):
+        ctx = b2.Context(tuple(range(g)))
+        per_gpu = 4096 // g if g > 1 else 4096
+        for name in ("resnet18", "alexnet"):
+            ot = synth.ensure_ot(name, os.path.join(ROOT, "tests", "_cache", name + ".ot"))
+            model = b2.Model(ctx, name, ot, max_batch=max(per_gpu, 1), micro_batch=256)
+            pin, imgs = pinned_images(4096, seed=1)
+            for bs in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096):
+                reps = 50 if bs <= 64 else (20 if bs <= 1024 else 8)
+                ms = timed(model, imgs[:bs], reps)
+                emit({"kind": "sweep", "model": name, "batch": bs, "gpus": g, "reps": reps,
+                      "p50_ms": ms[len(ms) // 2], "p99_ms": ms[min(len(ms) - 1, int(0.99 * len(ms)))],
+                      "images_per_s": bs / (sum(ms) / len(ms) / 1000.0), "api": "b2i_predict_u8 (blocking, pinned host buffers)"})
+            if g == 1:
+                rng = np.random.default_rng(3)
+                raw = [rng.integers(0, 256, (375, 500, 3), dtype=np.uint8) for _ in range(256)]
+                for bs in (1, 8, 32, 256):
+                    for _ in range(2):
+                        model.predict_raw(raw[:bs], k=5)
+                    ms = []
+                    for _ in range(10):
+                        t0 = time.perf_counter()
+                        model.predict_raw(raw[:bs], k=5)
+                        ms.append((time.perf_counter() - t0) * 1000.0)
+                    ms.sort()
+                    emit({"kind": "sweep_raw", "model": name, "batch": bs, "gpus": 1, "image": "375x500 decoded u8", "p50_ms": ms[len(ms) // 2],
+                          "images_per_s": bs / (sum(ms) / len(ms) / 1000.0), "api": "b2i_predict_raw_u8 (resize + crop + normalise on the GPU)"})
+            model.close()
+            pin.close()
+        ctx.close()
 
 
 def dual():
