@@ -57,6 +57,8 @@ struct KP {
   float* ws;
   int* ctr;
   int a_rows;   // persistent kernel, A_TILED: rows of the A box (the tensor map's), 128 unless the layer has fewer rows
+  int b_blocked;  // persistent kernel: the weights are stored tile by tile, [N tile][k-block][BN rows][64], so that a
+                  // weight tile is one contiguous BN x 128-byte run in memory (tmB is a map over that array)
 };
 
 // Where one tile's results go.
@@ -483,6 +485,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
             tma_load_2d(a_s, &tmA, full_bar(s), kb * BK, m0);
           }
           if (second) tma_load_2d(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
+          else if (p.b_blocked) tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), 0, (nn * p.num_kb + kb) * p.BN);
           else tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
@@ -1381,6 +1384,7 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->rev = a.reverse;
   p->nprod = 1;
   p->a_rows = BM;
+  p->b_blocked = 0;
   p->splits = 1;
   p->ldw = 0;
   p->ws = nullptr;
@@ -1421,6 +1425,7 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
     p.ctr = a.ctr;
     p.ldw = a.ldw;
   }
+  if (a.b_blocked && p.tiles_n2 == 0) p.b_blocked = 1;
   if (AMODE == A_TILED && a.a_rows >= 8 && a.a_rows < BM && (a.a_rows & 7) == 0 && p.tiles_m == 1) p.a_rows = a.a_rows;
   const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2) * p.splits;
   const int grid2 = total2 < sm_count[dev] ? total2 : sm_count[dev];

@@ -434,33 +434,31 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         else if (tiles256 < 148) bn = std::min(bn, 64);
       }
       while (bn > 32 && c.Cout_pad % bn) bn -= 32;
-      // FC layers of the 16-bit path: tile width, split-K factor and A-box rows from a model of what limits them.
-      // Measured (AlexNet classifier, batch 32 and 256): the kernel is bound by the TMA unit, which spends about 62
-      // cycles per request plus 3.5 per 128-byte row it moves, so a k-block costs 124 + 3.5 x (A rows + tile width)
-      // cycles whatever the MMAs need; an FC layer is fast when few rows carry many weight bytes (wide tiles, an A
-      // box no taller than the batch) and every SM has a share (split-K).  The factor is fixed per layer at load
-      // time, so an image's logits do not depend on the size of the batch it arrives in.  B2I_NO_SPLITK=1: off.
+      // FC layers of the 16-bit path stream a weight matrix that is read once per batch.  Two things make that
+      // stream fast: (i) the weights are re-laid at load time tile by tile, [N tile][k-block][tile rows][64], so
+      // that the TMA request of a weight tile reads ONE contiguous 8 KB run instead of 64 lines that lie K * 2 bytes
+      // apart (DRAM pages); (ii) split-K, so that every SM has a share when the layer has fewer tiles than SMs.
+      // The split factor is fixed per layer at load time: an image's logits do not depend on the size of the
+      // batch it arrives in.  B2I_NO_SPLITK=1 turns both off.
       static const bool fc_plan_on = [] { const char* e = getenv("B2I_NO_SPLITK"); return !(e && e[0] == '1'); }();
       bool fc_planned = false;
-      if (o.fc && fc_bn < 32 && cfg_.precision != PREC_FP32 && fc_plan_on) {
-        const int tiles_m = (mb_ + 127) / 128;
-        const int a_rows = tiles_m == 1 ? std::max(8, (mb_ + 7) / 8 * 8) : 128;
-        const int kb = c.K / 64;
-        double best = 1e30;
-        for (int cand : {64, 128, 256}) {
-          if (cand > std::min(cfg_.bn_max, 256) || c.Cout_pad % cand) continue;
-          for (int sp : {1, 2, 3, 4, 6, 8, 12, 16}) {
-            const int kb_per = (kb + sp - 1) / sp;
-            if (sp > 1 && (kb_per < 4 || (sp - 1) * kb_per >= kb)) continue;
-            const double items = static_cast<double>(tiles_m) * (c.Cout_pad / cand) * sp;
-            const double waves = std::ceil(items / 148.0);
-            const double ws_cycles = sp > 1 ? static_cast<double>(sp) * mb_ * c.Cout_pad * 8.0 / (148.0 * 40.0) : 0.0;
-            const double cost = waves * (kb_per * (124.0 + 3.5 * (a_rows + cand)) + 2500.0 + (sp > 1 ? 1500.0 : 0.0)) + ws_cycles;
-            if (cost < best) { best = cost; bn = cand; d.splits = sp; }
-          }
-        }
-        d.a_rows = a_rows;
-        fc_planned = best < 1e30;
+      // B2I_FC_SPLITS / B2I_FC_AROWS (with B2I_FC_BN) force a plan (A/B timing)
+      static const int fc_splits_env = [] { const char* e = getenv("B2I_FC_SPLITS"); return e ? atoi(e) : 0; }();
+      static const int fc_arows_env = [] { const char* e = getenv("B2I_FC_AROWS"); return e ? atoi(e) : 0; }();
+      if (o.fc && cfg_.precision != PREC_FP32 && cfg_.persistent && fc_bn >= 32 && (fc_splits_env > 0 || fc_arows_env > 0)) {
+        if (fc_splits_env > 0) d.splits = std::min(fc_splits_env, std::max(1, (c.K / 64) / 2));
+        if (fc_arows_env >= 8 && (mb_ + 127) / 128 == 1) d.a_rows = std::min(128, std::max((mb_ + 7) / 8 * 8, fc_arows_env / 8 * 8));
+        fc_planned = true;
+      }
+      if (o.fc && fc_bn < 32 && cfg_.precision != PREC_FP32 && fc_plan_on && cfg_.persistent) {
+        // measured (profiles/r03_fc_plan_matrix.txt): 64-wide tiles win at every batch; splitting K pays while the
+        // layer has fewer (tile, split) items than SMs and the partial sums stay small (one M tile)
+        const int tiles_mn = ((mb_ + 127) / 128) * (c.Cout_pad / bn);
+        int sp = std::max(1, std::min(8, 128 / std::max(1, tiles_mn)));
+        sp = std::min(sp, std::max(1, (c.K / 64) / 4));
+        while (sp > 1 && (sp - 1) * ((c.K / 64 + sp - 1) / sp) >= c.K / 64) --sp;
+        d.splits = sp;
+        fc_planned = true;
       }
       d.BN = bn;
       d.stages = conv_umma_pick_stages(bn);
@@ -546,7 +544,21 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         weight_bytes_ += wn * 4;
       } else {
         std::vector<uint16_t> wb(wn);
-        for (size_t i = 0; i < wn; ++i) wb[i] = host_f32_to_16(c.w[i], f16);
+        static const bool blocked_on = [] { const char* e = getenv("B2I_FC_NOBLOCK"); return !(e && e[0] == '1'); }();
+        if (fc_planned && blocked_on && o.fc && !d.pair && d.b_tma) {
+          // [N tile][k-block][BN rows][64]
+          const int nkb = c.K / 64, tn = c.Cout_pad / d.BN;
+          size_t o2 = 0;
+          for (int nt = 0; nt < tn; ++nt)
+            for (int kb = 0; kb < nkb; ++kb)
+              for (int r = 0; r < d.BN; ++r) {
+                const float* src = &c.w[(static_cast<size_t>(nt) * d.BN + r) * c.K + static_cast<size_t>(kb) * 64];
+                for (int e = 0; e < 64; ++e) wb[o2++] = host_f32_to_16(src[e], f16);
+              }
+          d.b_blocked = 1;
+        } else {
+          for (size_t i = 0; i < wn; ++i) wb[i] = host_f32_to_16(c.w[i], f16);
+        }
         B2I_CUDA(cudaMalloc(&d.w, wn * 2));
         B2I_CUDA(cudaMemcpy(d.w, wb.data(), wn * 2, cudaMemcpyHostToDevice));
         weight_bytes_ += wn * 2;
@@ -561,7 +573,12 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       if (cfg_.precision != PREC_FP32) {
         const char* terr = "";
         if (d.b_tma) {
-          if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.pair ? d.BN / 2 : d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
+          if (d.b_blocked) {
+            if (make_tmap_rows(&d.tmB, d.w, c.Cout_pad * (c.K / 64), 64, d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
+          } else if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.pair ? d.BN / 2 : d.BN, &terr)) {
+            *err = c.name + ": " + terr;
+            return false;
+          }
           d.has_tmB = true;
         }
         void* xin = bufs_[tensor_buf_[o.in]];
@@ -707,6 +724,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.f16 = f16;
         if (o.fc && !d.pair && d.amode == A_TILED) {
           a.a_rows = d.a_rows;
+          a.b_blocked = d.b_blocked;
           if (d.splits > 1 && splitk_ws_) {
             a.splits = d.splits;
             a.ws = splitk_ws_;
