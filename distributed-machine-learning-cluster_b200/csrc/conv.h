@@ -64,7 +64,6 @@ struct ConvArgs {
   int splits = 1, ldw = 0;
   float* ws = nullptr;
   int* ctr = nullptr;
-  int b_blocked = 0;              // persistent kernel: weights stored [N tile][k-block][BN][64] (tmB = make_tmap_rows over [tiles * BN][64])
   int a_rows = 128;               // A_TILED, persistent kernel: box rows of tmA (a multiple of 8 below 128 when the layer has one M tile)
 };
 

@@ -57,8 +57,6 @@ struct KP {
   float* ws;
   int* ctr;
   int a_rows;   // persistent kernel, A_TILED: rows of the A box (the tensor map's), 128 unless the layer has fewer rows
-  int b_blocked;  // persistent kernel: the weights are stored tile by tile, [N tile][k-block][BN rows][64], so that a
-                  // weight tile is one contiguous BN x 128-byte run in memory (tmB is a map over that array)
 };
 
 // Where one tile's results go.
@@ -392,8 +390,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 //   warp 0: TMA producer   warp 1: TMEM alloc + MMA issue   warps 2-9: epilogue
 constexpr int PTHREADS = 64 + 256;   // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
 
+// As in the pair kernel below, the k-blocks are dealt round-robin to up to three TMA-issuing warps (warp 0 and the
+// two warps after the epilogue warps): the requests of one warp complete one after the other, those of
+// different warps overlap.  An FC layer on a small batch is a pure weight stream and was bound by exactly that
+// (517 cycles per 8 KB weight tile with one issuing warp, whatever the tile width or the A box).
+constexpr int PERS_MAX_PROD = 3;
+constexpr int PERS_THREADS = PTHREADS + 32 * (PERS_MAX_PROD - 1);
 template <int AMODE, bool F16>
-__global__ void __launch_bounds__(PTHREADS, 1)
+__global__ void __launch_bounds__(PERS_THREADS, 1)
 conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                             const __grid_constant__ CUtensorMap tmB,
                             const __grid_constant__ CUtensorMap tmB2, const KP p) {
@@ -440,13 +444,14 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   const uint32_t tmem_base = tmem_slot;
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
-  if (warp == 0) {
-    if (lane == 0) {
+  const int prod_id = warp == 0 ? 0 : (warp >= PTHREADS / 32 ? warp - PTHREADS / 32 + 1 : -1);
+  if (prod_id >= 0) {
+    if (lane == 0 && prod_id < p.nprod) {
+      int turn = 0;   // whose k-block the next one is
       const int cpb = (AMODE == A_IM2COL) ? (p.C >> 6) : 1;
       const int ohw = p.OH * p.OW;
-      // A_TILED with fewer than 128 rows in the layer: the map's box holds only those rows (the TMA unit spends about
-      // 3.5 cycles per 128-byte row it moves, zero-filled or not, and that, not HBM, is what limits an FC layer
-      // on a small batch); the MMA still reads 128 rows, the rest are whatever the ring held and are never stored
+      // A_TILED with fewer than 128 rows in the layer: the map's box may hold only those rows; the MMA still reads 128
+      // rows, the rest are whatever the ring held and are never stored
       const uint32_t tx = b_tile_bytes + (AMODE == A_TILED ? static_cast<uint32_t>(p.a_rows) * 128u : static_cast<uint32_t>(A_TILE_BYTES));
       int s = 0, ph = 0;
       for (int w = blockIdx.x; w < total_tiles; w += gridDim.x) {
@@ -471,22 +476,25 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
         int cblk = kb_begin - tap0 * cpb, r = tap0 / p.S, sx = tap0 - (tap0 / p.S) * p.S;
         for (int j = 0; j < kb_count; ++j) {
           const int kb = kb_begin + j;
-          mbar_wait(empty_bar(s), ph ^ 1);
-          const uint32_t a_s = smem_base + s * stage_bytes;
-          mbar_expect_tx(full_bar(s), tx);
-          if (AMODE == A_IM2COL) {
-            tma_load_im2col_4d(a_s, &tmA, full_bar(s), cblk << 6, iw_base, ih_base, n_base,
-                               static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
-            if (++cblk == cpb) {
-              cblk = 0;
-              if (++sx == p.S) { sx = 0; ++r; }
+          const bool mine = turn == prod_id;
+          if (++turn == p.nprod) turn = 0;
+          if (mine) {
+            mbar_wait(empty_bar(s), ph ^ 1);
+            const uint32_t a_s = smem_base + s * stage_bytes;
+            mbar_expect_tx(full_bar(s), tx);
+            if (AMODE == A_IM2COL) {
+              tma_load_im2col_4d(a_s, &tmA, full_bar(s), cblk << 6, iw_base, ih_base, n_base,
+                                 static_cast<uint16_t>(sx), static_cast<uint16_t>(r));
+            } else {
+              tma_load_2d(a_s, &tmA, full_bar(s), kb * BK, m0);
             }
-          } else {
-            tma_load_2d(a_s, &tmA, full_bar(s), kb * BK, m0);
+            if (second) tma_load_2d(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
+            else tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
           }
-          if (second) tma_load_2d(a_s + A_TILE_BYTES, &tmB2, full_bar(s), j * BK, n0);
-          else if (p.b_blocked) tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), 0, (nn * p.num_kb + kb) * p.BN);
-          else tma_load_2d(a_s + A_TILE_BYTES, &tmB, full_bar(s), kb * BK, n0);
+          if (AMODE == A_IM2COL && ++cblk == cpb) {
+            cblk = 0;
+            if (++sx == p.S) { sx = 0; ++r; }
+          }
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -1384,7 +1392,6 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->rev = a.reverse;
   p->nprod = 1;
   p->a_rows = BM;
-  p->b_blocked = 0;
   p->splits = 1;
   p->ldw = 0;
   p->ws = nullptr;
@@ -1425,12 +1432,14 @@ cudaError_t launch_persistent(const ConvArgs& a, const CUtensorMap* tmA, const C
     p.ctr = a.ctr;
     p.ldw = a.ldw;
   }
-  if (a.b_blocked && p.tiles_n2 == 0) p.b_blocked = 1;
   if (AMODE == A_TILED && a.a_rows >= 8 && a.a_rows < BM && (a.a_rows & 7) == 0 && p.tiles_m == 1) p.a_rows = a.a_rows;
   const int total2 = p.tiles_m * (p.tiles_n + p.tiles_n2) * p.splits;
   const int grid2 = total2 < sm_count[dev] ? total2 : sm_count[dev];
   (void)grid;
-  return launch_pdl(kern, dim3(static_cast<unsigned>(grid2)), dim3(PTHREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
+  static const int nprod_env = [] { const char* e = getenv("B2I_NPROD"); return e ? atoi(e) : 0; }();
+  p.nprod = nprod_env >= 1 && nprod_env <= PERS_MAX_PROD ? nprod_env : PERS_MAX_PROD;
+  p.nprod = std::min(p.nprod, p.stages);
+  return launch_pdl(kern, dim3(static_cast<unsigned>(grid2)), dim3(PERS_THREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 
 template <int AMODE, bool F16>

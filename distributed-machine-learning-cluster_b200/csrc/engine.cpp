@@ -434,12 +434,11 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         else if (tiles256 < 148) bn = std::min(bn, 64);
       }
       while (bn > 32 && c.Cout_pad % bn) bn -= 32;
-      // FC layers of the 16-bit path stream a weight matrix that is read once per batch.  Two things make that
-      // stream fast: (i) the weights are re-laid at load time tile by tile, [N tile][k-block][tile rows][64], so
-      // that the TMA request of a weight tile reads ONE contiguous 8 KB run instead of 64 lines that lie K * 2 bytes
-      // apart (DRAM pages); (ii) split-K, so that every SM has a share when the layer has fewer tiles than SMs.
-      // The split factor is fixed per layer at load time: an image's logits do not depend on the size of the
-      // batch it arrives in.  B2I_NO_SPLITK=1 turns both off.
+      // FC layers of the 16-bit path stream a weight matrix that is read once per batch.  Split-K gives every SM a
+      // share when the layer has fewer tiles than SMs (64-wide tiles stay the best width at every batch; an A box
+      // shorter than 128 rows and weights re-laid as contiguous tiles were tried and change nothing:
+      // profiles/r03_fc_plan_matrix.txt).  The factor is fixed per layer at load time: an image's logits do not
+      // depend on the size of the batch it arrives in.  B2I_NO_SPLITK=1 turns it off.
       static const bool fc_plan_on = [] { const char* e = getenv("B2I_NO_SPLITK"); return !(e && e[0] == '1'); }();
       bool fc_planned = false;
       // B2I_FC_SPLITS / B2I_FC_AROWS (with B2I_FC_BN) force a plan (A/B timing)
@@ -455,7 +454,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         // layer has fewer (tile, split) items than SMs and the partial sums stay small (one M tile)
         const int tiles_mn = ((mb_ + 127) / 128) * (c.Cout_pad / bn);
         int sp = std::max(1, std::min(8, 128 / std::max(1, tiles_mn)));
-        sp = std::min(sp, std::max(1, (c.K / 64) / 4));
+        sp = std::min(sp, std::max(1, (c.K / 64) / 16));   // at least 16 k-blocks per split (ResNet's 8-k-block FC is not split)
         while (sp > 1 && (sp - 1) * ((c.K / 64 + sp - 1) / sp) >= c.K / 64) --sp;
         d.splits = sp;
         fc_planned = true;
@@ -544,21 +543,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         weight_bytes_ += wn * 4;
       } else {
         std::vector<uint16_t> wb(wn);
-        static const bool blocked_on = [] { const char* e = getenv("B2I_FC_NOBLOCK"); return !(e && e[0] == '1'); }();
-        if (fc_planned && blocked_on && o.fc && !d.pair && d.b_tma) {
-          // [N tile][k-block][BN rows][64]
-          const int nkb = c.K / 64, tn = c.Cout_pad / d.BN;
-          size_t o2 = 0;
-          for (int nt = 0; nt < tn; ++nt)
-            for (int kb = 0; kb < nkb; ++kb)
-              for (int r = 0; r < d.BN; ++r) {
-                const float* src = &c.w[(static_cast<size_t>(nt) * d.BN + r) * c.K + static_cast<size_t>(kb) * 64];
-                for (int e = 0; e < 64; ++e) wb[o2++] = host_f32_to_16(src[e], f16);
-              }
-          d.b_blocked = 1;
-        } else {
-          for (size_t i = 0; i < wn; ++i) wb[i] = host_f32_to_16(c.w[i], f16);
-        }
+        for (size_t i = 0; i < wn; ++i) wb[i] = host_f32_to_16(c.w[i], f16);
         B2I_CUDA(cudaMalloc(&d.w, wn * 2));
         B2I_CUDA(cudaMemcpy(d.w, wb.data(), wn * 2, cudaMemcpyHostToDevice));
         weight_bytes_ += wn * 2;
@@ -573,12 +558,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
       if (cfg_.precision != PREC_FP32) {
         const char* terr = "";
         if (d.b_tma) {
-          if (d.b_blocked) {
-            if (make_tmap_rows(&d.tmB, d.w, c.Cout_pad * (c.K / 64), 64, d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
-          } else if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.pair ? d.BN / 2 : d.BN, &terr)) {
-            *err = c.name + ": " + terr;
-            return false;
-          }
+          if (make_tmap_weights(&d.tmB, d.w, c.Cout_pad, c.K, d.pair ? d.BN / 2 : d.BN, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmB = true;
         }
         void* xin = bufs_[tensor_buf_[o.in]];
@@ -724,7 +704,6 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
         a.f16 = f16;
         if (o.fc && !d.pair && d.amode == A_TILED) {
           a.a_rows = d.a_rows;
-          a.b_blocked = d.b_blocked;
           if (d.splits > 1 && splitk_ws_) {
             a.splits = d.splits;
             a.ws = splitk_ws_;

@@ -125,7 +125,6 @@ class DeviceModel {
     CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};
     bool has_tmA = false, has_tmB = false;
     int amode = 0, BN = 0, stages = 0, b_tma = 0, patch = 0, pair = 0, resident_b = 0, flat = 0, msub = 1;
-    int b_blocked = 0;              // FC layers: weights re-laid tile by tile (contiguous weight tiles)
     int splits = 1, a_rows = 128;   // FC layers: split-K factor and rows of the A box (see conv_umma.cu, persistent kernel)
     int fused_second = -1;   // index of a 1x1 conv computed inside this op's kernel
     bool skip = false;       // computed by another op's kernel
