@@ -70,7 +70,7 @@ Api* api() {
 }
 
 // nvJPEG sizes its work buffers per batch and, left to itself, gets them from cudaMalloc / cudaFree -- both
-// synchronise the device, once or more per call.  These two allocators keep every block they were ever
+// synchronise the device and serialise against every other allocation in the process.  These two allocators keep every block they were ever
 // asked for on a free list (per process, never shrinking: a decoder's working set is a few hundred MB
 // at most) and hand back the smallest block that fits.
 struct BlockPool {
@@ -99,6 +99,11 @@ struct BlockPool {
   }
   int put(void* p) {
     if (!p) return 0;
+    // cudaFree / cudaFreeHost wait for the device, and nvJPEG relies on that: it frees a staging buffer that an
+    // asynchronous copy may still be reading.  A block goes back on the list only once the GPU is idle, or another
+    // decoder thread could be handed it and write into it under that copy.  (Frees stop once the buffers have
+    // grown to the working set, so this costs nothing in steady state.)
+    cudaDeviceSynchronize();
     std::lock_guard<std::mutex> lock(mu);
     auto it = live.find(p);
     if (it == live.end()) return 0;

@@ -105,6 +105,55 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int N, int iters, int same
   }
 }
 
+// A operand in TENSOR MEMORY (tcgen05.mma [d], [a], bdesc): cycles per MMA by N and by the number of independent
+// accumulate chains (different D columns) the issuing thread rotates through, and with two issuing warps.
+__global__ void __launch_bounds__(128, 1) ts_kernel(int N, int chains, int issuers, int iters, long long* cycles) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar[2];
+  __shared__ uint32_t slot;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) { mbar_init(smem_u32(&bar[0]), 1); mbar_init(smem_u32(&bar[1]), 1); mbar_fence_init(); }
+  for (uint32_t i = threadIdx.x; i < 200 * 1024 / 16; i += blockDim.x)
+    asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(base + i * 16), "r"(0u));
+  fence_proxy_async_smem();
+  if (warp == 0) tmem_alloc(smem_u32(&slot), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = slot;
+  {  // zero the A region (columns 384..447) through tcgen05.st
+    const uint32_t row = tm + (static_cast<uint32_t>(warp * 32) << 16) + 384;
+    for (int c = 0; c < 64; c += 8)
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(row + c), "r"(0u) : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if ((warp == 1 || (warp == 2 && issuers == 2)) && lane == 0) {
+    const int me = warp - 1;
+    const uint32_t idesc = umma_idesc_bf16(128, N);
+    long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+      const uint64_t bd = umma_smem_desc_sw128(base + (it & 3) * 32768);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t d = tm + static_cast<uint32_t>(((me * chains + (it * 4 + k) % chains) * N) % 384);
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+                     "r"(tm + 384 + 8 * k), "l"(bd + 2u * k), "r"(idesc), "r"(1u) : "memory");
+      }
+    }
+    umma_commit(smem_u32(&bar[me]));
+    mbar_wait(smem_u32(&bar[me]), 0);
+    long long t1 = clock64();
+    if (blockIdx.x == 0 && me == 0) cycles[0] = t1 - t0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tm, 512);
+}
+
 int main() {
   long long* d_cyc;
   cudaMalloc(&d_cyc, 8);
@@ -139,6 +188,19 @@ int main() {
             printf("cta_group %d N %3d %s: %7.1f cycles/MMA (ideal %3d) kernel %.3f ms -> %.0f TFLOP/s chip  [%s]\n", cg, N,
                    same ? "one stage   " : "four stages ", per_mma, N / 2, ms, flops / (ms * 1e-3) / 1e12, cudaGetErrorString(err));
           }
+        }
+      }
+  cudaFuncSetAttribute(ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  for (int N : {32, 64, 128, 256})
+    for (int issuers : {1, 2})
+      for (int chains : {1, 2, 4}) {
+        if (N * chains * issuers > 384) continue;
+        for (int rep = 0; rep < 2; ++rep) {
+          ts_kernel<<<148, 128, smem>>>(N, chains, issuers, iters, d_cyc);
+          cudaError_t err = cudaDeviceSynchronize();
+          long long cyc = 0; cudaMemcpy(&cyc, d_cyc, 8, cudaMemcpyDeviceToHost);
+          if (rep == 1) printf("A in TMEM, N %3d, %d issuing warp(s), %d chain(s) each: %6.1f cycles per MMA per SM (floor %3d) [%s]\n", N, issuers, chains,
+                               (double)cyc / (iters * 4.0 * issuers), N / 2, cudaGetErrorString(err));
         }
       }
   cudaFuncSetAttribute(adesc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
