@@ -139,6 +139,7 @@ struct Engine {
   nvjpegHandle_t handle = nullptr;
   nvjpegJpegState_t state = nullptr;
   int batch = -1;   // batch size of the last nvjpegDecodeBatchedInitialize
+  cudaEvent_t drained = nullptr;   // recorded after each per-image decode: the state's staging buffers are free again
 };
 
 bool engine_open(Api* a, nvjpegBackend_t backend, Engine* e) {
@@ -161,6 +162,7 @@ bool engine_open(Api* a, nvjpegBackend_t backend, Engine* e) {
 }
 
 void engine_close(Api* a, Engine* e) {
+  if (e->drained) cudaEventDestroy(e->drained);
   if (e->state) a->nvjpegJpegStateDestroy(e->state);
   if (e->handle) a->nvjpegDestroy(e->handle);
   *e = Engine();
@@ -296,10 +298,16 @@ bool jpeg_decode_batch(JpegDecoder* d, const uint8_t* const* data, const size_t*
     for (size_t j = first; j < to_cpu.size(); j += step) {
       const int i = to_cpu[j];
       nvjpegImage_t im = image_of(i);
+      // nvjpegDecode returns once the GPU part is enqueued; the state's pinned staging buffer is still being copied
+      // from.  Wait for the previous image of THIS state to have left it before entropy-decoding the next one into
+      // it (the GPU part of an image is tens of microseconds against a millisecond of host work: rarely a wait).
+      if (!e.drained) cudaEventCreateWithFlags(&e.drained, cudaEventDisableTiming);
+      else cudaEventSynchronize(e.drained);
       if (a->nvjpegDecode(e.handle, e.state, data[i], len[i], NVJPEG_OUTPUT_RGBI, &im, st) != NVJPEG_STATUS_SUCCESS) {
         cudaGetLastError();
         status[i] = B2I_EDECODE;
       }
+      cudaEventRecord(e.drained, st);
     }
   };
   const size_t helpers = to_cpu.size() >= 8 ? std::min(d->pool.size(), to_cpu.size() / 4) : 0;
