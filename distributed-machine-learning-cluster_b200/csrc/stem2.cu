@@ -22,13 +22,13 @@
 //     3-tap max, and the vertical max of the two same-parity rows, are register operations on raw accumulators
 //     (+bias, ReLU and the rounding are monotone, so they commute with max and are applied once per POOLED value).
 //     Only the pooled values cross threads: 2 x 6 KB per tile through shared memory instead of 32 KB + 56 KB.
-// One CTA per SM (all 512 TMEM columns: two accumulator sets of 128 + 144 of weights), 28 warps; tiles alternate
+// One CTA per SM (all 512 TMEM columns: two accumulator sets of 128 + 144 of weights), 26 warps; tiles alternate
 // between two loader groups and two epilogue groups (even / odd tile of the CTA's sequence = patch buffer =
 // accumulator set), because both are latency chains (global loads; TMEM loads feeding dependent max chains)
 // that take longer than the MMAs of a tile:
 //   warps 0-15  two epilogue groups of eight warps: two sets (pooled rows 0-3 / 4-6) x four TMEM lane quarters
-//   warps 16-19 MMA issue: (column half) x (accumulator set)
-//   warps 20-27 two loader groups of four warps
+//   warps 16-17 MMA issue, one per half of the tile's columns
+//   warps 18-25 two loader groups of four warps
 #include "conv.h"
 #include "ops.h"
 #include "ptx.cuh"
@@ -38,7 +38,7 @@ namespace {
 
 constexpr int S2_DRAIN = 512;
 constexpr int S2_GROUP = 128;                          // threads of one loader group
-constexpr int S2_MMA_WARPS = 4;                         // (column half) x (accumulator set): see the kernel
+constexpr int S2_MMA_WARPS = 2;                         // one per half of the tile's columns: see the kernel
 constexpr int S2_THREADS = S2_DRAIN + 32 * S2_MMA_WARPS + 2 * S2_GROUP;
 constexpr int PATCH_H = 37, PATCH_W = 40;              // pixels of 8 bytes (r, g, b, 0 in the 16-bit storage format)
 constexpr uint32_t PATCH_ROW_BYTES = PATCH_W * 8;      // 320
@@ -124,8 +124,8 @@ stem2_kernel(const Stem2Params p) {
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
       mbar_init(patch_full(b), S2_GROUP);
-      mbar_init(patch_empty(b), 2);   // one commit per MMA-issuing warp of the set (the two column halves)
-      mbar_init(acc_full(b), 2);
+      mbar_init(patch_empty(b), S2_MMA_WARPS);   // one commit per MMA-issuing warp
+      mbar_init(acc_full(b), S2_MMA_WARPS);
       mbar_init(acc_empty(b), 8);
     }
     mbar_fence_init();
@@ -156,32 +156,41 @@ stem2_kernel(const Stem2Params p) {
 
   if (warp >= MMA_WARP && warp < MMA_WARP + S2_MMA_WARPS) {
     // ------------------------------------------------------------------ MMA issue
-    // Four issuing warps: (column half hx of the tile) x (accumulator set b = even / odd tile of the CTA's sequence).
-    // A tcgen05.mma whose A operand is in tensor memory completes 161 cycles after the same warp's previous one,
-    // whatever its N and however many accumulators the warp rotates through, while MMAs of different warps overlap
-    // (tools/microbench/umma_rate.cu, "A in TMEM" rows: 160.9 cycles per MMA with one issuing warp, 80.5 with two).
-    // A warp's 18 MMAs of a tile therefore take ~2900 cycles against 576 of tensor-pipe time, and the way to fill the
-    // pipe is more issuing warps on independent accumulators: both halves of two tiles at once.  tcgen05.commit
-    // tracks the MMAs of the committing thread, so both warps of a set commit and the barriers count two arrivals.
-    const int hx = (warp - MMA_WARP) & 1;
-    const int b = (warp - MMA_WARP) >> 1;
+    // Two issuing warps, one per half of the tile's conv columns (its own 64 accumulator columns, the same
+    // weights).  A tcgen05.mma whose A operand is in tensor memory completes about 160 cycles after the same warp's
+    // previous one, whatever its N and however many accumulators the warp rotates through, while MMAs of different
+    // warps overlap (tools/microbench/umma_rate.cu, "A in TMEM" rows: 160.9 cycles per MMA with one issuing warp,
+    // 80.5 with two; the shared-memory form has no such limit).  The 18 MMAs of a half therefore take ~2900 cycles
+    // against 576 of tensor-pipe time, and two warps halve the tile time of one.  Four warps (both accumulator
+    // sets filled at once) were measured slower, 0.146-0.150 ms against 0.138: a set is then held by its MMAs and
+    // by its epilogue's tensor-memory reads in turn, with nothing to overlap them.  tcgen05.commit tracks the MMAs
+    // of the committing thread, so both warps commit and the barriers count two arrivals.
+    const int hx = warp - MMA_WARP;
     const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
-    const uint32_t pbase = patch0 + b * PATCH_BYTES;
-    const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + hx * 64);
-    for (int k = 0;; ++k) {
-      const int i = 2 * k + b;
-      const uint32_t ph = static_cast<uint32_t>(k & 1);
+    bool done[2] = {false, false};
+    for (int i = 0;; ++i) {
+      const int b = i & 1;
+      if (done[b]) {
+        if (done[b ^ 1]) break;
+        continue;
+      }
+      const uint32_t ph = static_cast<uint32_t>((i >> 1) & 1);
       mbar_wait(acc_empty(b), ph ^ 1);
       mbar_wait(patch_full(b), ph);
       if (*reinterpret_cast<volatile int*>(&tile_ring[i & 7]) < 0) {   // this group is out of tiles: tell the epilogue
         umma_commit_elect(acc_full(b));
-        break;
+        done[b] = true;
+        continue;
       }
       tc_fence_after();
+      const uint32_t pbase = patch0 + b * PATCH_BYTES;
+      {                                         // conv columns 8 * hx .. 8 * hx + 7 of the tile
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + hx * 64);
 #pragma unroll
-      for (int t = 0; t < KCHUNKS; ++t) {      // input row rho = t / 2 under the pair's even conv row, taps 4 * (t & 1) .. + 3
-        const uint32_t b_addr = pbase + static_cast<uint32_t>((t >> 1) * PATCH_ROW_BYTES + hx * 128 + (t & 1) * 32);
-        umma_ts_elect(d_tmem, tmem_base + A_COL + static_cast<uint32_t>(t * 8), patch_desc_pairs(b_addr), idesc, t != 0 ? 1u : 0u);
+        for (int t = 0; t < KCHUNKS; ++t) {      // input row rho = t / 2 under the pair's even conv row, taps 4 * (t & 1) .. + 3
+          const uint32_t b_addr = pbase + static_cast<uint32_t>((t >> 1) * PATCH_ROW_BYTES + hx * 128 + (t & 1) * 32);
+          umma_ts_elect(d_tmem, tmem_base + A_COL + static_cast<uint32_t>(t * 8), patch_desc_pairs(b_addr), idesc, t != 0 ? 1u : 0u);
+        }
       }
       umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
       umma_commit_elect(acc_full(b));
