@@ -53,10 +53,6 @@ void enqueue_shard(DevSlot& s, int lane_id, const uint8_t* images, int n, int k,
   if (cu(cudaSetDevice(s.dm->device()), "cudaSetDevice")) return;
   const int classes = s.dm->classes();
   const size_t cap = static_cast<size_t>(s.dm->max_batch());
-  if (logits && !L.d_logits) {
-    if (cu(cudaMalloc(reinterpret_cast<void**>(&L.d_logits), cap * classes * 4), "cudaMalloc(logits)")) return;
-    if (cu(cudaMallocHost(reinterpret_cast<void**>(&L.h_logits), cap * classes * 4), "cudaMallocHost(logits)")) return;
-  }
   const uint8_t* src = images;
   if (!is_pinned(images)) {
     // pageable source: stage through pinned memory so the copy is a real asynchronous DMA
@@ -153,6 +149,10 @@ bool slot_setup(DevSlot* s, int max_batch, std::string* err) {
     chk(cudaMalloc(reinterpret_cast<void**>(&L.d_prob), nk * 4));
     chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_idx), nk * 4));
     chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_prob), nk * 4));
+    // logits staging up front as well (4 KB per image and lane): the first call that asks for logits must not
+    // be the one that allocates
+    chk(cudaMalloc(reinterpret_cast<void**>(&L.d_logits), static_cast<size_t>(max_batch) * B2I_CLASSES * 4));
+    chk(cudaMallocHost(reinterpret_cast<void**>(&L.h_logits), static_cast<size_t>(max_batch) * B2I_CLASSES * 4));
     chk(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
     L.copied.assign(chunks, nullptr);
     for (auto& ev : L.copied) chk(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));

@@ -32,10 +32,10 @@ struct Lane {
   uint8_t* h_stage = nullptr;    // pinned, max_batch images; allocated the first time a pageable source shows up
   int32_t* d_idx = nullptr;
   float* d_prob = nullptr;
-  float* d_logits = nullptr;     // device, allocated on first use
+  float* d_logits = nullptr;     // device
   int32_t* h_idx = nullptr;      // pinned
   float* h_prob = nullptr;
-  float* h_logits = nullptr;     // pinned, allocated on first use
+  float* h_logits = nullptr;     // pinned
   std::vector<cudaEvent_t> copied;  // one per micro-batch chunk
   cudaEvent_t done = nullptr;
   // the request currently using this lane

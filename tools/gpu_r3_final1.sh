@@ -1,0 +1,34 @@
+#!/bin/bash
+# Round-3 final one-GPU pass: suite, no-alloc test alone, smoke, bench lines, parity over the 1000 reference images,
+# ncu launch list + full tables (ResNet-18 and AlexNet), batch sweep on one GPU.
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+timeout 1800 python -m pytest tests/ -x -q -m gpu -p no:cacheprovider > gpurun_out/gpu_suite.log 2>&1
+echo "=== full -m gpu suite exit $?"; grep -E "passed|failed|error" gpurun_out/gpu_suite.log | tail -n 3 | cut -c1-300
+grep -E "^E  |^FAILED" gpurun_out/gpu_suite.log | head -20 | cut -c1-400
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -q -m gpu -p no:cacheprovider > gpurun_out/zz_alone.log 2>&1; echo "=== zz alone exit $?"; tail -n 2 gpurun_out/zz_alone.log | cut -c1-200
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "=== smoke exit $?"; tail -n 1 gpurun_out/smoke.log
+timeout 900 python bench.py --steps 20 --warmup 5 --profile-out gpurun_out/launch_share.csv > gpurun_out/bench.json 2> gpurun_out/bench.err
+echo "=== bench exit $?"; tail -3 gpurun_out/bench.err; python - <<'P'
+import json
+d=json.load(open('gpurun_out/bench.json'))
+print('value',round(d['value']),'e2e',round(d['e2e']['value']),'ms',round(d['ms_per_step'],4),'sustained',d['sustained'],'\nroofline',{k:d['roofline'][k] for k in ('achieved','frac','frac_burst','frac_sustained','traffic','whole_step','whole_step_sustained_segment')},'\nfp16',d['fp16'],'parity',d['parity'], '\n', d['launch_ms'])
+P
+timeout 600 python bench.py --precision fp16 --steps 20 --warmup 5 --cpu-budget 1 > gpurun_out/bench_fp16.json 2> gpurun_out/bench_fp16.err; echo "=== fp16 bench exit $?"
+timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "=== reference arm exit $?"; cut -c1-200 gpurun_out/bench_reference.json
+for b in 32 256; do timeout 600 python bench.py --model alexnet --batch $b --steps 20 --warmup 5 --cpu-budget 5 > gpurun_out/bench_alexnet_bs$b.json 2> gpurun_out/bench_alexnet_bs$b.err; echo "=== alexnet bs$b exit $?"; python -c "
+import json; d=json.load(open('gpurun_out/bench_alexnet_bs$b.json')); print(round(d['value']), round(d['e2e']['value']), d['ms_per_step'], d['roofline']['achieved'], d['sustained'], d['launch_ms'])"; done
+timeout 1500 python tools/parity_1000.py --out gpurun_out/parity_1000.json > gpurun_out/parity_1000.log 2>&1
+echo "=== parity_1000 exit $?"; tail -20 gpurun_out/parity_1000.log | cut -c1-300
+timeout 900 python tools/sweep.py gpurun_out/sweep_1gpu.jsonl sweep > gpurun_out/sweep.log 2>&1; echo "=== sweep exit $?"; tail -2 gpurun_out/sweep.log; wc -l gpurun_out/sweep_1gpu.jsonl
+python tools/profile_step.py 2 1 > gpurun_out/plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -s 40 -c 20 --csv --log-file gpurun_out/ncu_launches.csv python tools/profile_step.py 2 1 > gpurun_out/ncu_l.log 2>&1
+echo "=== ncu launch list exit $?"
+python tools/profile_step.py 2 1 > gpurun_out/plain.log 2>&1 && \
+ncu --set full --clock-control none -s 40 -c 20 -f -o gpurun_out/prof_step python tools/profile_step.py 2 1 > gpurun_out/ncu_f.log 2>&1
+echo "=== ncu full exit $?"
+ncu -i gpurun_out/prof_step.ncu-rep --page raw --csv > gpurun_out/ncu_step_raw.csv 2>/dev/null; rm -f gpurun_out/prof_step.ncu-rep
+python tools/profile_step.py 2 1 0 alexnet > gpurun_out/plain_a.log 2>&1 && \
+ncu --set full --clock-control none -s 22 -c 11 -f -o gpurun_out/prof_alex python tools/profile_step.py 2 1 0 alexnet > gpurun_out/ncu_a.log 2>&1
+echo "=== ncu alexnet exit $?"; tail -1 gpurun_out/plain_a.log
+ncu -i gpurun_out/prof_alex.ncu-rep --page raw --csv > gpurun_out/ncu_alex_raw.csv 2>/dev/null; rm -f gpurun_out/prof_alex.ncu-rep; ls -la gpurun_out/*.csv

@@ -48,7 +48,7 @@ def timed(model, imgs, reps, devices=None):
 
 
 def sweep():
-    for g in sorted({1, n_gpus}):
+    for g in ([n_gpus] if os.environ.get("SWEEP_ONLY_ALL_GPUS") == "1" else sorted({1, n_gpus})):
         ctx = b2.Context(tuple(range(g)))
         per_gpu = 4096 // g if g > 1 else 4096
         for name in ("resnet18", "alexnet"):
