@@ -513,7 +513,11 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           // requests of different issuing warps overlap (tools/microbench/tma_rate.cu, two-issuer rows): with the pair
           // kernel's three producer warps one completes every req / 3 cycles
           const long long req = (ms <= 2 ? 700 : (ms == 3 ? 730 : 764)) / 3;
-          const long long kb_cycles = std::max<long long>(req, static_cast<long long>(ms) * 4 * (bn / 2));
+          // what a k-block costs: the request turn-around, its MMAs, or the time the SM needs to take in its
+          // operands (this CTA's A rows and its half of the weight tile at ~40 B/clk: the im2col layers of layer3 /
+          // layer4 run at that fill rate, profiles/r03_ncu_step_full.csv)
+          const long long fill = (static_cast<long long>(ms) * 16384 + (d.resident_b ? 0 : bn / 2 * 128)) / 40;
+          const long long kb_cycles = std::max<long long>(std::max<long long>(req, fill), static_cast<long long>(ms) * 4 * (bn / 2));
           const long long epi = (2 * ms * bn > 512) ? 10000 : 0;
           const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
           return waves * (kb_avg * kb_cycles + epi + 600);   // + per-tile set-up (barrier turn-around, bias / residual fetch)

@@ -29,6 +29,6 @@ ncu --set full --clock-control none -s 40 -c 20 -f -o gpurun_out/prof_step pytho
 echo "=== ncu full exit $?"
 ncu -i gpurun_out/prof_step.ncu-rep --page raw --csv > gpurun_out/ncu_step_raw.csv 2>/dev/null; rm -f gpurun_out/prof_step.ncu-rep
 python tools/profile_step.py 2 1 0 alexnet > gpurun_out/plain_a.log 2>&1 && \
-ncu --set full --clock-control none -s 22 -c 11 -f -o gpurun_out/prof_alex python tools/profile_step.py 2 1 0 alexnet > gpurun_out/ncu_a.log 2>&1
+ncu --set full --clock-control none -s 26 -c 13 -f -o gpurun_out/prof_alex python tools/profile_step.py 2 1 0 alexnet > gpurun_out/ncu_a.log 2>&1
 echo "=== ncu alexnet exit $?"; tail -1 gpurun_out/plain_a.log
 ncu -i gpurun_out/prof_alex.ncu-rep --page raw --csv > gpurun_out/ncu_alex_raw.csv 2>/dev/null; rm -f gpurun_out/prof_alex.ncu-rep; ls -la gpurun_out/*.csv

@@ -163,7 +163,7 @@ def main():
                 lab = [(w, dict(labels).get(w, "?")) for w in sub]
                 leader = b2.Leader(member, lab)
                 leader.resnet18.assigned_member_ids = [0]
-                leader.run_job(leader.resnet18, batch=256, limit=min(256, len(sub)))      # warm-up: decoder set-up, scratch growth
+                leader.run_job(leader.resnet18, batch=256)      # warm-up over the whole set: both staging lanes, decoder set-up, scratch growth
                 leader.resnet18 = b2.Job("resnet18")
                 leader.resnet18.assigned_member_ids = [0]
                 t0 = time.perf_counter()
