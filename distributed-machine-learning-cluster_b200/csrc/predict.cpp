@@ -428,25 +428,36 @@ void raw_stage(DevSlot& s, int device, int max_batch, const uint8_t* const* imag
     return;
   }
   sh->jobs.assign(n, ResizeJob());
-  for (int i = 0; i < n; ++i) {
-    if (!usable(i)) continue;
-    if (!jpeg) std::memcpy(R.h_img + img_off[i], images[i], static_cast<size_t>(hs[i]) * ws[i] * 3);
-    uint8_t* ht = R.h_tab + tab_off[i];
-    uint8_t* dt = R.d_tab + tab_off[i];
-    size_t o = 0;
-    auto put = [&](const void* src, size_t bytes) { std::memcpy(ht + o, src, bytes); const size_t at = o; o += bytes; return at; };
-    ResizeJob& j = sh->jobs[i];
-    j.d_img = (jpeg ? R.d_jimg : R.d_img) + img_off[i]; j.h = hs[i]; j.w = ws[i];
-    j.xf = reinterpret_cast<const int*>(dt + put(px[i].first.data(), 224 * 4));
-    j.xc = reinterpret_cast<const int*>(dt + put(px[i].count.data(), 224 * 4));
-    j.yf = reinterpret_cast<const int*>(dt + put(py[i].first.data(), 224 * 4));
-    j.yc = reinterpret_cast<const int*>(dt + put(py[i].count.data(), 224 * 4));
-    j.xi = reinterpret_cast<const int*>(dt + put(px[i].idx.data(), px[i].idx.size() * 4));
-    j.yi = reinterpret_cast<const int*>(dt + put(py[i].idx.data(), py[i].idx.size() * 4));
-    j.xw = reinterpret_cast<const float*>(dt + put(px[i].coef.data(), px[i].coef.size() * 4));
-    j.yw = reinterpret_cast<const float*>(dt + put(py[i].coef.data(), py[i].coef.size() * 4));
-    j.d_tmp = R.d_tmp;
-    j.d_out = L.d_in + static_cast<size_t>(i) * B2I_IMAGE_BYTES;
+  {
+    // per image: the pixels into pinned staging (decoded-pixel path: 0.5 MB per ImageNet-sized image, so a few
+    // threads for a large batch) and the resampling tables behind one another in the table buffer
+    const int nt = n >= 32 ? std::min<int>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    auto fill_range = [&](int t) {
+      for (int i = t; i < n; i += nt) {
+        if (!usable(i)) continue;
+        if (!jpeg) std::memcpy(R.h_img + img_off[i], images[i], static_cast<size_t>(hs[i]) * ws[i] * 3);
+        uint8_t* ht = R.h_tab + tab_off[i];
+        uint8_t* dt = R.d_tab + tab_off[i];
+        size_t o = 0;
+        auto put = [&](const void* src, size_t bytes) { std::memcpy(ht + o, src, bytes); const size_t at = o; o += bytes; return at; };
+        ResizeJob& j = sh->jobs[i];
+        j.d_img = (jpeg ? R.d_jimg : R.d_img) + img_off[i]; j.h = hs[i]; j.w = ws[i];
+        j.xf = reinterpret_cast<const int*>(dt + put(px[i].first.data(), 224 * 4));
+        j.xc = reinterpret_cast<const int*>(dt + put(px[i].count.data(), 224 * 4));
+        j.yf = reinterpret_cast<const int*>(dt + put(py[i].first.data(), 224 * 4));
+        j.yc = reinterpret_cast<const int*>(dt + put(py[i].count.data(), 224 * 4));
+        j.xi = reinterpret_cast<const int*>(dt + put(px[i].idx.data(), px[i].idx.size() * 4));
+        j.yi = reinterpret_cast<const int*>(dt + put(py[i].idx.data(), py[i].idx.size() * 4));
+        j.xw = reinterpret_cast<const float*>(dt + put(px[i].coef.data(), px[i].coef.size() * 4));
+        j.yw = reinterpret_cast<const float*>(dt + put(py[i].coef.data(), py[i].coef.size() * 4));
+        j.d_tmp = R.d_tmp;
+        j.d_out = L.d_in + static_cast<size_t>(i) * B2I_IMAGE_BYTES;
+      }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(fill_range, t);
+    fill_range(0);
+    for (auto& x : th) x.join();
   }
   stamp("tables");
   if (cu(cudaMemcpyAsync(R.d_tab, R.h_tab, tab_bytes, cudaMemcpyHostToDevice, L.st), "H2D resize tables")) return;
