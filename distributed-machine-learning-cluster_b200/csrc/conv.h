@@ -96,11 +96,8 @@ cudaError_t launch_stem(const uint8_t* in_u8, void* out_bf16, const CUtensorMap*
 // parity, channel), pixels along N, pooling in the epilogue's registers.  w2_dev: the [128][144] packed matrix
 // stem2_pack_weights builds from the [64][256] 16-bit weights launch_stem uses.
 void stem2_pack_weights(const uint16_t* w64x256, uint32_t* out128x144);
-void stem2_pack_weights_smem(const uint16_t* w64x256, uint16_t* out128x320);
-// tmW_smem: null = weights in tensor memory (w2_dev); else a make_tmap_weights(.., 128, 320, 128) map over the [128][320]
-// matrix of stem2_pack_weights_smem = weights as a shared-memory operand.
-cudaError_t launch_stem2(const uint8_t* in_u8, void* out16, const uint32_t* w2_dev, const CUtensorMap* tmW_smem, const float* bias_host,
-                         int n_images, unsigned int* sched, int f16, cudaStream_t st);
+cudaError_t launch_stem2(const uint8_t* in_u8, void* out16, const uint32_t* w2_dev, const float* bias_host, int n_images,
+                         unsigned int* sched, int f16, cudaStream_t st);
 
 // Fused AlexNet stem (bf16 path): u8 [n][224][224][3] -> normalise -> features.0 11x11/4 pad 2 + bias + ReLU -> bf16
 // [n][55][55][64].  tmW: weight map over [64][704] (K order: filter row, plane (R,G)/(B,0), 16 taps, 2 channels).

@@ -361,15 +361,6 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         owned_.push_back(p2);
         d.w2 = static_cast<uint32_t*>(p2);
         weight_bytes_ += w2.size() * 4;
-        std::vector<uint16_t> w2s(128 * 320);
-        stem2_pack_weights_smem(wb.data(), w2s.data());
-        void* p3 = nullptr;
-        B2I_CUDA(cudaMalloc(&p3, w2s.size() * 2));
-        B2I_CUDA(cudaMemcpy(p3, w2s.data(), w2s.size() * 2, cudaMemcpyHostToDevice));
-        owned_.push_back(p3);
-        weight_bytes_ += w2s.size() * 2;
-        const char* terr2 = "";
-        if (make_tmap_weights(&d.tmW2, p3, 128, 320, 128, &terr2)) { *err = std::string("stem (second form): ") + terr2; return false; }
       }
       void* bp = nullptr;
       B2I_CUDA(cudaMalloc(&bp, c.bias.size() * 4));
@@ -663,8 +654,7 @@ bool DeviceModel::run_microbatch(const uint8_t* d_u8, int nb, int k, int32_t* d_
       case OpSpec::STEM: {
         // B2I_STEM=1: the first form of the kernel (pixels on the accumulator lanes, stem.cu); default: stem2.cu
         static const int stem_form = [] { const char* e = getenv("B2I_STEM"); return e ? atoi(e) : 2; }();
-        // 2: weights in tensor memory, 3: weights in shared memory (both stem2.cu)
-        if (stem_form != 1) B2I_CUDA(launch_stem2(d_u8, buf(o.out), d.w2, stem_form == 3 ? &d.tmW2 : nullptr, d.bias_host.data(), nb, stem_sched_, f16, st));
+        if (stem_form != 1) B2I_CUDA(launch_stem2(d_u8, buf(o.out), d.w2, d.bias_host.data(), nb, stem_sched_, f16, st));
         else B2I_CUDA(launch_stem(d_u8, buf(o.out), &d.tmB, d.bias_host.data(), nb, stem_sched_, f16, st));
         break;
       }

@@ -120,7 +120,6 @@ class DeviceModel {
     ConvGeom g{};
     void* w = nullptr;
     uint32_t* w2 = nullptr;         // fused ResNet stem, second form: packed (parity, channel) x K matrix
-    CUtensorMap tmW2{};             // the same matrix as [128][320] 16-bit for the shared-memory form of that kernel
     float* bias = nullptr;
     std::vector<float> bias_host;   // fused stem only: its bias travels as kernel parameters
     CUtensorMap tmA{}, tmB{}, tmR{}, tmO{};

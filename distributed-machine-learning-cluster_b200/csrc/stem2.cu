@@ -29,8 +29,6 @@
 //   warps 0-15  two epilogue groups of eight warps: two sets (pooled rows 0-3 / 4-6) x four TMEM lane quarters
 //   warps 16-17 MMA issue, one per half of the tile's columns
 //   warps 18-25 two loader groups of four warps
-#include <vector>
-
 #include "conv.h"
 #include "ops.h"
 #include "ptx.cuh"
@@ -47,9 +45,6 @@ constexpr uint32_t PATCH_ROW_BYTES = PATCH_W * 8;      // 320
 constexpr uint32_t PATCH_BYTES = ((PATCH_H * PATCH_W * 8 + 127) / 128) * 128;
 constexpr uint32_t X_BYTES = 2 * 49 * 128;             // pooled candidates of one tile: [parity][7 x 7][64] 16-bit
 constexpr uint32_t S2_SMEM = 2 * PATCH_BYTES + 2 * X_BYTES + 1024;
-constexpr int W_KBLOCKS = 5;                            // shared-memory form of the weights: [128][320] as five 128B-swizzled k-blocks
-constexpr uint32_t W_BYTES = W_KBLOCKS * 128 * 128;     // 80 KB
-constexpr uint32_t S2_SMEM_WS = S2_SMEM + W_BYTES;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t A_COL = 256;                        // weights: columns 256 .. 399 (18 K chunks x 8 columns)
 constexpr int KCHUNKS = 18;                            // 9 input rows x 2 halves of 4 taps x 4 channels
@@ -105,16 +100,12 @@ template <bool F16> __device__ __forceinline__ uint16_t to16(float v) {
   else return __bfloat16_as_ushort(__float2bfloat16_rn(v));
 }
 
-// WS = false: the weights are the MMA's A operand in TENSOR memory (tcgen05.st once per CTA);
-// WS = true:  the weights are the A operand in SHARED memory (five TMA loads once per CTA): 6 KB of operand reads per
-//             MMA instead of 2 KB, but MMAs with shared-memory operands pipeline from one issuing warp, while the
-//             tensor-memory form completes one MMA per ~160 cycles and issuing warp.
-template <bool F16, bool WS>
+template <bool F16>
 __global__ void __launch_bounds__(S2_THREADS, 1)
-stem2_kernel(const __grid_constant__ CUtensorMap tmW, const Stem2Params p) {
+stem2_kernel(const Stem2Params p) {
   griddep_launch();
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[9];   // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2], w_full
+  __shared__ __align__(8) uint64_t bars[8];   // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2]
   __shared__ uint32_t tmem_slot;
   __shared__ int tile_ring[8];                // tile of iteration i (or -1 = this loader group is out of tiles)
 
@@ -122,10 +113,8 @@ stem2_kernel(const __grid_constant__ CUtensorMap tmW, const Stem2Params p) {
   const int warp = tid >> 5;
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t w_smem = base;                                   // WS only
-  const uint32_t patch0 = base + (WS ? W_BYTES : 0u);
-  const uint32_t x0 = patch0 + 2 * PATCH_BYTES;
-  const uint32_t w_full = smem_u32(bars) + 8u * 8;
+  const uint32_t patch0 = base;
+  const uint32_t x0 = base + 2 * PATCH_BYTES;
   const uint32_t bar0 = smem_u32(bars);
   auto patch_full = [&](int b) { return bar0 + 8u * b; };
   auto patch_empty = [&](int b) { return bar0 + 8u * (2 + b); };
@@ -139,22 +128,15 @@ stem2_kernel(const __grid_constant__ CUtensorMap tmW, const Stem2Params p) {
       mbar_init(acc_full(b), S2_MMA_WARPS);
       mbar_init(acc_empty(b), 8);
     }
-    mbar_init(w_full, 1);
     mbar_fence_init();
   }
   constexpr int MMA_WARP = S2_DRAIN / 32;
-  if (warp == MMA_WARP) tmem_alloc(smem_u32(&tmem_slot), WS ? 256u : TMEM_COLS);
+  if (warp == MMA_WARP) tmem_alloc(smem_u32(&tmem_slot), TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
-  if (WS) {
-    if (warp == MMA_WARP && lane == 0) {   // weights -> shared memory, once
-      tma_prefetch_desc(&tmW);
-      mbar_expect_tx(w_full, W_BYTES);
-      for (int kb = 0; kb < W_KBLOCKS; ++kb) tma_load_2d(w_smem + kb * 16384u, &tmW, w_full, kb * 64, 0);
-    }
-  } else if (warp < 4) {
+  if (warp < 4) {
     // weights -> tensor memory, once: thread = row (parity, channel) of its warp's lane quarter
     const uint32_t* src = p.w2 + static_cast<size_t>(warp * 32 + lane) * (KCHUNKS * 8);
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + A_COL;
@@ -185,7 +167,6 @@ stem2_kernel(const __grid_constant__ CUtensorMap tmW, const Stem2Params p) {
     // of the committing thread, so both warps commit and the barriers count two arrivals.
     const int hx = warp - MMA_WARP;
     const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
-    if (WS) mbar_wait(w_full, 0);
     bool done[2] = {false, false};
     for (int i = 0;; ++i) {
       const int b = i & 1;
@@ -208,8 +189,7 @@ stem2_kernel(const __grid_constant__ CUtensorMap tmW, const Stem2Params p) {
 #pragma unroll
         for (int t = 0; t < KCHUNKS; ++t) {      // input row rho = t / 2 under the pair's even conv row, taps 4 * (t & 1) .. + 3
           const uint32_t b_addr = pbase + static_cast<uint32_t>((t >> 1) * PATCH_ROW_BYTES + hx * 128 + (t & 1) * 32);
-          if (WS) umma_bf16_elect(d_tmem, umma_smem_desc_sw128(w_smem + static_cast<uint32_t>(t >> 2) * 16384u) + 2u * (t & 3), patch_desc_pairs(b_addr), idesc, t != 0 ? 1u : 0u);
-          else umma_ts_elect(d_tmem, tmem_base + A_COL + static_cast<uint32_t>(t * 8), patch_desc_pairs(b_addr), idesc, t != 0 ? 1u : 0u);
+          umma_ts_elect(d_tmem, tmem_base + A_COL + static_cast<uint32_t>(t * 8), patch_desc_pairs(b_addr), idesc, t != 0 ? 1u : 0u);
         }
       }
       umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
@@ -395,7 +375,7 @@ stem2_kernel(const __grid_constant__ CUtensorMap tmW, const Stem2Params p) {
   }
   if (warp == MMA_WARP) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, WS ? 256u : TMEM_COLS);
+    tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -420,36 +400,17 @@ void stem2_pack_weights(const uint16_t* w64x256, uint32_t* out) {
       }
 }
 
-// The same matrix as 16-bit [128][320] (K padded from 288 to five 64-wide blocks) for the shared-memory form.
-void stem2_pack_weights_smem(const uint16_t* w64x256, uint16_t* out128x320) {
-  std::vector<uint32_t> packed(128 * KCHUNKS * 8);
-  stem2_pack_weights(w64x256, packed.data());
-  for (int m = 0; m < 128; ++m)
-    for (int k = 0; k < 320; ++k) {
-      uint16_t v = 0;
-      if (k < KCHUNKS * 16) {
-        const uint32_t wd = packed[static_cast<size_t>(m) * (KCHUNKS * 8) + (k >> 1)];
-        v = static_cast<uint16_t>((k & 1) ? (wd >> 16) : (wd & 0xFFFFu));
-      }
-      out128x320[m * 320 + k] = v;
-    }
-}
-
-cudaError_t launch_stem2(const uint8_t* in_u8, void* out16, const uint32_t* w2_dev, const CUtensorMap* tmW_smem, const float* bias_host,
-                         int n_images, unsigned int* sched, int f16, cudaStream_t st) {
+cudaError_t launch_stem2(const uint8_t* in_u8, void* out16, const uint32_t* w2_dev, const float* bias_host, int n_images,
+                         unsigned int* sched, int f16, cudaStream_t st) {
   static bool attr_set[16] = {};
   static int sm_count[16] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(stem2_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(stem2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(stem2_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(stem2_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_WS);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(stem2_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM_WS);
+    e = cudaFuncSetAttribute(stem2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
@@ -465,13 +426,8 @@ cudaError_t launch_stem2(const uint8_t* in_u8, void* out16, const uint32_t* w2_d
   p.total_tiles = n_images * 64;
   p.sched = sched;
   const int grid = (p.total_tiles + 1) / 2 < sm_count[dev] ? (p.total_tiles + 1) / 2 : sm_count[dev];
-  if (tmW_smem) {
-    if (f16) return launch_pdl(stem2_kernel<true, true>, dim3(grid), dim3(S2_THREADS), S2_SMEM_WS, st, *tmW_smem, p);
-    return launch_pdl(stem2_kernel<false, true>, dim3(grid), dim3(S2_THREADS), S2_SMEM_WS, st, *tmW_smem, p);
-  }
-  CUtensorMap none{};
-  if (f16) return launch_pdl(stem2_kernel<true, false>, dim3(grid), dim3(S2_THREADS), S2_SMEM, st, none, p);
-  return launch_pdl(stem2_kernel<false, false>, dim3(grid), dim3(S2_THREADS), S2_SMEM, st, none, p);
+  if (f16) return launch_pdl(stem2_kernel<true>, dim3(grid), dim3(S2_THREADS), S2_SMEM, st, p);
+  return launch_pdl(stem2_kernel<false>, dim3(grid), dim3(S2_THREADS), S2_SMEM, st, p);
 }
 
 }  // namespace b2i
