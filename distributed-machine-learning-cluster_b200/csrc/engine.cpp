@@ -518,7 +518,10 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           // layer4 run at that fill rate, profiles/r03_ncu_step_full.csv)
           const long long fill = (static_cast<long long>(ms) * 16384 + (d.resident_b ? 0 : bn / 2 * 128)) / 40;
           const long long kb_cycles = std::max<long long>(std::max<long long>(req, fill), static_cast<long long>(ms) * 4 * (bn / 2));
-          const long long epi = (2 * ms * bn > 512) ? 10000 : 0;
+          // one accumulator set only: the MMAs of the next tile wait for the whole epilogue and the operand ring runs
+          // dry meanwhile.  30000 reproduces layer4 at (256, 2): 118k cycles measured, against 111k at (256, 1)
+          // (profiles/r03_layer4_tiling_matrix.txt)
+          const long long epi = (2 * ms * bn > 512) ? 30000 : 0;
           const long long kb_avg = carries ? (kb + c.Cin_pad / 64) / 2 : kb;
           return waves * (kb_avg * kb_cycles + epi + 600);   // + per-tile set-up (barrier turn-around, bias / residual fetch)
         };

@@ -28,6 +28,25 @@ def child(args):
     with b2.Model(ctx, "resnet18", ot, max_batch=args.batch) as m:
         for lo in range(0, len(blobs), args.batch):      # warm-up: decoder set-up, buffers grow to their final size
             m.predict_jpeg(blobs[lo:lo + args.batch], k=5)
+        if args.save:      # logits of every image, to compare the arrangements' decoded pixels through the network
+            lg = np.concatenate([m.predict_jpeg(blobs[lo:lo + args.batch], k=5, want_logits=True)[2] for lo in range(0, len(blobs), args.batch)])
+            np.save(args.save, lg)
+        if args.callers > 1:   # several caller threads on one model: one request's decode overlaps another's forward
+            import threading
+            best = 0.0
+            for r in range(args.reps):
+                chunks = [blobs[lo:lo + args.batch] for lo in range(0, len(blobs), args.batch)] * 2
+                def work(ix):
+                    for c in chunks[ix::args.callers]:
+                        m.predict_jpeg(c, k=5)
+                th = [threading.Thread(target=work, args=(i,)) for i in range(args.callers)]
+                t0 = time.perf_counter()
+                [t.start() for t in th]
+                [t.join() for t in th]
+                best = max(best, 2 * len(blobs) / (time.perf_counter() - t0))
+            print(json.dumps({"arrangement": args.label, "backend": ctx.jpeg_backend(), "callers": args.callers, "images_per_s": best,
+                              "batch": args.batch, "images": 2 * len(blobs)}), flush=True)
+            return
         best = 0.0
         for r in range(args.reps):
             t0 = time.perf_counter()
@@ -48,6 +67,8 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--label", default="")
+    ap.add_argument("--callers", type=int, default=1)
+    ap.add_argument("--save", default="")
     args = ap.parse_args()
     if args.label:
         return child(args)
