@@ -165,6 +165,27 @@ def cpu_oracle_rate(model, budget_s, batch=64):
     return done / el, torch.get_num_threads(), "%d images in batches of %d (%.1f s)" % (done, batch, el)
 
 
+def cpu_reference_mode(model):
+    """The two other CPU figures SURVEY.md 8(d) asks for beside the batched one: the restatement run the way the reference
+    runs it (one image per forward, services.rs:421,493) and its preprocessing (resize + crop of a 500 x 375 image)."""
+    import numpy as np
+    from oracle import stb_resize, synth, tch_oracle
+    w, _, _ = bench_weights(model)
+    imgs = synth.synthetic_images(12, seed=3)
+    tch_oracle.predict_u8(model, w, imgs[:1], k=1, batch=1)
+    t0 = time.perf_counter()
+    for i in range(len(imgs)):
+        tch_oracle.predict_u8(model, w, imgs[i:i + 1], k=1, batch=1)
+    b1 = len(imgs) / (time.perf_counter() - t0)
+    raw = np.random.default_rng(5).integers(0, 256, (375, 500, 3), dtype=np.uint8)
+    stb_resize.resize_crop_224(raw)
+    t0 = time.perf_counter()
+    for _ in range(8):
+        stb_resize.resize_crop_224(raw)
+    return {"batch1_images_per_s": b1, "preprocess_ms_per_image": 1000.0 * (time.perf_counter() - t0) / 8,
+            "note": "one image per forward as the reference does (torch CPU, all host threads); resize + crop of a 500 x 375 image by the numpy restatement of stb_image_resize, one thread (test infrastructure, not the reference's C code)"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the CPU restatement of the path, each step a bounded sample of the batch."""
     if rank != 0:
@@ -193,6 +214,48 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
+
+
+def from_files_record(b2, ctx, ot, prec):
+    """File names -> answers through the reference-facing interface (Leader.run_job, services.rs:404-433 / 476-496) over the
+    committed reference JPEGs, cycled: images/s with one PIL decode at a time on the calling thread (the reference's
+    arrangement) and with the library's decode stage (nvJPEG on host threads + GPU where it loads, else a PIL pool)."""
+    import shutil
+    import tempfile
+    root = os.path.join(ROOT, "tests", "golden", "imagenet_1k", "train")
+    labels = b2.load_labels(os.path.join(ROOT, "tests", "golden", "synset_words.txt"))
+    have = set(os.listdir(root))
+    lab = [(w, name) for w, name in labels if w in have]
+    if not lab:
+        return None
+    rec = {"api": "Leader.run_job(batch=256, in_flight=2) from image ids", "jpeg_files": len(lab), "unit": "images/s"}
+    wd = tempfile.mkdtemp()
+    os.symlink(os.path.abspath(ot), os.path.join(wd, "resnet18.ot"))
+    try:
+        for key, decoder, threads, ids, passes in (("pil_on_calling_thread", "pil", 1, lab[:128], 2),
+                                                   ("decode_stage", "auto", None, lab * max(1, 1024 // len(lab)), 3)):
+            member = b2.MemberState(ctx, labels, weight_dir=wd, image_root=root, precision=prec, max_batch=256,
+                                    models=("resnet18",), decoder=decoder, decode_threads=threads)
+            try:
+                best = 0.0
+                for rep in range(passes):   # the first pass warms the lanes and the decoder up
+                    leader = b2.Leader(member, ids)
+                    leader.resnet18.assigned_member_ids = [0]
+                    t0 = time.perf_counter()
+                    leader.run_job(leader.resnet18, batch=256)
+                    dt = time.perf_counter() - t0
+                    if rep:
+                        best = max(best, leader.resnet18.finished_prediction_count / dt)
+                rec[key] = {"value": best, "images": len(ids), "decoder": member.decoder, "host_threads": member.pool._max_workers}
+                if member.decoder == "nvjpeg":
+                    rec[key]["backend"] = ctx.jpeg_backend()
+            finally:
+                member.close()
+        if rec["pil_on_calling_thread"]["value"] > 0:
+            rec["ratio"] = rec["decode_stage"]["value"] / rec["pil_on_calling_thread"]["value"]
+    finally:
+        shutil.rmtree(wd, ignore_errors=True)
+    return rec
 
 
 def bind_to_gpu_numa_node(gpu_index):
@@ -549,10 +612,21 @@ def main():
     if world == 1:   # rank 0 at N = 1 only: with more ranks the other processes compete for the host cores
         cpu_val, cores, sample = cpu_oracle_rate(MODEL, args.cpu_budget)
         cpu_baseline = {"value": cpu_val, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample}
+        if not args.no_extras:
+            try:
+                cpu_baseline["reference_mode"] = cpu_reference_mode(MODEL)
+            except Exception as ex:   # an extra record must not cost the bench line
+                cpu_baseline["reference_mode"] = {"error": str(ex)}
     else:
         cpu_baseline = {"value": None, "unit": "images/s", "cores": None, "kind": "port",
                         "sample": "taken at N = 1 only (the --impl reference arm measures it at every N)"}
     gpu_launches = model.launches_per_microbatch * n_micro * args.steps
+    from_files = None
+    if world == 1 and not args.no_extras and MODEL == "resnet18":
+        try:
+            from_files = from_files_record(b2, ctx, ot, prec)
+        except Exception as ex:   # an extra record must not cost the bench line
+            from_files = {"error": str(ex)}
     inproc = None
     if world == 1 and not args.no_extras and MODEL == "resnet18":
         try:
@@ -592,6 +666,7 @@ def main():
         "parity": parity,
         ("fp16" if args.precision == "bf16" else "bf16"): other,
         "inproc": inproc,
+        "from_files": from_files,
         "launch_ms": {name: round(ms, 4) for name, ms in prof},
     }
     print(json.dumps(out))
