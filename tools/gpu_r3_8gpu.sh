@@ -9,7 +9,7 @@ timeout 400 python bench.py --steps 20 --warmup 5 --cpu-budget 0.3 > gpurun_out/
 python -c "
 import json; d=json.load(open('gpurun_out/bench_inproc8.json')); print('value',round(d['value']),'e2e',round(d['e2e']['value'])); print(json.dumps(d['inproc'])[:1200])"
 port=29520
-for n in 4 8; do
+for n in 2 4 8; do
   port=$((port+1))
   timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port bench.py --gpus $n --steps 20 --warmup 5 > gpurun_out/bench_${n}gpu.json 2> gpurun_out/bench_${n}gpu.err; echo "=== torchrun N=$n exit $?"; tail -1 gpurun_out/bench_${n}gpu.err | cut -c1-300
   python -c "
