@@ -58,7 +58,7 @@ struct ConvArgs {
   const CUtensorMap* tmR = nullptr;   // halo-patch kernel: 16 x 8 tile maps over the residual and the output
   const CUtensorMap* tmO = nullptr;
   int patch = 0;                  // 3x3/s1/p1, 64->64 only: halo-patch kernel (tmA = make_tmap_patch)
-  int flat = 0;                   // 3x3/s1/p1, one N tile: flattened-row CTA-pair kernel (tmA = make_tmap_flat, tmB with BN/2 box rows)
+  int flat = 0;                   // 1: 3x3/s1/p1, one N tile: flattened-row CTA-pair kernel, resident weights (tmA = make_tmap_flat, tmB with BN/2 box rows); 2: streamed weights, several N tiles (tmA = make_tmap_flat_pitch with conv_flat_stream_pitch)
   // split-K (persistent kernel, A_TILED = FC layers): `splits` CTAs per output tile over disjoint k-block ranges;
   // ws: fp32 [splits][rows padded to 128][ldw] scratch; ctr: one int per output tile, all zero between launches
   int splits = 1, ldw = 0;
@@ -71,6 +71,10 @@ struct ConvArgs {
 bool conv_flat_applicable(const ConvGeom& g, int BN);
 int conv_flat_pitch(int W);
 int make_tmap_flat(CUtensorMap* tm, const void* x, int N, int H, int W, int C, const char** err);
+// streamed-weights form of the same kernel (a.flat = 2): several N tiles, weights through a ring, pitch W + 1 where that is a power of two
+bool conv_flat_stream_applicable(const ConvGeom& g, int BN);
+int conv_flat_stream_pitch(int W);
+int make_tmap_flat_pitch(CUtensorMap* tm, const void* x, int N, int H, int W, int C, int pitch, const char** err);
 // True when the halo-patch kernel handles this geometry (ResNet layer1 convolutions).
 bool conv_patch_applicable(const ConvGeom& g);
 int make_tmap_patch(CUtensorMap* tm, const void* x, int N, int H, int W, const char** err);   // 18 x 10 halo patch

@@ -179,7 +179,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 1];
   __shared__ uint32_t tmem_slot;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
   const int tile_n = blockIdx.x % p.tiles_n;
   const int tile_m = blockIdx.x / p.tiles_n;
@@ -211,7 +211,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
   if (warp < 4) {
@@ -407,7 +407,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   __shared__ uint32_t tmem_slot;
   __shared__ int split_last;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t b_tile_bytes = static_cast<uint32_t>(p.BN) * 128u;
@@ -441,7 +441,7 @@ conv_umma_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
 
   const int prod_id = warp == 0 ? 0 : (warp >= PTHREADS / 32 ? warp - PTHREADS / 32 + 1 : -1);
@@ -694,9 +694,9 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 5];
   __shared__ uint32_t tmem_slot;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
+  const uint32_t rank = __shfl_sync(0xffffffffu, cluster_ctarank(), 0);
   const bool leader = rank == 0;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
@@ -753,7 +753,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   __syncthreads();
   cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   if (resb && warp == 0 && lane == 0) {   // weights do not depend on the previous kernel: fetch them before waiting for it
     if (leader) mbar_expect_tx(b_full_bar, 2u * resb_bytes);
     else mbar_arrive_cluster(b_full_bar, 0);
@@ -967,9 +967,9 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   __shared__ __align__(8) uint64_t bars[2 * FLAT_MAXBUF + 5];   // full[], empty[], acc_full[2], acc_empty[2], b_full
   __shared__ uint32_t tmem_slot;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
+  const uint32_t rank = __shfl_sync(0xffffffffu, cluster_ctarank(), 0);
   const bool leader = rank == 0;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
@@ -1017,7 +1017,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   __syncthreads();
   cluster_sync_all();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   if (warp == 0 && lane == 0) {   // weights do not depend on the previous kernel: fetch them before waiting for it
     if (leader) mbar_expect_tx(b_full_bar, 2u * resb_bytes);
     else mbar_arrive_cluster(b_full_bar, 0);
@@ -1132,6 +1132,229 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
 }
 
 // ------------------------------------------------------------------------------------------------
+// The same flattened-row form with STREAMED weights and several N tiles (ResNet layer4: 512 -> 512 channels on 7x7
+// maps, 4.7 MB of weights).  Why: an SM's TMA unit takes about 1.5 cycles per 128-byte row of a tiled box and more
+// per row (pixel) of an im2col box (tools/microbench/l2_rate.cu: 85 B/clk per SM with three issuing warps of tiled
+// loads; the im2col pair kernel above runs at 43 B/clk).  With 128-byte-swizzled operands every row is 128 bytes, so a
+// k-block of the im2col kernel costs 128 pixel rows + 128 weight rows of TMA work = ~760 cycles against 512 cycles of
+// MMAs.  Here a k-block costs 1/9 of a halo patch (16 rows for a 144-pixel patch) + 128 weight rows.
+// Row pitch: W + 1 when that is a power of two (7x7 maps: pitch 8: pixel 0 of a row is the left zero pad and doubles
+// as the right pad of the row above; 49 of every 64 positions are real outputs), else conv_flat_pitch(W).
+// Warps: 0 = patch loads, 1 = MMA issue (leader CTA), 2..9 = epilogue, 10..11 = weight loads (k-blocks dealt in turn).
+struct FlatSP {
+  int H, W, N, slices, BN, pitch, rpt, box_w, tiles_n;
+  int total_pairs, na, nb;
+  int ldo, relu, Cout, f16, rev;
+  uint32_t tmem_cols;
+  const float* bias;
+  const __nv_bfloat16* residual;
+  void* out;
+};
+
+constexpr int FLATS_MAXA = 4, FLATS_MAXB = 8;
+constexpr int FLATS_THREADS = PTHREADS + 64;
+
+template <bool F16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FLATS_THREADS, 1)
+conv3x3_flat_stream_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB, const FlatSP p) {
+  griddep_launch();
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * FLATS_MAXA + 2 * FLATS_MAXB + 4];   // a_full[], a_empty[], b_full[], b_empty[], acc_full[2], acc_empty[2]
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = __shfl_sync(0xffffffffu, cluster_ctarank(), 0);
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int half_n = p.BN >> 1;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_tile_bytes = static_cast<uint32_t>(half_n) * 128u;
+  const uint32_t row_bytes = static_cast<uint32_t>(p.pitch) * 128u;
+  // one 64-channel slice of the halo patch; the view of tap (2, 2) runs two pixels past the last patch row (they only
+  // feed dropped pad outputs), hence the extra KB that keeps those reads inside the buffer
+  const uint32_t patch_bytes = ((static_cast<uint32_t>(p.rpt + 2) * row_bytes + 1024u) + 1023u) & ~1023u;
+  const uint32_t tx_bytes = static_cast<uint32_t>(p.rpt + 2) * static_cast<uint32_t>(p.box_w) * 128u;
+  const uint32_t a_base = smem_base;
+  const uint32_t b_base = smem_base + static_cast<uint32_t>(p.na) * patch_bytes;
+  const uint32_t bar0 = smem_u32(bars);
+  auto a_full = [&](int s) { return bar0 + 8u * s; };
+  auto a_empty = [&](int s) { return bar0 + 8u * (FLATS_MAXA + s); };
+  auto b_full = [&](int s) { return bar0 + 8u * (2 * FLATS_MAXA + s); };
+  auto b_empty = [&](int s) { return bar0 + 8u * (2 * FLATS_MAXA + FLATS_MAXB + s); };
+  auto acc_full_bar = [&](int b) { return bar0 + 8u * (2 * FLATS_MAXA + 2 * FLATS_MAXB + b); };
+  auto acc_empty_bar = [&](int b) { return bar0 + 8u * (2 * FLATS_MAXA + 2 * FLATS_MAXB + 2 + b); };
+  const int total_items = p.total_pairs * p.tiles_n;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.na; ++s) {
+      mbar_init(a_full(s), 2);    // leader's expect_tx arrive + the peer's arrive
+      mbar_init(a_empty(s), 1);
+    }
+    for (int s = 0; s < p.nb; ++s) {
+      mbar_init(b_full(s), 2);
+      mbar_init(b_empty(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full_bar(b), 1);
+      mbar_init(acc_empty_bar(b), 16);  // 8 epilogue warps in each of the two CTAs
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
+  const int hp = p.H + 1;   // padded rows per image
+
+  if (warp >= PTHREADS / 32) {
+    // weight k-blocks: they do not depend on the previous kernel, so the first ring-full goes out before the wait
+    if (lane == 0) {
+      const int me = warp - PTHREADS / 32;
+      int s = 0, ph = 0, turn = 0;
+      for (int w0 = cluster_id; w0 < total_items; w0 += num_clusters) {
+        const int w = p.rev ? total_items - 1 - w0 : w0;
+        const int nn = w % p.tiles_n;
+        const int nrow = nn * p.BN + static_cast<int>(rank) * half_n;
+        for (int sl = 0; sl < p.slices; ++sl) {
+          for (int tap = 0; tap < 9; ++tap) {
+            const bool mine = turn == me;
+            turn ^= 1;
+            if (mine) {
+              mbar_wait(b_empty(s), ph ^ 1);
+              if (leader) mbar_expect_tx(b_full(s), 2u * b_tile_bytes);
+              else mbar_arrive_cluster(b_full(s), 0);
+              tma_load_2d_2sm(b_base + s * b_tile_bytes, &tmB, b_full(s), (tap * p.slices + sl) * BK, nrow);
+            }
+            if (++s == p.nb) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 0) {
+    griddep_wait();   // activations of the previous kernel are read from here on
+    if (lane == 0) {
+      int s = 0, ph = 0;
+      for (int w0 = cluster_id; w0 < total_items; w0 += num_clusters) {
+        const int w = p.rev ? total_items - 1 - w0 : w0;
+        const int t = w / p.tiles_n;
+        const int y0 = (2 * t + static_cast<int>(rank)) * p.rpt - 1;   // first patch row (one above the tile)
+        for (int sl = 0; sl < p.slices; ++sl) {
+          mbar_wait(a_empty(s), ph ^ 1);
+          const uint32_t a_s = a_base + s * patch_bytes;
+          if (leader) mbar_expect_tx(a_full(s), 2u * tx_bytes);
+          else mbar_arrive_cluster(a_full(s), 0);
+          for (int j = 0; j < p.rpt + 2; ++j) {
+            const int Y = y0 + j;
+            int n = -1, y = 0;                       // Y = -1: above the first image, all out of range -> zeros
+            if (Y >= 0) { n = Y / hp; y = Y - n * hp; }   // y == H (or n >= N) is out of range too -> the shared zero row
+            tma_load_4d_2sm(a_s + j * row_bytes, &tmX, a_full(s), sl * 64, -1, y, n);
+          }
+          if (++s == p.na) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader) {
+      const uint32_t idesc = umma_idesc_bf16(256, p.BN, F16 ? 1 : 0);
+      int sa = 0, pha = 0, sb = 0, phb = 0, i = 0;
+      for (int w0 = cluster_id; w0 < total_items; w0 += num_clusters, ++i) {
+        const int buf = i & 1;
+        mbar_wait(acc_empty_bar(buf), ((i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * p.BN);
+        for (int sl = 0; sl < p.slices; ++sl) {
+          mbar_wait(a_full(sa), pha);
+          tc_fence_after();
+          const uint32_t a_s = a_base + sa * patch_bytes;
+#pragma unroll 1
+          for (int tap = 0; tap < 9; ++tap) {
+            mbar_wait(b_full(sb), phb);
+            tc_fence_after();
+            const uint64_t adesc = umma_smem_desc_sw128(a_s + static_cast<uint32_t>((tap / 3) * p.pitch + (tap % 3)) * 128u);
+            const uint64_t bdesc = umma_smem_desc_sw128(b_base + sb * b_tile_bytes);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_2sm(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (sl | tap | k) != 0 ? 1u : 0u);
+            umma_commit_2sm(b_empty(sb));
+            if (++sb == p.nb) { sb = 0; phb ^= 1; }
+          }
+          umma_commit_2sm(a_empty(sa));
+          if (++sa == p.na) { sa = 0; pha ^= 1; }
+        }
+        umma_commit_2sm(acc_full_bar(buf));
+      }
+    }
+  } else {
+    griddep_wait();   // the residual is an earlier kernel's output
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int n_chunks = p.BN >> 5;
+    const int last_c = ((n_chunks - 1 - half) & ~1) + half;
+    Epi epi;
+    epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
+    int i = 0;
+    for (int w0 = cluster_id; w0 < total_items; w0 += num_clusters, ++i) {
+      const int w = p.rev ? total_items - 1 - w0 : w0;
+      const int t = w / p.tiles_n;
+      const int n0 = (w % p.tiles_n) * p.BN;
+      const int buf = i & 1;
+      const int pos = q * 32 + lane;                                  // position inside this CTA's tile
+      const int Y = (2 * t + static_cast<int>(rank)) * p.rpt + pos / p.pitch;
+      const int xo = pos % p.pitch;
+      const int n = Y / hp, y = Y - n * hp;
+      const bool row_ok = xo < p.W && y < p.H && n < p.N;
+      const int m = (n * p.H + y) * p.W + xo;
+      const bool pre = row_ok && epi.residual != nullptr;
+      uint32_t rr[4][16];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (pre && half + 2 * j < n_chunks) prefetch_residual(epi, m, n0 + (half + 2 * j) * 32, rr[j]);
+      mbar_wait(acc_full_bar(buf), (i >> 1) & 1);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * p.BN);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = half + 2 * j;
+        if (c >= n_chunks) break;
+        uint32_t v[32];
+        tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
+        tmem_ld_wait();
+        if (c == last_c) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (leader) mbar_arrive(acc_empty_bar(buf));
+            else mbar_arrive_cluster(acc_empty_bar(buf), 0);
+          }
+        }
+        if (row_ok) epilogue_chunk<F16>(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // 3x3 / stride 1 / pad 1 convolution with 64 input and 64 output channels (ResNet layer1), reading
 // the nine filter taps as SHIFTED VIEWS of one halo patch instead of nine im2col loads.
 //
@@ -1184,7 +1407,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   __shared__ __align__(8) uint64_t bars[3 * PT_BUFS + 5];  // patch_full[], patch_empty[], res_empty[], acc_full[2], acc_empty[2], w_full
   __shared__ uint32_t tmem_slot;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_smem = base;
@@ -1223,7 +1446,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   if (warp == 0 && lane == 0) {   // the weights do not depend on the previous kernel: fetch them before waiting for it
     mbar_expect_tx(w_full, PT_WBYTES);
     for (int tap = 0; tap < 9; ++tap) tma_load_2d(w_smem + tap * 8192u, &tmW, w_full, tap * 64, 0);
@@ -1556,6 +1779,46 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   return launch_pdl(conv3x3_flat_pair_kernel<F16>, dim3(static_cast<unsigned>(grid)), dim3(PTHREADS), smem, st, *tmX, *tmB, p);
 }
 
+template <bool F16>
+cudaError_t launch_flat_stream(const ConvArgs& a, const CUtensorMap* tmX, const CUtensorMap* tmB, cudaStream_t st) {
+  static bool attr_set[16] = {};
+  static int sm_count[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 16) return cudaErrorInvalidDevice;
+  if (!attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_flat_stream_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  const ConvGeom& g = a.g;
+  FlatSP p;
+  p.H = g.H; p.W = g.W; p.N = g.N; p.slices = g.C / 64; p.BN = a.BN;
+  p.pitch = conv_flat_stream_pitch(g.W);
+  p.rpt = 128 / p.pitch;
+  p.box_w = p.pitch;
+  p.tiles_n = g.Cout / a.BN;
+  const int rows_total = g.N * (g.H + 1);
+  p.total_pairs = (rows_total + 2 * p.rpt - 1) / (2 * p.rpt);
+  const size_t patch = ((static_cast<size_t>(p.rpt + 2) * p.pitch * 128 + 1024) + 1023) & ~static_cast<size_t>(1023);
+  const size_t btile = static_cast<size_t>(a.BN / 2) * 128;
+  p.na = 3;
+  p.nb = static_cast<int>(std::min<size_t>(FLATS_MAXB, (225 * 1024 - 1024 - p.na * patch) / btile));
+  if (p.nb < 3) return cudaErrorInvalidValue;
+  p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout; p.f16 = a.f16; p.rev = a.reverse;
+  uint32_t cols = 32;
+  while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.bias = a.bias;
+  p.residual = static_cast<const __nv_bfloat16*>(a.residual);
+  p.out = a.out;
+  const int grid = std::min(2 * p.total_pairs * p.tiles_n, sm_count[dev] & ~1);
+  const size_t smem = p.na * patch + p.nb * btile + 1024;
+  return launch_pdl(conv3x3_flat_stream_kernel<F16>, dim3(static_cast<unsigned>(grid)), dim3(FLATS_THREADS), smem, st, *tmX, *tmB, p);
+}
+
 template <int AMODE, bool B_TMA, bool F16>
 cudaError_t launch_t(const ConvArgs& a, const CUtensorMap* tmA, const CUtensorMap* tmB,
                      cudaStream_t st) {
@@ -1609,6 +1872,10 @@ static cudaError_t launch_conv_umma_t(const ConvArgs& a, const CUtensorMap* tmA,
     return cudaErrorInvalidValue;
   if (!a.out_fp32 && ((a.ldo & 15) || (g.Cout & 31))) return cudaErrorInvalidValue;
   if (a.tmB2 && !((a.amode == A_IM2COL) && (a.persistent || a.pair))) return cudaErrorInvalidValue;
+  if (a.flat == 2) {
+    if (!conv_flat_stream_applicable(g, a.BN) || a.out_fp32 || a.ldo != g.Cout || !tmA || !tmB) return cudaErrorInvalidValue;
+    return launch_flat_stream<F16>(a, tmA, tmB, st);
+  }
   if (a.flat) {
     if (!conv_flat_applicable(g, a.BN) || a.out_fp32 || a.ldo != g.Cout || !tmA || !tmB) return cudaErrorInvalidValue;
     return launch_flat<F16>(a, tmA, tmB, st);
@@ -1701,13 +1968,33 @@ bool conv_flat_applicable(const ConvGeom& g, int BN) {
   return resb + 2 * patch + 1024 <= 226 * 1024;
 }
 
-// Tiled 4-D map over NHWC [N][H][W][C] whose box is one 64-channel slice of `box_w` pixels of one row.
+// Row pitch of the streamed-weights flattened-row kernel: W + 1 when that is a power of two >= 8 (the left pad of a row
+// is the right pad of the row above), else the pitch of the resident-weights kernel.
+int conv_flat_stream_pitch(int W) {
+  const int p1 = W + 1;
+  return (p1 >= 8 && p1 <= 64 && (p1 & (p1 - 1)) == 0) ? p1 : conv_flat_pitch(W);
+}
+
+// True when conv3x3_flat_stream_kernel handles this geometry: 3x3 / s1 / p1, channels a multiple of 64, output
+// channels a multiple of the tile width (128 or 256).
+bool conv_flat_stream_applicable(const ConvGeom& g, int BN) {
+  if (g.R != 3 || g.S != 3 || g.stride != 1 || g.pad != 1 || g.OH != g.H || g.OW != g.W) return false;
+  if (g.C % 64 || g.K != 9 * g.C || (BN != 128 && BN != 256) || g.Cout % BN || g.Cout != g.Cout_pad) return false;
+  const int pitch = conv_flat_stream_pitch(g.W);
+  return pitch <= 64 && (g.W + 2 <= pitch || g.W + 1 == pitch);
+}
+
 int make_tmap_flat(CUtensorMap* tm, const void* x, int N, int H, int W, int C, const char** err) {
+  return make_tmap_flat_pitch(tm, x, N, H, W, C, conv_flat_pitch(W), err);
+}
+
+// Tiled 4-D map over NHWC [N][H][W][C] whose box is one 64-channel slice of `pitch` pixels of one row.
+int make_tmap_flat_pitch(CUtensorMap* tm, const void* x, int N, int H, int W, int C, int pitch, const char** err) {
   static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
   if (!fn) { *err = "cuTensorMapEncodeTiled entry point not found"; return -1; }
   cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(N)};
   cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2, static_cast<cuuint64_t>(H) * W * C * 2};
-  cuuint32_t box[4] = {64, static_cast<cuuint32_t>(conv_flat_pitch(W)), 1, 1};
+  cuuint32_t box[4] = {64, static_cast<cuuint32_t>(pitch), 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,

@@ -489,6 +489,17 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
         d.pair = 1;
       }
 
+      // 3x3 / s1 convs whose weights do not fit in shared memory (layer4, layer3): the same flattened rows with the weights
+      // streamed through a ring (conv3x3_flat_stream_kernel).  B2I_FLATS_MAXW = widest map that takes this path
+      // (default 0 = off: measured slower than the im2col form on layer4 and layer3, profiles/r03_layer4_tiling_matrix.txt; 7 = layer4, 14 = layer3 too).
+      static const int flats_maxw = [] { const char* e = getenv("B2I_FLATS_MAXW"); return e ? atoi(e) : 0; }();
+      if (flat_on && !d.flat && cfg_.pair_mma && cfg_.precision != PREC_FP32 && !d.patch && !o.fc && d.amode == A_IM2COL &&
+          g.W <= flats_maxw && d.BN >= 128 && conv_flat_stream_applicable(g, d.BN)) {
+        d.flat = 2;
+        d.pair = 1;
+        d.resident_b = 0;
+      }
+
       // CTA-pair im2col layers: an im2col TMA request costs ~700 cycles whatever its size (tools/microbench/
       // tma_rate.cu), so a CTA that owns `msub` 128-row sub-tiles (one request of msub * 128 pixels per k-block)
       // feeds msub times the MMAs per request.  It also divides the number of tiles, and when msub * BN exceeds 256
@@ -575,7 +586,7 @@ bool DeviceModel::init(int device, const NetSpec& net, const EngineConfig& cfg, 
           if (o.res >= 0 && make_tmap_tile(&d.tmR, bufs_[tensor_buf_[o.res]], mb_, g.H, g.W, &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.flat) {
-          if (make_tmap_flat(&d.tmA, xin, mb_, g.H, g.W, g.C, &terr)) { *err = c.name + ": " + terr; return false; }
+          if (make_tmap_flat_pitch(&d.tmA, xin, mb_, g.H, g.W, g.C, d.flat == 2 ? conv_flat_stream_pitch(g.W) : conv_flat_pitch(g.W), &terr)) { *err = c.name + ": " + terr; return false; }
           d.has_tmA = true;
         } else if (d.amode == A_IM2COL) {
           if (make_tmap_im2col_px(&d.tmA, xin, g, mb_, 128 * d.msub, &terr)) { *err = c.name + ": " + terr; return false; }

@@ -86,7 +86,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
 #ifdef B2I_STEM_TRACE
   if (tid == 0 && blockIdx.x < 512) g_stem_cta[blockIdx.x][0] = stem_now_ns();
 #endif
-  const int warp = tid >> 5;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t b_smem = base;
@@ -113,7 +113,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   griddep_wait();   // the pooled map written below may still be read by the previous forward's kernels
 
   if (warp == 8) {

@@ -110,7 +110,7 @@ stem2_kernel(const Stem2Params p) {
   __shared__ int tile_ring[8];                // tile of iteration i (or -1 = this loader group is out of tiles)
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t patch0 = base;
@@ -135,7 +135,7 @@ stem2_kernel(const Stem2Params p) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   if (warp < 4) {
     // weights -> tensor memory, once: thread = row (parity, channel) of its warp's lane quarter
     const uint32_t* src = p.w2 + static_cast<size_t>(warp * 32 + lane) * (KCHUNKS * 8);

@@ -65,7 +65,7 @@ alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p
   __shared__ uint32_t tmem_slot;
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_smem = base;
@@ -91,7 +91,7 @@ alex_stem_kernel(const __grid_constant__ CUtensorMap tmW, const AlexStemParams p
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
   if (warp == 8 && lane == 0) {   // the weights do not depend on the previous kernel
     tma_prefetch_desc(&tmW);
     mbar_expect_tx(w_full, AW_BYTES);
