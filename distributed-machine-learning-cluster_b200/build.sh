@@ -7,7 +7,7 @@ OUT="$HERE/libb200infer.so"
 OBJ="$HERE/build"
 mkdir -p "$OBJ"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
-FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-ffp-contract=off,-Wall,-Wno-unused-function)
+FLAGS=(${B2I_EXTRA_NVCC_FLAGS:-} -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-ffp-contract=off,-Wall,-Wno-unused-function)
 pids=()
 for f in conv_umma.cu stem.cu stem2.cu stem_alex.cu conv_fp32.cu misc_kernels.cu resize.cu ot_reader.cpp engine.cpp predict.cpp jpeg_decode.cpp capi.cpp; do
   o="$OBJ/${f%.*}.o"

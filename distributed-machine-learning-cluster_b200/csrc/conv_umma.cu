@@ -14,6 +14,7 @@
 // both TMA (CU_TENSOR_MAP_SWIZZLE_128B) and the hand gather produce and what the UMMA shared-memory
 // descriptors in ptx.cuh declare.
 #include <algorithm>
+#include <cstdio>
 
 #include "conv.h"
 #include "ptx.cuh"
@@ -57,11 +58,14 @@ struct KP {
   float* ws;
   int* ctr;
   int a_rows;   // persistent kernel, A_TILED: rows of the A box (the tensor map's), 128 unless the layer has fewer rows
+  long long* trace;   // pair kernel, debugging (B2I_PAIR_TRACE=1): clock stamps of one CTA's producers and MMA warp, else null
+  int trace_cta;
 };
 
 // Where one tile's results go.
 struct Epi {
   const float* bias;
+  uint32_t bias_smem;   // shared-memory copy of `bias` (address; 0 = none): the epilogue reads it from there instead of L2
   const __nv_bfloat16* residual;
   void* out;
   int ldo, relu, out_fp32, Cout, f16;
@@ -69,6 +73,7 @@ struct Epi {
 __device__ __forceinline__ Epi epi_of(const KP& p, bool second) {
   Epi e;
   e.bias = second ? p.bias2 : p.bias;
+  e.bias_smem = 0;
   e.residual = second ? nullptr : p.residual;
   e.out = second ? p.out2 : p.out;
   e.ldo = second ? p.ldo2 : p.ldo;
@@ -125,14 +130,26 @@ template <bool F16>
 __device__ __forceinline__ void epilogue_chunk(const Epi& p, int m, int nb, const uint32_t (&v)[32],
                                                const uint32_t (*rpre)[16] = nullptr) {
   float f[32];
-  const float4* b4 = reinterpret_cast<const float4*>(p.bias + nb);   // bias is padded to Cout_pad: always in range
+  if (p.bias_smem) {   // staged at kernel start: no L2 round trip between the accumulator and the store
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float4 b = __ldg(b4 + j);
-    f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
-    f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
-    f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
-    f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+    for (int j = 0; j < 8; ++j) {
+      float4 b;
+      asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "r"(p.bias_smem + static_cast<uint32_t>(nb + 4 * j) * 4u));
+      f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+      f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+      f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+      f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+    }
+  } else {
+    const float4* b4 = reinterpret_cast<const float4*>(p.bias + nb);   // bias is padded to Cout_pad: always in range
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 b = __ldg(b4 + j);
+      f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+      f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+      f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+      f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+    }
   }
   if (p.out_fp32) {
     float* o = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
@@ -683,16 +700,24 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) 
 // round-robin to `nprod` producer warps (warp 0 and warps 10 ..), each walking the same tile / stage sequence
 // and issuing every nprod-th request: with three of them a request completes every ~300 cycles, around the MMA
 // time of a k-block (256 cycles at tile-N 128, 512 at 256).
+// -DB2I_PAIR_TRACE compiles clock stamps into the pair kernel (B2I_PAIR_TRACE=1 at run time prints them per launch)
+#ifdef B2I_PAIR_TRACE
+constexpr bool kPairTrace = true;
+#else
+constexpr bool kPairTrace = false;
+#endif
 constexpr int PAIR_MAX_PROD = 3;   // 384 threads: one more warp would push the epilogue warps under the registers they need (spills)
 constexpr int PAIR_THREADS = PTHREADS + 32 * (PAIR_MAX_PROD - 1);
 template <int AMODE, bool F16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PAIR_THREADS, 1)
 conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmB2, const KP p) {
+  const long long t_start = kPairTrace ? clock64() : 0;
   griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * MAX_STAGES + 5];
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float bias_s[1024];   // bias of the layer (and of a riding downsample): constants, staged before the wait for the previous grid
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
@@ -743,6 +768,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
+  const int nbias1 = p.tiles_n * p.BN, nbias2 = p.tiles_n2 * p.BN;
+  const bool bias_staged = nbias1 + nbias2 <= 1024;
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
                  "r"(p.tmem_cols)
@@ -764,6 +791,7 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         tma_load_2d_2sm(smem_base + (p.num_kb + j) * b_tile_bytes, &tmB2, b_full_bar, j * BK, nrow);
   }
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
+  if (kPairTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta && threadIdx.x == 0) { p.trace[8000] = t_start; p.trace[8001] = clock64(); }
 
   const int prod_id = warp == 0 ? 0 : (warp >= PTHREADS / 32 ? warp - PTHREADS / 32 + 1 : -1);
   if (prod_id >= 0) {
@@ -772,6 +800,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int ohw = p.OH * p.OW;
       int s = 0, ph = 0;
       int turn = 0;   // whose k-block the next one is
+      int g = 0;      // k-block sequence number (trace)
+      const bool tr = kPairTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta;
       for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters) {
         const int t = p.rev ? total_tiles - 1 - t0 : t0;   // snake order: start with what the producer wrote last
         const int tm = t / tn_all;
@@ -798,7 +828,9 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const bool mine = turn == prod_id;
           if (++turn == p.nprod) turn = 0;
           if (mine) {
+            if (tr) p.trace[4096 + g * 4] = clock64();
             mbar_wait(empty_bar(s), ph ^ 1);
+            if (tr) p.trace[4096 + g * 4 + 1] = clock64();
             const uint32_t a_s = ring_base + s * stage_bytes;
             if (leader) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
             else mbar_arrive_cluster(full_bar(s), 0);
@@ -812,7 +844,9 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
               if (second) tma_load_2d_2sm(a_s + a_bytes, &tmB2, full_bar(s), j * BK, n0);
               else tma_load_2d_2sm(a_s + a_bytes, &tmB, full_bar(s), kb * BK, n0);
             }
+            if (tr) { p.trace[4096 + g * 4 + 2] = clock64(); p.trace[4096 + g * 4 + 3] = prod_id; }
           }
+          ++g;
           if (AMODE == A_IM2COL && ++cblk == cpb) {
             cblk = 0;
             if (++sx == p.S) { sx = 0; ++r; }
@@ -826,17 +860,22 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const uint32_t idesc = umma_idesc_bf16(256, p.BN, F16 ? 1 : 0);
       if (resb) mbar_wait(b_full_bar, 0);
       int s = 0, ph = 0, i = 0;
+      int g = 0;
+      const bool tr = kPairTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta && lane == 0;
       for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters, ++i) {
         const int t = p.rev ? total_tiles - 1 - t0 : t0;
         const int buf = acc2 ? (i & 1) : 0;
         const int use = acc2 ? (i >> 1) : i;          // how often this accumulator buffer has been used before
+        if (tr) p.trace[g * 4 + 3] = clock64();
         mbar_wait(acc_empty_bar(buf), (use & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * acc_cols);
         const bool second = (t % tn_all) >= p.tiles_n;
         const int kb_count = second ? p.num_kb2 : p.num_kb;
         for (int kb = 0; kb < kb_count; ++kb) {
+          if (tr) p.trace[g * 4] = clock64();
           mbar_wait(full_bar(s), ph);
+          if (tr) p.trace[g * 4 + 1] = clock64();
           tc_fence_after();
           {
             const uint32_t a_s = ring_base + s * stage_bytes;
@@ -853,6 +892,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             umma_commit_2sm(empty_bar(s));
             if (kb == kb_count - 1) umma_commit_2sm(acc_full_bar(buf));
           }
+          if (tr) p.trace[g * 4 + 2] = clock64();
+          ++g;
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -862,6 +903,11 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int half = (warp - 2) >> 2;
     const int n_chunks = p.BN >> 5;
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
+    if (bias_staged) {   // by the epilogue warps alone, while the first tile's operands are on their way
+      for (int i = threadIdx.x - 64; i < nbias1; i += 256) bias_s[i] = __ldg(p.bias + i);
+      for (int i = threadIdx.x - 64; i < nbias2; i += 256) bias_s[nbias1 + i] = __ldg(p.bias2 + i);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
     int i = 0;
     for (int t0 = cluster_id; t0 < total_tiles; t0 += num_clusters, ++i) {
       const int t = p.rev ? total_tiles - 1 - t0 : t0;
@@ -872,7 +918,8 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const bool second = nn >= p.tiles_n;
       const int m0 = (tm * 2 + static_cast<int>(rank)) * rows_cta;
       const int n0 = (second ? nn - p.tiles_n : nn) * p.BN;
-      const Epi epi = epi_of(p, second);
+      Epi epi = epi_of(p, second);
+      if (bias_staged) epi.bias_smem = smem_u32(bias_s) + (second ? static_cast<uint32_t>(nbias1) * 4u : 0u);
       // the residual of the first sub-tile is fetched before the accumulator is waited for
       int m = m0 + q * 32 + lane;
       bool row_ok = m < p.M;
@@ -896,8 +943,11 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const int c = half + 2 * j;
           if (c >= n_chunks) break;
           uint32_t v[32];
+          const bool tre = kPairTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta && threadIdx.x == 64 && i < 4;
+          if (tre) p.trace[6000 + (i * 4 + j) * 4] = clock64();
           tmem_ld32(t_row + static_cast<uint32_t>(c * 32), v);
           tmem_ld_wait();
+          if (tre) p.trace[6000 + (i * 4 + j) * 4 + 1] = clock64() + (v[0] & 0);
           if (c == last_c && sb == msub - 1) {
             tc_fence_before();
             __syncwarp();
@@ -907,14 +957,17 @@ conv_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             }
           }
           if (row_ok) epilogue_chunk<F16>(epi, m, n0 + c * 32, v, pre ? &rr[j] : nullptr);
+          if (tre) p.trace[6000 + (i * 4 + j) * 4 + 2] = clock64();
         }
       }
     }
   }
 
+  if (kPairTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta && threadIdx.x == 64) p.trace[8002] = clock64();   // first epilogue thread done
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();   // the peer may still be arriving on / reading this CTA's barriers and smem
+  if (kPairTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta && threadIdx.x == 0) p.trace[8003] = clock64();
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
@@ -1083,7 +1136,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     const int n_chunks = p.BN >> 5;
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
     Epi epi;
-    epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
+    epi.bias = p.bias; epi.bias_smem = 0; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
     int i = 0;
     for (int t0 = cluster_id; t0 < p.total_pairs; t0 += num_clusters, ++i) {
       const int t = p.rev ? p.total_pairs - 1 - t0 : t0;
@@ -1304,7 +1357,7 @@ conv3x3_flat_stream_kernel(const __grid_constant__ CUtensorMap tmX, const __grid
     const int n_chunks = p.BN >> 5;
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
     Epi epi;
-    epi.bias = p.bias; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
+    epi.bias = p.bias; epi.bias_smem = 0; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
     int i = 0;
     for (int w0 = cluster_id; w0 < total_items; w0 += num_clusters, ++i) {
       const int w = p.rev ? total_items - 1 - w0 : w0;
@@ -1615,6 +1668,8 @@ void fill_kp(KP* p, const ConvArgs& a) {
   p->rev = a.reverse;
   p->nprod = 1;
   p->a_rows = BM;
+  p->trace = nullptr;
+  p->trace_cta = 0;
   p->splits = 1;
   p->ldw = 0;
   p->ws = nullptr;
@@ -1674,7 +1729,7 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   if (dev >= 16) return cudaErrorInvalidDevice;
   auto kern = conv_umma_pair_kernel<AMODE, F16>;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 221 * 1024);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
@@ -1694,9 +1749,9 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   int grid = std::min(2 * total, sm_count[dev] & ~1);
   size_t smem = static_cast<size_t>(p.stages) * stage + 1024;
   const size_t resb_bytes = static_cast<size_t>(p.num_kb + (p.tiles_n2 ? p.num_kb2 : 0)) * (a.BN / 2) * 128;
-  if (a.resident_b && p.tiles_n == 1 && p.tiles_n2 <= 1 && resb_bytes + 3 * a_bytes + 1024 <= 226 * 1024) {
+  if (a.resident_b && p.tiles_n == 1 && p.tiles_n2 <= 1 && resb_bytes + 3 * a_bytes + 1024 <= 221 * 1024) {
     p.resb = 1;
-    p.stages = std::min<int>(MAX_STAGES, static_cast<int>((226 * 1024 - 1024 - resb_bytes) / a_bytes));
+    p.stages = std::min<int>(MAX_STAGES, static_cast<int>((221 * 1024 - 1024 - resb_bytes) / a_bytes));
     smem = resb_bytes + static_cast<size_t>(p.stages) * a_bytes + 1024;
   }
   if (p.stages < 3) return cudaErrorInvalidValue;
@@ -1705,6 +1760,51 @@ cudaError_t launch_pair(const ConvArgs& a, const CUtensorMap* tmA, const CUtenso
   static const int nprod_env = [] { const char* e = getenv("B2I_NPROD"); return e ? atoi(e) : 0; }();
   p.nprod = nprod_env >= 1 && nprod_env <= PAIR_MAX_PROD ? nprod_env : (AMODE == A_IM2COL ? PAIR_MAX_PROD : 1);
   p.nprod = std::min(p.nprod, p.stages);
+  static const bool trace_on = [] { const char* e = getenv("B2I_PAIR_TRACE"); return e && e[0] == '1'; }();
+  if (kPairTrace && trace_on) {   // debugging: run this launch alone and print what CTA 0's producers and MMA warp saw, k-block by k-block
+    static long long* d_trace = nullptr;
+    if (!d_trace) cudaMalloc(&d_trace, 8192 * sizeof(long long));
+    cudaMemsetAsync(d_trace, 0, 8192 * sizeof(long long), st);
+    p.trace = d_trace;
+    static const int trace_cta = [] { const char* e = getenv("B2I_PAIR_TRACE_CTA"); return e ? atoi(e) : 0; }();
+    p.trace_cta = trace_cta < grid ? (trace_cta & ~1) : 0;
+    cudaError_t e = launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PAIR_THREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return e;
+    static long long h[8192];
+    cudaMemcpy(h, d_trace, sizeof h, cudaMemcpyDeviceToHost);
+    const int my_tiles = (total - p.trace_cta / 2 + grid / 2 - 1) / (grid / 2);
+    const int per_cta = my_tiles * p.num_kb;
+    fprintf(stderr, "[pair trace] CTA %d: kernel entry -> past the wait for the previous grid %lld cycles; -> first MMA-warp wait %lld; last MMA issued at %lld; epilogue warps done at %lld; cluster released at %lld\n",
+            p.trace_cta, h[8001] - h[8000], h[0] - h[8000], h[(std::min(per_cta, 1000) - 1) * 4 + 2] - h[8000], h[8002] - h[8000], h[8003] - h[8000]);
+    const int n = std::min(per_cta, 1000);
+    long long wait_full = 0, wait_empty = 0, issue = 0, lat = 0;
+    int lat_n = 0;
+    for (int g = 0; g < n; ++g) {
+      wait_full += h[g * 4 + 1] - h[g * 4];
+      if (h[4096 + g * 4 + 1]) {
+        wait_empty += h[4096 + g * 4 + 1] - h[4096 + g * 4];
+        issue += h[4096 + g * 4 + 2] - h[4096 + g * 4 + 1];
+        if (h[g * 4 + 1] > h[4096 + g * 4 + 2]) { lat += h[g * 4 + 1] - h[4096 + g * 4 + 2]; ++lat_n; }
+      }
+    }
+    const long long span = h[(n - 1) * 4 + 2] - h[0];
+    fprintf(stderr, "[pair trace] M %d Cout %d K %d BN %d msub %d stages %d nprod %d grid %d: %d k-blocks in CTA 0, %lld cycles = %.0f per k-block; MMA warp waited for data %.0f per k-block; producers waited for a free stage %.0f, spent %.0f issuing; request issued -> MMA saw it full %.0f (n %d)\n",
+            a.g.M, a.g.Cout, a.g.K, a.BN, p.msub, p.stages, p.nprod, grid, n, span, static_cast<double>(span) / n, static_cast<double>(wait_full) / n,
+            static_cast<double>(wait_empty) / n, static_cast<double>(issue) / n, lat_n ? static_cast<double>(lat) / lat_n : 0.0, lat_n);
+    for (int i = 0; i < my_tiles && i < 4; ++i)
+      for (int j = 0; j < 4; ++j)
+        if (h[6000 + (i * 4 + j) * 4])
+          fprintf(stderr, "    epilogue warp 2, tile %d chunk %d: starts at %lld, accumulator read %lld cycles, bias / residual / store %lld cycles\n", i, j,
+                  h[6000 + (i * 4 + j) * 4] - h[8000], h[6000 + (i * 4 + j) * 4 + 1] - h[6000 + (i * 4 + j) * 4], h[6000 + (i * 4 + j) * 4 + 2] - h[6000 + (i * 4 + j) * 4 + 1]);
+    if (getenv("B2I_PAIR_TRACE_DUMP")) {
+      for (int g = 0; g < std::min(n, 80); ++g)
+        fprintf(stderr, "  kb %3d prod %lld: empty-wait %6lld..%6lld issued %6lld | mma full-wait %6lld..%6lld done-issue %6lld\n", g, h[4096 + g * 4 + 3],
+                h[4096 + g * 4] - h[0], h[4096 + g * 4 + 1] - h[0], h[4096 + g * 4 + 2] - h[0], h[g * 4] - h[0], h[g * 4 + 1] - h[0], h[g * 4 + 2] - h[0]);
+    }
+    return cudaSuccess;
+  }
   return launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(PAIR_THREADS), smem, st, *tmA, *tmB, a.tmB2 ? *a.tmB2 : *tmB, p);
 }
 

@@ -1,0 +1,20 @@
+#!/bin/bash
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+true
+true
+run() {  # label, env...
+  label=$1; shift
+  env "$@" timeout 300 python bench.py --steps 20 --warmup 5 --no-extras --cpu-budget 0.2 > gpurun_out/v_$label.json 2> gpurun_out/v_$label.err || tail -2 gpurun_out/v_$label.err
+  python - "$label" <<'P'
+import json,sys
+d=json.load(open('gpurun_out/v_%s.json' % sys.argv[1]))
+L=d['launch_ms']
+print('%-10s value %d step %.4f |' % (sys.argv[1], d['value'], d['ms_per_step']), ' '.join('%.4f' % v for k,v in list(L.items())[5:17]))
+P
+}
+run new A=1
+run prev B2I_LIB=/root/repo/ab/libb200infer_prev.so
+run new_b A=1
+run prev_b B2I_LIB=/root/repo/ab/libb200infer_prev.so
+timeout 600 python -m pytest tests/test_kernels_gpu.py tests/test_model_gpu.py -q -m gpu -p no:cacheprovider -x 2>&1 | tail -2
