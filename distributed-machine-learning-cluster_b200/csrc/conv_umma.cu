@@ -1019,6 +1019,7 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * FLAT_MAXBUF + 5];   // full[], empty[], acc_full[2], acc_empty[2], b_full
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float bias_s[256];   // the layer's bias, staged by the epilogue warps (one N tile of at most 256 channels)
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = threadIdx.x & 31;
@@ -1135,8 +1136,10 @@ conv3x3_flat_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     const int half = (warp - 2) >> 2;
     const int n_chunks = p.BN >> 5;
     const int last_c = ((n_chunks - 1 - half) & ~1) + half;
+    for (int i = threadIdx.x - 64; i < p.BN; i += 256) bias_s[i] = __ldg(p.bias + i);
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     Epi epi;
-    epi.bias = p.bias; epi.bias_smem = 0; epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
+    epi.bias = p.bias; epi.bias_smem = smem_u32(bias_s); epi.residual = p.residual; epi.out = p.out; epi.ldo = p.ldo; epi.relu = p.relu; epi.out_fp32 = 0; epi.Cout = p.Cout; epi.f16 = p.f16;
     int i = 0;
     for (int t0 = cluster_id; t0 < p.total_pairs; t0 += num_clusters, ++i) {
       const int t = p.rev ? p.total_pairs - 1 - t0 : t0;
@@ -1850,7 +1853,7 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   cudaGetDevice(&dev);
   if (dev >= 16) return cudaErrorInvalidDevice;
   if (!attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(conv3x3_flat_pair_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_flat_pair_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
@@ -1866,7 +1869,7 @@ cudaError_t launch_flat(const ConvArgs& a, const CUtensorMap* tmX, const CUtenso
   p.total_pairs = (p.rows_total + 2 * p.rpt - 1) / (2 * p.rpt);
   const size_t resb = static_cast<size_t>(9) * p.slices * (a.BN / 2) * 128;
   const size_t patch = static_cast<size_t>(p.rpt + 2) * p.pitch * 128 + 1024;
-  p.nbuf = static_cast<int>(std::min<size_t>(FLAT_MAXBUF, (226 * 1024 - 1024 - resb) / patch));
+  p.nbuf = static_cast<int>(std::min<size_t>(FLAT_MAXBUF, (225 * 1024 - 1024 - resb) / patch));
   p.ldo = a.ldo; p.relu = a.relu; p.Cout = g.Cout; p.f16 = a.f16; p.rev = a.reverse;
   uint32_t cols = 32;
   while (cols < static_cast<uint32_t>(2 * a.BN)) cols <<= 1;

@@ -10,7 +10,7 @@ run() {  # label, env...
 import json,sys
 d=json.load(open('gpurun_out/v_%s.json' % sys.argv[1]))
 L=d['launch_ms']
-print('%-10s value %d step %.4f |' % (sys.argv[1], d['value'], d['ms_per_step']), ' '.join('%.4f' % v for k,v in list(L.items())[5:17]))
+print('%-10s value %d step %.4f |' % (sys.argv[1], d['value'], d['ms_per_step']), ' '.join('%.4f' % v for k,v in list(L.items())[:17]))
 P
 }
 run new A=1
