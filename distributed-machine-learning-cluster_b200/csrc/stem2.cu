@@ -29,6 +29,8 @@
 //   warps 0-15  two epilogue groups of eight warps: two sets (pooled rows 0-3 / 4-6) x four TMEM lane quarters
 //   warps 16-17 MMA issue, one per half of the tile's columns
 //   warps 18-25 two loader groups of four warps
+#include <cstdio>
+#include <cstdlib>
 #include "conv.h"
 #include "ops.h"
 #include "ptx.cuh"
@@ -37,14 +39,15 @@ namespace b2i {
 namespace {
 
 constexpr int S2_DRAIN = 512;
-constexpr int S2_GROUP = 128;                          // threads of one loader group
+constexpr int S2_GROUP = 192;                          // threads of one loader group
 constexpr int S2_MMA_WARPS = 2;                         // one per half of the tile's columns: see the kernel
 constexpr int S2_THREADS = S2_DRAIN + 32 * S2_MMA_WARPS + 2 * S2_GROUP;
 constexpr int PATCH_H = 37, PATCH_W = 40;              // pixels of 8 bytes (r, g, b, 0 in the 16-bit storage format)
 constexpr uint32_t PATCH_ROW_BYTES = PATCH_W * 8;      // 320
 constexpr uint32_t PATCH_BYTES = ((PATCH_H * PATCH_W * 8 + 127) / 128) * 128;
 constexpr uint32_t X_BYTES = 2 * 49 * 128;             // pooled candidates of one tile: [parity][7 x 7][64] 16-bit
-constexpr uint32_t S2_SMEM = 2 * PATCH_BYTES + 2 * X_BYTES + 1024;
+constexpr int S2_PBUF = 2;                              // patch buffers per loader group: a group converts its next tile while the MMAs read its last one
+constexpr uint32_t S2_SMEM = 2 * S2_PBUF * PATCH_BYTES + 2 * X_BYTES + 1024;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t A_COL = 256;                        // weights: columns 256 .. 399 (18 K chunks x 8 columns)
 constexpr int KCHUNKS = 18;                            // 9 input rows x 2 halves of 4 taps x 4 channels
@@ -56,7 +59,13 @@ struct Stem2Params {
   float bias[64];
   int total_tiles;      // N * 64
   unsigned int* sched;  // [0] tiles handed out beyond the first 2 per CTA, [1] CTAs done; both zero between launches
+  long long* trace;     // -DB2I_STEM2_TRACE + B2I_STEM2_TRACE=1: clock stamps of CTA 0's roles, else null
 };
+#ifdef B2I_STEM2_TRACE
+constexpr bool kS2Trace = true;
+#else
+constexpr bool kS2Trace = false;
+#endif
 
 // B-operand descriptor over the raw patch (no swizzle, K-major): row x of an 8-row core matrix is the next conv
 // pixel = 16 bytes on; the next 8-row group is the next row PAIR = 4 patch rows = 1280 bytes; the second core
@@ -105,26 +114,29 @@ __global__ void __launch_bounds__(S2_THREADS, 1)
 stem2_kernel(const Stem2Params p) {
   griddep_launch();
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[8];   // patch_full[2], patch_empty[2], acc_full[2], acc_empty[2]
+  __shared__ __align__(8) uint64_t bars[4 * S2_PBUF + 4];   // patch_full[2 * S2_PBUF], patch_empty[2 * S2_PBUF], acc_full[2], acc_empty[2]
   __shared__ uint32_t tmem_slot;
-  __shared__ int tile_ring[8];                // tile of iteration i (or -1 = this loader group is out of tiles)
+  __shared__ int tile_ring[32];                // tile of iteration i (or -1 = this loader group is out of tiles)
 
   const int tid = threadIdx.x;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform, and the compiler knows it (MMA operands stay in uniform registers)
   const int lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t patch0 = base;
-  const uint32_t x0 = base + 2 * PATCH_BYTES;
+  const uint32_t x0 = base + 2 * S2_PBUF * PATCH_BYTES;
   const uint32_t bar0 = smem_u32(bars);
-  auto patch_full = [&](int b) { return bar0 + 8u * b; };
-  auto patch_empty = [&](int b) { return bar0 + 8u * (2 + b); };
-  auto acc_full = [&](int b) { return bar0 + 8u * (4 + b); };
-  auto acc_empty = [&](int b) { return bar0 + 8u * (6 + b); };
+  // patch buffer of group g's k-th tile: slot g * S2_PBUF + k % S2_PBUF, its barriers flip every S2_PBUF tiles of the group
+  auto patch_full = [&](int s) { return bar0 + 8u * s; };
+  auto patch_empty = [&](int s) { return bar0 + 8u * (2 * S2_PBUF + s); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (4 * S2_PBUF + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (4 * S2_PBUF + 2 + b); };
 
   if (tid == 0) {
+    for (int s = 0; s < 2 * S2_PBUF; ++s) {
+      mbar_init(patch_full(s), S2_GROUP);
+      mbar_init(patch_empty(s), S2_MMA_WARPS);   // one commit per MMA-issuing warp
+    }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(patch_full(b), S2_GROUP);
-      mbar_init(patch_empty(b), S2_MMA_WARPS);   // one commit per MMA-issuing warp
       mbar_init(acc_full(b), S2_MMA_WARPS);
       mbar_init(acc_empty(b), 8);
     }
@@ -156,15 +168,15 @@ stem2_kernel(const Stem2Params p) {
 
   if (warp >= MMA_WARP && warp < MMA_WARP + S2_MMA_WARPS) {
     // ------------------------------------------------------------------ MMA issue
-    // Two issuing warps, one per half of the tile's conv columns (its own 64 accumulator columns, the same
-    // weights).  A tcgen05.mma whose A operand is in tensor memory completes about 160 cycles after the same warp's
-    // previous one, whatever its N and however many accumulators the warp rotates through, while MMAs of different
-    // warps overlap (tools/microbench/umma_rate.cu, "A in TMEM" rows: 160.9 cycles per MMA with one issuing warp,
-    // 80.5 with two; the shared-memory form has no such limit).  The 18 MMAs of a half therefore take ~2900 cycles
-    // against 576 of tensor-pipe time, and two warps halve the tile time of one.  Four warps (both accumulator
-    // sets filled at once) were measured slower, 0.146-0.150 ms against 0.138: a set is then held by its MMAs and
-    // by its epilogue's tensor-memory reads in turn, with nothing to overlap them.  tcgen05.commit tracks the MMAs
-    // of the committing thread, so both warps commit and the barriers count two arrivals.
+    // Two issuing warps, one per half of the tile's conv columns (its own 64 accumulator columns, the same weights).
+    // History: an earlier reading of tools/microbench/umma_rate.cu had a TMEM-A MMA complete ~160 cycles after the same
+    // warp's previous one whatever its N; that was the issuing loop of the benchmark (and of this kernel) ferrying
+    // descriptors into uniform registers under `lane == 0`, not the tensor pipe.  Issued warp-uniformly the TMEM-A form
+    // runs at the same floor as the shared-memory form (profiles/r03_microbench_umma_tmem_a_lean_issue.txt), and the
+    // 36 MMAs of a tile are ~1150 cycles of pipe time.  What the clock stamps of one CTA show now (-DB2I_STEM2_TRACE):
+    // ~1700 cycles per tile, with the loader groups (~2000 cycles of conversion per tile and group), the accumulator
+    // hand-over (MMAs ~1100 + epilogue reads ~1200 per set) and the epilogue groups all near that rate.
+    // tcgen05.commit tracks the MMAs of the committing thread, so both warps commit and the barriers count two arrivals.
     const int hx = warp - MMA_WARP;
     const uint32_t idesc = umma_idesc_bf16(128, 64, F16 ? 1 : 0);
     bool done[2] = {false, false};
@@ -175,15 +187,21 @@ stem2_kernel(const Stem2Params p) {
         continue;
       }
       const uint32_t ph = static_cast<uint32_t>((i >> 1) & 1);
+      const bool tr = kS2Trace && p.trace != nullptr && blockIdx.x == 0 && hx == 0 && lane == 0 && i < 200;
+      if (tr) p.trace[i * 12 + 0] = clock64();
+      const int kk = i >> 1;                                   // the group's tile number
+      const int ps = b * S2_PBUF + kk % S2_PBUF;               // its patch slot
       mbar_wait(acc_empty(b), ph ^ 1);
-      mbar_wait(patch_full(b), ph);
-      if (*reinterpret_cast<volatile int*>(&tile_ring[i & 7]) < 0) {   // this group is out of tiles: tell the epilogue
+      if (tr) p.trace[i * 12 + 1] = clock64();
+      mbar_wait(patch_full(ps), static_cast<uint32_t>((kk / S2_PBUF) & 1));
+      if (tr) p.trace[i * 12 + 2] = clock64();
+      if (*reinterpret_cast<volatile int*>(&tile_ring[i & 31]) < 0) {   // this group is out of tiles: tell the epilogue
         umma_commit_elect(acc_full(b));
         done[b] = true;
         continue;
       }
       tc_fence_after();
-      const uint32_t pbase = patch0 + b * PATCH_BYTES;
+      const uint32_t pbase = patch0 + ps * PATCH_BYTES;
       {                                         // conv columns 8 * hx .. 8 * hx + 7 of the tile
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 128 + hx * 64);
 #pragma unroll
@@ -192,12 +210,13 @@ stem2_kernel(const Stem2Params p) {
           umma_ts_elect(d_tmem, tmem_base + A_COL + static_cast<uint32_t>(t * 8), patch_desc_pairs(b_addr), idesc, t != 0 ? 1u : 0u);
         }
       }
-      umma_commit_elect(patch_empty(b));   // the loaders may overwrite this patch buffer
+      umma_commit_elect(patch_empty(ps));   // the loaders may overwrite this patch buffer
       umma_commit_elect(acc_full(b));
+      if (tr) p.trace[i * 12 + 3] = clock64();
     }
   } else if (warp >= MMA_WARP + S2_MMA_WARPS) {
     // ------------------------------------------------------------------ patch loaders: group g fills buffer g
-    const int g = (warp - MMA_WARP - S2_MMA_WARPS) >> 2;
+    const int g = (warp - MMA_WARP - S2_MMA_WARPS) / (S2_GROUP / 32);
     const int lt = tid - (S2_DRAIN + 32 * S2_MMA_WARPS) - g * S2_GROUP;
     uint8_t* const gen_base = smem_raw + (base - smem_u32(smem_raw));
     __shared__ int next_tile[2];
@@ -210,19 +229,23 @@ stem2_kernel(const Stem2Params p) {
     int t = 2 * blockIdx.x + g;              // first tile of this group; the rest come from the global counter
     for (int k = 0;; ++k) {
       const int i = 2 * k + g;               // iteration number in the CTA's tile sequence
-      if (lt == 0) tile_ring[i & 7] = t < p.total_tiles ? t : -1;
+      if (lt == 0) tile_ring[i & 31] = t < p.total_tiles ? t : -1;
+      const int ps = g * S2_PBUF + k % S2_PBUF;
+      const uint32_t pph = static_cast<uint32_t>((k / S2_PBUF) & 1);
       if (t >= p.total_tiles) {
-        mbar_wait(patch_empty(g), static_cast<uint32_t>((k & 1) ^ 1));
-        mbar_arrive(patch_full(g));
+        mbar_wait(patch_empty(ps), pph ^ 1);
+        mbar_arrive(patch_full(ps));
         break;
       }
       unsigned int ticket = 0;
       if (lt == 0) ticket = atomicAdd(p.sched, 1u);
+      const bool trl = kS2Trace && p.trace != nullptr && blockIdx.x == 0 && lt == 0 && i < 200;
+      if (trl) p.trace[i * 12 + 4] = clock64();
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
       const int ih0 = 28 * pty - 5, iw0 = 28 * ptx - 5;
       const uint8_t* img = p.in + static_cast<size_t>(n) * (224 * 224 * 3);
-      uint8_t* dst = gen_base + g * PATCH_BYTES;
+      uint8_t* dst = gen_base + ps * PATCH_BYTES;
       uint32_t w[ROUNDS][4];
 #pragma unroll
       for (int r = 0; r < ROUNDS; ++r) {
@@ -238,7 +261,9 @@ stem2_kernel(const Stem2Params p) {
           w[r][j] = (row_ok && o >= 0 && o < 672) ? __ldg(src + j) : 0u;
         }
       }
-      mbar_wait(patch_empty(g), static_cast<uint32_t>((k & 1) ^ 1));
+      if (trl) p.trace[i * 12 + 5] = clock64() + (w[0][0] & 0);
+      mbar_wait(patch_empty(ps), pph ^ 1);
+      if (trl) p.trace[i * 12 + 6] = clock64();
 #pragma unroll
       for (int r = 0; r < ROUNDS; ++r) {
         const int e = lt + r * S2_GROUP;
@@ -267,7 +292,8 @@ stem2_kernel(const Stem2Params p) {
         d4[first ^ 1] = first ? lo : hi;
       }
       fence_proxy_async_smem();
-      mbar_arrive(patch_full(g));
+      mbar_arrive(patch_full(ps));
+      if (trl) p.trace[i * 12 + 7] = clock64();
       if (lt == 0) next_tile[g] = static_cast<int>(2 * gridDim.x + ticket);
       if (g == 0) asm volatile("bar.sync 2, %0;" ::"n"(S2_GROUP) : "memory");
       else asm volatile("bar.sync 3, %0;" ::"n"(S2_GROUP) : "memory");
@@ -286,8 +312,11 @@ stem2_kernel(const Stem2Params p) {
     uint8_t* const x_gen = smem_raw + (x0 - smem_u32(smem_raw));
     for (int k = 0;; ++k) {
       const int i = 2 * k + b;
+      const bool tre = kS2Trace && p.trace != nullptr && blockIdx.x == 0 && (warp & 7) == 0 && lane == 0 && i < 200;
+      if (tre) p.trace[i * 12 + 8] = clock64();
       mbar_wait(acc_full(b), static_cast<uint32_t>(k & 1));
-      const int t = *reinterpret_cast<volatile int*>(&tile_ring[i & 7]);
+      if (tre) p.trace[i * 12 + 9] = clock64();
+      const int t = *reinterpret_cast<volatile int*>(&tile_ring[i & 31]);
       if (t < 0) break;
       const int n = t >> 6;
       const int pty = (t >> 3) & 7, ptx = t & 7;
@@ -342,6 +371,7 @@ stem2_kernel(const Stem2Params p) {
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(b));   // this warp has read what it needs of accumulator set b
+      if (tre) p.trace[i * 12 + 10] = clock64();
       asm volatile("bar.sync %0, %1;" ::"r"(4 + 2 * b + set), "n"(128) : "memory");   // the set's 128 threads
       // the set's pooled rows: max of the two parities' candidates, 16 bytes (8 channels) per task
       const uint8_t* xe = x_gen + b * X_BYTES;
@@ -360,6 +390,7 @@ stem2_kernel(const Stem2Params p) {
       }
       // this group's candidates buffer is rewritten by its next tile: order these reads before those writes
       asm volatile("bar.sync %0, %1;" ::"r"(4 + 2 * b + set), "n"(128) : "memory");
+      if (tre) p.trace[i * 12 + 11] = clock64();
     }
   }
 
@@ -425,6 +456,31 @@ cudaError_t launch_stem2(const uint8_t* in_u8, void* out16, const uint32_t* w2_d
   for (int c = 0; c < 64; ++c) p.bias[c] = bias_host[c];
   p.total_tiles = n_images * 64;
   p.sched = sched;
+  p.trace = nullptr;
+  static const bool trace_on = [] { const char* e = getenv("B2I_STEM2_TRACE"); return e && e[0] == '1'; }();
+  if (kS2Trace && trace_on) {
+    static long long* d_trace = nullptr;
+    if (!d_trace) cudaMalloc(&d_trace, 2400 * sizeof(long long));
+    cudaMemsetAsync(d_trace, 0, 2400 * sizeof(long long), st);
+    p.trace = d_trace;
+    const int grid_t = (p.total_tiles + 1) / 2 < sm_count[dev] ? (p.total_tiles + 1) / 2 : sm_count[dev];
+    cudaError_t e = f16 ? launch_pdl(stem2_kernel<true>, dim3(grid_t), dim3(S2_THREADS), S2_SMEM, st, p)
+                        : launch_pdl(stem2_kernel<false>, dim3(grid_t), dim3(S2_THREADS), S2_SMEM, st, p);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return e;
+    static long long h[2400];
+    cudaMemcpy(h, d_trace, sizeof h, cudaMemcpyDeviceToHost);
+    const long long t0 = h[4] ? h[4] : h[0];
+    fprintf(stderr, "[stem2 trace] CTA 0, tile by tile (cycles since the first loader started): loader: loads issued / data in registers / buffer free / patch written | MMA warp: starts waiting / accumulators free / patch full / MMAs issued | epilogue: starts waiting / accumulators full / accumulators read / tile stored\n");
+    for (int i = 0; i < 200 && (h[i * 12 + 4] || h[i * 12]); ++i) {
+      if (i < 24 || (i % 20) == 0)
+        fprintf(stderr, "  tile %3d: %7lld %7lld %7lld %7lld | %7lld %7lld %7lld %7lld | %7lld %7lld %7lld %7lld\n", i, h[i * 12 + 4] - t0, h[i * 12 + 5] - t0, h[i * 12 + 6] - t0,
+                h[i * 12 + 7] - t0, h[i * 12 + 0] - t0, h[i * 12 + 1] - t0, h[i * 12 + 2] - t0, h[i * 12 + 3] - t0, h[i * 12 + 8] - t0, h[i * 12 + 9] - t0, h[i * 12 + 10] - t0,
+                h[i * 12 + 11] - t0);
+    }
+    return cudaSuccess;
+  }
   const int grid = (p.total_tiles + 1) / 2 < sm_count[dev] ? (p.total_tiles + 1) / 2 : sm_count[dev];
   if (f16) return launch_pdl(stem2_kernel<true>, dim3(grid), dim3(S2_THREADS), S2_SMEM, st, p);
   return launch_pdl(stem2_kernel<false>, dim3(grid), dim3(S2_THREADS), S2_SMEM, st, p);

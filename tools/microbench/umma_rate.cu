@@ -131,23 +131,29 @@ __global__ void __launch_bounds__(128, 1) ts_kernel(int N, int chains, int issue
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if ((warp == 1 || (warp == 2 && issuers == 2)) && lane == 0) {
-    const int me = warp - 1;
+  // The issuing loop runs WARP-UNIFORM (every lane executes it, one elected lane issues): a loop under `lane == 0`
+  // costs ~15-20 instructions per MMA of descriptor traffic into uniform registers, which is what an earlier
+  // version of this benchmark measured (161 cycles per MMA whatever N) instead of the tensor pipe.
+  const int uwarp = __shfl_sync(0xffffffffu, warp, 0);
+  const uint32_t utm = __shfl_sync(0xffffffffu, tm, 0);
+  if (uwarp == 1 || (uwarp == 2 && issuers == 2)) {
+    const int me = uwarp - 1;
     const uint32_t idesc = umma_idesc_bf16(128, N);
+    const uint32_t d0 = utm + static_cast<uint32_t>((me * chains * N) % 384);
     long long t0 = clock64();
     for (int it = 0; it < iters; ++it) {
       const uint64_t bd = umma_smem_desc_sw128(base + (it & 3) * 32768);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint32_t d = tm + static_cast<uint32_t>(((me * chains + (it * 4 + k) % chains) * N) % 384);
-        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
-                     "r"(tm + 384 + 8 * k), "l"(bd + 2u * k), "r"(idesc), "r"(1u) : "memory");
+        const uint32_t d = d0 + static_cast<uint32_t>(((it * 4 + k) & (chains - 1)) * N);   // chains is a power of two
+        asm volatile("{\n\t.reg .pred p, pe;\n\telect.sync _|pe, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t@pe tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+                     "r"(utm + 384 + 8 * k), "l"(bd + 2u * k), "r"(idesc), "r"(1u) : "memory");
       }
     }
-    umma_commit(smem_u32(&bar[me]));
+    umma_commit_elect(smem_u32(&bar[me]));
     mbar_wait(smem_u32(&bar[me]), 0);
     long long t1 = clock64();
-    if (blockIdx.x == 0 && me == 0) cycles[0] = t1 - t0;
+    if (blockIdx.x == 0 && me == 0 && lane == 0) cycles[0] = t1 - t0;
   }
   tc_fence_before();
   __syncthreads();
