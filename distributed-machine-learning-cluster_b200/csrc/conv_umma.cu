@@ -1430,6 +1430,7 @@ struct PatchP {
   const float* bias;
   const __nv_bfloat16* residual;
   __nv_bfloat16* out;
+  long long* trace;   // -DB2I_PAIR_TRACE + B2I_PATCH_TRACE=1: clock stamps of CTA 0
 };
 
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0,
@@ -1534,8 +1535,12 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       const int b = i & 1;
       const int pbuf = i % PT_BUFS;
+      const bool tr = kPairTrace && p.trace != nullptr && blockIdx.x == 0 && lane == 0 && i < 200;
+      if (tr) p.trace[i * 8] = clock64();
       mbar_wait(acc_empty(b), ((i >> 1) & 1) ^ 1);
+      if (tr) p.trace[i * 8 + 1] = clock64();
       mbar_wait(patch_full(pbuf), (i / PT_BUFS) & 1);
+      if (tr) p.trace[i * 8 + 2] = clock64();
       tc_fence_after();
       {
         const uint32_t pb = patch0 + pbuf * PT_BYTES;
@@ -1555,6 +1560,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
         umma_commit_elect(patch_empty(pbuf));
         umma_commit_elect(acc_full(b));
       }
+      if (tr) p.trace[i * 8 + 3] = clock64();
     }
   } else {
     const int q = warp & 3;
@@ -1576,7 +1582,10 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       const int n = tt / tiles_per_img;
       const int rem = tt - n * tiles_per_img;
       const int ty = rem / p.tiles_w, tx = rem - ty * p.tiles_w;
+      const bool tre = kPairTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 64 && i < 200;
+      if (tre) p.trace[i * 8 + 4] = clock64();
       mbar_wait(acc_full(b), (i >> 1) & 1);
+      if (tre) p.trace[i * 8 + 5] = clock64();
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(b * 64 + c * 32);
       uint32_t v[32];
@@ -1585,6 +1594,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(b));
+      if (tre) p.trace[i * 8 + 6] = clock64() + (v[0] & 0);
       float f[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + bias[j];
@@ -1624,6 +1634,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
         tma_store_4d(&tmO, out0 + b * PT_TILE_BYTES, 0, tx * 8, ty * 16, n);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
+      if (tre) p.trace[i * 8 + 7] = clock64();
     }
     if (storer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
@@ -1842,6 +1853,26 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
   p.residual = static_cast<const __nv_bfloat16*>(a.residual);
   p.out = static_cast<__nv_bfloat16*>(a.out);
   const int grid = p.total_tiles < sm_count[dev] ? p.total_tiles : sm_count[dev];
+  p.trace = nullptr;
+  static const bool trace_on = [] { const char* e = getenv("B2I_PATCH_TRACE"); return e && e[0] == '1'; }();
+  if (kPairTrace && trace_on) {
+    static long long* d_trace = nullptr;
+    if (!d_trace) cudaMalloc(&d_trace, 1600 * sizeof(long long));
+    cudaMemsetAsync(d_trace, 0, 1600 * sizeof(long long), st);
+    p.trace = d_trace;
+    cudaError_t e = launch_pdl(conv3x3_c64_patch_kernel<F16>, dim3(grid), dim3(PATCH_THREADS), smem, st, *tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return e;
+    static long long h[1600];
+    cudaMemcpy(h, d_trace, sizeof h, cudaMemcpyDeviceToHost);
+    fprintf(stderr, "[patch trace] CTA 0 (residual %d): MMA warp: starts waiting / accumulator free / patch full / MMAs issued | epilogue warp 2: starts waiting / accumulator full / accumulator read / tile staged\n", a.residual ? 1 : 0);
+    for (int i = 0; i < 170 && h[i * 8]; ++i)
+      if (i < 12 || (i >= 100 && i < 112))
+        fprintf(stderr, "  tile %3d: %7lld %7lld %7lld %7lld | %7lld %7lld %7lld %7lld\n", i, h[i * 8] - h[0], h[i * 8 + 1] - h[0], h[i * 8 + 2] - h[0], h[i * 8 + 3] - h[0],
+                h[i * 8 + 4] - h[0], h[i * 8 + 5] - h[0], h[i * 8 + 6] - h[0], h[i * 8 + 7] - h[0]);
+    return cudaSuccess;
+  }
   return launch_pdl(conv3x3_c64_patch_kernel<F16>, dim3(grid), dim3(PATCH_THREADS), smem, st, *tmX, *tmW, a.residual ? *a.tmR : *a.tmO, *a.tmO, p);
 }
 
