@@ -1459,6 +1459,7 @@ __global__ void __launch_bounds__(PATCH_THREADS, 1)
 conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                          const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO,
                          const PatchP p) {
+  const long long t_entry = kPairTrace ? clock64() : 0;
   griddep_launch();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[3 * PT_BUFS + 5];  // patch_full[], patch_empty[], res_empty[], acc_full[2], acc_empty[2], w_full
@@ -1509,6 +1510,7 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     for (int tap = 0; tap < 9; ++tap) tma_load_2d(w_smem + tap * 8192u, &tmW, w_full, tap * 64, 0);
   }
   griddep_wait();   // everything above overlaps the previous kernel's tail; activations are read below
+  if (kPairTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) { p.trace[1590] = t_entry; p.trace[1591] = clock64(); }
   const int tiles_per_img = p.tiles_w * p.tiles_h;
 
   if (warp == 0) {
@@ -1636,7 +1638,9 @@ conv3x3_c64_patch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       }
       if (tre) p.trace[i * 8 + 7] = clock64();
     }
+    if (kPairTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 64) p.trace[1592] = clock64();
     if (storer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (kPairTrace && p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 64) p.trace[1593] = clock64();
   }
 
   tc_fence_before();
@@ -1867,8 +1871,12 @@ cudaError_t launch_patch(const ConvArgs& a, const CUtensorMap* tmX, const CUtens
     static long long h[1600];
     cudaMemcpy(h, d_trace, sizeof h, cudaMemcpyDeviceToHost);
     fprintf(stderr, "[patch trace] CTA 0 (residual %d): MMA warp: starts waiting / accumulator free / patch full / MMAs issued | epilogue warp 2: starts waiting / accumulator full / accumulator read / tile staged\n", a.residual ? 1 : 0);
+    int last = 0;
+    while (last < 170 && h[(last + 1) * 8]) ++last;
+    fprintf(stderr, "  kernel entry -> past the wait for the previous grid %lld cycles; -> MMA warp's first wait %lld; last MMAs issued at %lld (%d tiles); last tile staged at %lld; its store complete at %lld\n",
+            h[1591] - h[1590], h[0] - h[1590], h[last * 8 + 3] - h[1590], last + 1, h[1592] - h[1590], h[1593] - h[1590]);
     for (int i = 0; i < 170 && h[i * 8]; ++i)
-      if (i < 12 || (i >= 100 && i < 112))
+      if (i < 4)
         fprintf(stderr, "  tile %3d: %7lld %7lld %7lld %7lld | %7lld %7lld %7lld %7lld\n", i, h[i * 8] - h[0], h[i * 8 + 1] - h[0], h[i * 8 + 2] - h[0], h[i * 8 + 3] - h[0],
                 h[i * 8 + 4] - h[0], h[i * 8 + 5] - h[0], h[i * 8 + 6] - h[0], h[i * 8 + 7] - h[0]);
     return cudaSuccess;
