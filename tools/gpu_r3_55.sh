@@ -13,8 +13,7 @@ L=d['launch_ms']
 print('%-10s value %d step %.4f |' % (sys.argv[1], d['value'], d['ms_per_step']), ' '.join('%.4f' % v for k,v in list(L.items())[:17]))
 P
 }
-run rolled A=1
+run epw16 A=1
 run prev B2I_LIB=/root/repo/ab/libb200infer_prev.so
-run rolled_notma B2I_NO_TMA_OUT=1
-run unrolled B2I_LIB=/root/repo/ab/libb200infer_unrolled.so
-run rolled_b A=1
+run epw16_b A=1
+run prev_b B2I_LIB=/root/repo/ab/libb200infer_prev.so
